@@ -1,0 +1,85 @@
+// Shared device/host helpers for libb2t_sm100.so (sm_100a only).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#define B2T_OK 0
+#define B2T_EARG (-1)
+
+// thread-local error string, surfaced through b2t_last_error()
+void b2t_set_error(const char* fmt, ...);
+
+#define B2T_CHECK_ARG(cond, ...)                 \
+    do {                                         \
+        if (!(cond)) {                           \
+            b2t_set_error(__VA_ARGS__);          \
+            return B2T_EARG;                     \
+        }                                        \
+    } while (0)
+
+#define B2T_CHECK_LAUNCH(name)                                                     \
+    do {                                                                           \
+        cudaError_t e__ = cudaGetLastError();                                      \
+        if (e__ != cudaSuccess) {                                                  \
+            b2t_set_error("%s: launch failed: %s", name, cudaGetErrorString(e__)); \
+            return (int)e__;                                                       \
+        }                                                                          \
+    } while (0)
+
+#define B2T_CUDA(call)                                                                  \
+    do {                                                                                \
+        cudaError_t e__ = (call);                                                       \
+        if (e__ != cudaSuccess) {                                                       \
+            b2t_set_error("%s failed: %s", #call, cudaGetErrorString(e__));             \
+            return (int)e__;                                                            \
+        }                                                                               \
+    } while (0)
+
+static inline int ceil_div_i(long a, long b) { return (int)((a + b - 1) / b); }
+
+#ifdef __CUDACC__
+typedef __nv_bfloat16 bf16;
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// fp32 -> (hi, lo) bf16 pair with hi + lo ~= x to ~2^-17 relative (the bf16x3 GEMM operand form)
+__device__ __forceinline__ void split_bf16(float x, bf16& hi, bf16& lo) {
+    hi = __float2bfloat16_rn(x);
+    lo = __float2bfloat16_rn(x - __bfloat162float(hi));
+}
+
+__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
+__device__ __forceinline__ float gelu_erf_grad(float x) {
+    const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
+    const float pdf = 0.39894228040143267794f * __expf(-0.5f * x * x);
+    return cdf + x * pdf;
+}
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + __expf(-x)); }
+__device__ __forceinline__ float silu_f(float x) { return x * sigmoidf_(x); }
+__device__ __forceinline__ float silu_grad(float x) {
+    const float s = sigmoidf_(x);
+    return s * (1.0f + x * (1.0f - s));
+}
+
+// stateless counter-based uniform in [0,1): same (seed, idx) -> same value in forward and backward
+__device__ __forceinline__ float hash_uniform(unsigned long long seed, unsigned long long idx) {
+    unsigned long long z = seed + idx * 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z = z ^ (z >> 31);
+    return (float)(z >> 40) * (1.0f / 16777216.0f);
+}
+#endif
