@@ -70,6 +70,13 @@ typedef struct {
     int32_t split_k;          /* >=1; >1 requires atomic, act==0, no hi/lo/pre */
     float   alpha;
     int32_t block_n;          /* 0 = auto, else 64 / 128 / 256 */
+    /* inverted dropout applied after act / act'(aux), before the residual: element `off` is kept
+     * iff hash(drop_seed, off) >= drop_p (off = output offset), so the backward GEMM that passes
+     * the same seed over the same layout regenerates the mask instead of storing it */
+    float    drop_p;
+    uint64_t drop_seed;
+    /* bias row of batch b = bias + slot(b) * bias_batch_stride, slot = b_batch_idx[b] or b (0: shared) */
+    int64_t  bias_batch_stride;
 } b2t_gemm_args;
 
 int b2t_gemm(const b2t_gemm_args* args, b2t_stream stream);
@@ -88,6 +95,80 @@ int b2t_split_bf16(const float* x, void* hi, void* lo, int64_t rows, int64_t col
  * un-materialised unfold view).  inverse=1 maps a gradient in k*C+c order back (fp32 -> fp32). */
 int b2t_permute_unfold_cols(const float* w, void* hi, void* lo, float* out_f32, int64_t rows, int C,
                             int KL, int inverse, b2t_stream stream);
+
+/* ---------------------------------------------------------------------------------------
+ * Stage 1: augmentation + Gaussian smoothing   (src/train/train_loop.py:46-62 intended form,
+ * src/model/b2p2t_model.py:41-90,150-152 GaussianSmoothing / F.conv1d groups=C, padding="same")
+ * x [B,T,C] fp32, taps [C,ntaps]; y = sum_k taps[c][k] * xa[b, t+k-pad_left, c], zeros outside.
+ * white_sd / offset_sd = 0 is the parity path.  Outputs: y fp32 and/or hi/lo.
+ * ------------------------------------------------------------------------------------- */
+int b2t_smooth_fwd(const float* x, const float* taps, float* y, void* y_hi, void* y_lo, int B, int T, int C,
+                   int ntaps, int pad_left, float white_sd, float offset_sd, uint64_t seed, b2t_stream stream);
+/* backward of softsign (b2p2t_model.py:159): dz = ds/(1+|z|)^2 as bf16 hi/lo, and
+ * dbias[day[b]][c] += sum_t dz[b,t,c]  (day_bias gradient, b2p2t_model.py:158) */
+int b2t_softsign_bwd(const float* ds, const float* z, const int32_t* day, void* dz_hi, void* dz_lo, float* dbias,
+                     int B, int T, int C, b2t_stream stream);
+
+/* ---------------------------------------------------------------------------------------
+ * LayerNorm (transformers modeling_wav2vec2.py:690-693,592-609) and small HBM-bound helpers.
+ * fwd: y = LN(x)*gamma+beta [then inverted dropout(drop_p, seed)], saves mean / rstd.
+ * bwd: dy may carry that output dropout; writes dx (fp32), the branch copy dx*mask(br_drop) as
+ *      bf16 hi/lo (operand of the upstream GEMMs) and accumulates dgamma, dbeta, dcol (+=).
+ * ------------------------------------------------------------------------------------- */
+int b2t_layernorm_fwd(const float* x, const float* gamma, const float* beta, float eps, float* y, void* y_hi,
+                      void* y_lo, float* mean, float* rstd, int rows, int n, float drop_p, uint64_t seed,
+                      b2t_stream stream);
+int b2t_layernorm_bwd(const float* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
+                      float* dx, void* dx_hi, void* dx_lo, float* dgamma, float* dbeta, float* dcol, int rows,
+                      int n, float out_drop_p, uint64_t out_seed, float br_drop_p, uint64_t br_seed,
+                      b2t_stream stream);
+/* y = dropout(x) with the library's counter-based mask; outputs fp32 and/or bf16 hi/lo (p=0: split) */
+int b2t_dropout(const float* x, float* y, void* hi, void* lo, int64_t n, float p, uint64_t seed, b2t_stream stream);
+/* out[c] += sum_r x[r*ld + c] */
+int b2t_colsum(const float* x, float* out, int64_t rows, int n, int64_t ld, b2t_stream stream);
+/* out = alpha*a + beta*b (b may be NULL) */
+int b2t_axpby(const float* a, const float* b, float* out, int64_t n, float alpha, float beta, b2t_stream stream);
+
+/* ---------------------------------------------------------------------------------------
+ * Fused self-attention (transformers modeling_wav2vec2.py:466-549 eager path; conformer
+ * modeling_wav2vec2_conformer.py:420-527 after RoPE).  qkv is one [B*T, ld] buffer holding q, k, v
+ * at column offsets q_off/k_off/v_off (+ head*d).  probs [B,H,T,T] is saved for backward (may be
+ * NULL in inference).  kv_lens (optional) masks keys >= kv_lens[b]; the reference passes no mask.
+ * ------------------------------------------------------------------------------------- */
+int b2t_attention_fwd(const float* qkv, int64_t ld, int q_off, int k_off, int v_off, const int32_t* kv_lens,
+                      float* probs, float* ctx, void* ctx_hi, void* ctx_lo, int64_t ld_ctx, int B, int T, int H,
+                      int d, float scale, float drop_p, uint64_t seed, b2t_stream stream);
+int b2t_attention_bwd(const float* qkv, int64_t ld, int q_off, int k_off, int v_off, const float* probs,
+                      const float* dctx, int64_t ld_ctx, float* ds_ws, float* dqkv, void* dqkv_hi, void* dqkv_lo,
+                      int B, int T, int H, int d, float scale, float drop_p, uint64_t seed, b2t_stream stream);
+
+/* ---------------------------------------------------------------------------------------
+ * Persistent GRU recurrence (src/model/brain_feature_extractor.py:39-47,61-65 nn.GRU).
+ * gi = x.W_ih^T + b_ih for all frames and both directions, [B*T, ndir*3H] (gate order r,z,n).
+ * Hidden sizes 32/64/128/256/512 (a cluster of H/32 CTAs keeps W_hh on chip for the sequence).
+ * ------------------------------------------------------------------------------------- */
+int b2t_gru_supported_hidden(int H);
+int b2t_gru_fwd(const float* gi, const float* w_hh, const float* b_hh, const float* h0, float* out, void* out_hi,
+                void* out_lo, float* save_r, float* save_z, float* save_n, float* save_ghn, void* hprev_hi,
+                void* hprev_lo, int B, int T, int H, int ndir, float drop_p, uint64_t seed, b2t_stream stream);
+int b2t_gru_bwd(const float* dout, const float* out, const float* w_hh, const float* h0, const float* save_r,
+                const float* save_z, const float* save_n, const float* save_ghn, float* dgi, void* dgi_hi,
+                void* dgi_lo, void* dgh_hi, void* dgh_lo, float* dghn, float* dh0, int B, int T, int H, int ndir,
+                float drop_p, uint64_t seed, b2t_stream stream);
+
+/* ---------------------------------------------------------------------------------------
+ * CTC (src/model/w2v_custom_feat_extractor.py:59,81-90: log_softmax + nn.CTCLoss(blank=0,
+ * reduction="mean", zero_infinity=True)) and greedy decode (src/train/evaluator.py:108-120).
+ * logits[b][t][v] at b*ld_b + t*ld_t + v, V <= 32.  loss (scalar) += mean_b nll_b/max(S_b,1);
+ * grad [B,T,V] = d loss / d logits.  alpha_ws: b2t_ctc_workspace_floats(B,T,s_max) floats.
+ * ------------------------------------------------------------------------------------- */
+int64_t b2t_ctc_workspace_floats(int B, int T, int s_max);
+int b2t_ctc_fwd_bwd(const float* logits, int64_t ld_t, int64_t ld_b, const int64_t* targets, int s_max,
+                    const int32_t* input_lens, const int64_t* target_lens, float* alpha_ws, float* nll, float* loss,
+                    float* grad, int B, int T, int V, int zero_infinity, b2t_stream stream);
+/* argmax [B,T]; ids [B,T] = collapsed repeats without blanks (0-padded); lens [B] */
+int b2t_greedy_decode(const float* logits, int64_t ld_t, int64_t ld_b, int32_t* argmax, int32_t* ids,
+                      int32_t* lens, int B, int T, int V, b2t_stream stream);
 
 #ifdef __cplusplus
 }

@@ -139,7 +139,8 @@ def test_unfold_view_forward():
              a_batched=True)
     u = s.double().unfold(1, KL, S)              # [B, Tp, C, KL] -> feature c*KL + k
     ref = u.reshape(Bn, Tp, C * KL) @ w.double().t()
-    assert rel(out, ref) < 2e-5
+    # K = 8192: the tensor core's fp32 accumulate truncates, error grows with the number of k-steps
+    assert rel(out, ref) < 6e-5
 
 
 def test_unfold_view_wgrad_and_fold():

@@ -1,0 +1,179 @@
+"""Per-kernel parity of libb2t_sm100.so against torch fp64 / the CPU oracle on the same inputs."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _ops():
+    from wav2vec2forbrain_b200 import ops
+    return ops
+
+
+def rel(a, b):
+    a = a.double().cpu()
+    b = b.double().cpu()
+    return ((a - b).norm() / b.norm().clamp_min(1e-30)).item()
+
+
+def rnd(*shape, seed=0, scale=1.0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    return torch.randn(*shape, generator=g, device="cuda") * scale
+
+
+def test_smooth_matches_oracle():
+    from oracle import b2t_oracle as O
+    ops = _ops()
+    x = rnd(3, 117, 256, seed=1)
+    taps = O.gaussian_taps(1.5).cuda()
+    w = taps.view(1, 1, -1).repeat(256, 1, 1)
+    y, hi, lo = ops.smooth_fwd(x, w, pad_left=9, want_f32=True)
+    ref = O.smooth(x.cpu().double(), taps.double())
+    assert rel(y, ref) < 1e-6
+    assert rel(hi.double() + lo.double(), ref) < 1e-5
+
+
+def test_augmentation_statistics():
+    ops = _ops()
+    x = torch.zeros(4, 400, 256, device="cuda")
+    taps = torch.zeros(256, 1, 20, device="cuda")
+    taps[:, :, 9] = 1.0                       # identity stencil exposes the injected noise
+    y, _, _ = ops.smooth_fwd(x, taps, pad_left=9, want_f32=True, white_sd=0.5, offset_sd=0.0, seed=7)
+    assert abs(y.std().item() - 0.5) < 0.01 and abs(y.mean().item()) < 0.01
+    y2, _, _ = ops.smooth_fwd(x, taps, pad_left=9, want_f32=True, white_sd=0.0, offset_sd=0.25, seed=7)
+    assert (y2[:, 0] - y2[:, 100]).abs().max().item() == 0.0     # constant over time
+    assert abs(y2[:, 0].std().item() - 0.25) < 0.03
+
+
+@pytest.mark.parametrize("n", [48, 768, 1024])
+def test_layernorm_fwd_bwd(n):
+    ops = _ops()
+    rows = 333
+    x, g, b, dy = rnd(rows, n, seed=2), 1 + 0.1 * rnd(n, seed=3), rnd(n, seed=4), rnd(rows, n, seed=5)
+    y, hi, lo, mean, rstd = ops.layernorm_fwd(x, g, b, 1e-5)
+    xd = x.double().requires_grad_(True)
+    gd, bd = g.double().requires_grad_(True), b.double().requires_grad_(True)
+    ref = F.layer_norm(xd, (n,), gd, bd, 1e-5)
+    assert rel(y, ref) < 1e-6
+    assert rel(hi.double() + lo.double(), ref) < 1e-5
+    ref.backward(dy.double())
+    dg, db, dc = torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+    dx, dxh, dxl = ops.layernorm_bwd(dy, x, g, mean, rstd, dg, db, dc)
+    assert rel(dx, xd.grad) < 2e-6
+    assert rel(dg, gd.grad) < 1e-5 and rel(db, bd.grad) < 1e-5
+    assert rel(dc, xd.grad.sum(0)) < 1e-4
+    assert rel(dxh.double() + dxl.double(), xd.grad) < 1e-5
+
+
+def test_dropout_mask_is_reproducible_and_unbiased():
+    ops = _ops()
+    x = torch.ones(1 << 20, device="cuda")
+    y1, _, _ = ops.dropout(x, 0.3, seed=11)
+    y2, _, _ = ops.dropout(x, 0.3, seed=11)
+    y3, _, _ = ops.dropout(x, 0.3, seed=12)
+    assert torch.equal(y1, y2) and not torch.equal(y1, y3)
+    keep = (y1 != 0).float().mean().item()
+    assert abs(keep - 0.7) < 0.003
+    assert abs(y1.mean().item() - 1.0) < 0.01
+
+
+@pytest.mark.parametrize("B,T,H,d", [(2, 23, 4, 12), (3, 118, 12, 64)])
+def test_attention_fwd_bwd(B, T, H, d):
+    ops = _ops()
+    hd = H * d
+    qkv = rnd(B * T, 3 * hd, seed=6)
+    dctx = rnd(B * T, hd, seed=7)
+    ctx, hi, lo, probs = ops.attention_fwd(qkv, B, T, H, d, want_f32=True)
+    x = qkv.double().requires_grad_(True)
+    q, k, v = [t.reshape(B, T, H, d).transpose(1, 2) for t in x.split(hd, dim=1)]
+    p = torch.softmax(q @ k.transpose(-1, -2) * d ** -0.5, -1)
+    ref = (p @ v).transpose(1, 2).reshape(B * T, hd)
+    assert rel(ctx, ref) < 2e-6
+    assert rel(probs, p) < 2e-6
+    ref.backward(dctx.double())
+    ws = torch.empty(B, H, T, T, device="cuda")
+    dqkv, dh, dl = ops.attention_bwd(qkv, probs, dctx, ws, B, T, H, d)
+    assert rel(dqkv, x.grad) < 5e-6
+    assert rel(dh.double() + dl.double(), x.grad) < 2e-5
+
+
+@pytest.mark.parametrize("B,T,H,ndir,h0", [(3, 17, 32, 2, False), (5, 30, 64, 1, True), (20, 118, 512, 2, False)])
+def test_gru_recurrence_fwd_bwd(B, T, H, ndir, h0):
+    ops = _ops()
+    M = B * T
+    gi = rnd(M, ndir * 3 * H, seed=8)
+    w_hh = rnd(ndir, 3 * H, H, seed=9, scale=H ** -0.5)
+    b_hh = rnd(ndir, 3 * H, seed=10, scale=0.1)
+    h0t = rnd(ndir, H, seed=11, scale=0.5) if h0 else None
+    dout = rnd(M, ndir * H, seed=12)
+    fw = ops.gru_fwd(gi, w_hh, b_hh, h0t, B, T, H, ndir)
+    # fp64 reference of the same recurrence (App. A.2)
+    gi_d = gi.double().reshape(B, T, ndir, 3 * H).requires_grad_(True)
+    w_d, b_d = w_hh.double().requires_grad_(True), b_hh.double().requires_grad_(True)
+    h0_d = h0t.double().requires_grad_(True) if h0 else None
+    outs = []
+    for dr in range(ndir):
+        h = h0_d[dr].expand(B, H) if h0 else torch.zeros(B, H, dtype=torch.float64, device="cuda")
+        hs = [None] * T
+        for s in range(T):
+            t = s if dr == 0 else T - 1 - s
+            gh = h @ w_d[dr].t() + b_d[dr]
+            g = gi_d[:, t, dr]
+            r = torch.sigmoid(g[:, :H] + gh[:, :H])
+            z = torch.sigmoid(g[:, H:2 * H] + gh[:, H:2 * H])
+            n = torch.tanh(g[:, 2 * H:] + r * gh[:, 2 * H:])
+            h = (1 - z) * n + z * h
+            hs[t] = h
+        outs.append(torch.stack(hs, 1))
+    ref = torch.cat(outs, -1).reshape(M, ndir * H)
+    assert rel(fw["out"], ref) < 1e-5
+    assert rel(fw["out_hi"].double() + fw["out_lo"].double(), ref) < 2e-5
+    ref.backward(dout.double())
+    dh0 = torch.zeros(ndir, H, device="cuda") if h0 else None
+    bw = ops.gru_bwd(dout, fw, w_hh, h0t, dh0, B, T, H, ndir)
+    assert rel(bw["dgi"], gi_d.grad.reshape(M, ndir * 3 * H)) < 2e-5
+    # dW_hh = dgh^T . hprev (what the engine feeds to the GEMM)
+    dgh = bw["dgh_hi"].double() + bw["dgh_lo"].double()
+    hp = fw["hprev_hi"].double() + fw["hprev_lo"].double()
+    dw = torch.stack([dgh[dr].t() @ hp[dr] for dr in range(ndir)])
+    assert rel(dw, w_d.grad) < 5e-5
+    dbh = torch.cat([dgh[:, :, :2 * H].sum(1), bw["dghn"].double().sum(1)], -1)
+    assert rel(dbh, b_d.grad) < 5e-5
+    if h0:
+        assert rel(dh0, h0_d.grad) < 2e-5
+
+
+@pytest.mark.parametrize("B,T,S,ragged", [(4, 50, 10, False), (8, 118, 40, True), (3, 60, 70, True)])
+def test_ctc_matches_torch(B, T, S, ragged):
+    ops = _ops()
+    g = torch.Generator().manual_seed(13)
+    logits = torch.randn(B, T, 32, generator=g).cuda()
+    targets = torch.randint(1, 32, (B, S), generator=g)
+    tl = torch.randint(1, S + 1, (B,), generator=g) if ragged else torch.full((B,), S)
+    il = torch.randint(T // 2, T + 1, (B,), generator=g).int() if ragged else torch.full((B,), T).int()
+    if ragged:
+        tl[0] = 0 if S < 60 else S            # empty target / infeasible (S > T/2 repeated labels)
+    for b in range(B):
+        targets[b, tl[b]:] = 0
+    loss, nll, grad = ops.ctc_fwd_bwd(logits, targets.cuda(), il.cuda(), tl.cuda())
+    x = logits.double().cpu().requires_grad_(True)
+    lp = F.log_softmax(x, -1).transpose(0, 1)
+    ref = F.ctc_loss(lp, targets, il.long(), tl, blank=0, reduction="mean", zero_infinity=True)
+    ref.backward()
+    assert abs(loss.item() - ref.item()) < 1e-5 * max(1.0, abs(ref.item()))
+    assert rel(grad, x.grad) < 1e-5
+
+
+def test_greedy_decode():
+    from oracle import b2t_oracle as O
+    ops = _ops()
+    logits = rnd(6, 118, 32, seed=14)
+    logits[:, :, 0] += 1.5                    # plenty of blanks and repeats
+    logits[2, 5] = logits[2, 4]
+    am, ids, lens = ops.greedy_decode(logits)
+    assert torch.equal(am.long().cpu(), logits.cpu().argmax(-1))
+    want = O.greedy_decode(logits.cpu())
+    for b in range(6):
+        assert ids[b, :lens[b]].tolist() == want[b]
+        assert ids[b, lens[b]:].abs().sum().item() == 0

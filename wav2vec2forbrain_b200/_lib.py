@@ -39,6 +39,7 @@ class GemmArgs(ctypes.Structure):
         ("bias", c_void_p), ("residual", c_void_p), ("aux", c_void_p), ("colsum", c_void_p),
         ("act", c_int32), ("aux_mode", c_int32), ("atomic", c_int32), ("split_k", c_int32),
         ("alpha", c_float), ("block_n", c_int32),
+        ("drop_p", c_float), ("drop_seed", ctypes.c_uint64), ("bias_batch_stride", c_int64),
     ]
 
 

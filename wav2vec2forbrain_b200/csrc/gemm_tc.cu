@@ -38,13 +38,15 @@ struct KParams {
     float* out_pre;
     bf16* out_hi;
     bf16* out_lo;
-    long long ldc, c_batch_stride;
+    long long ldc, c_batch_stride, bias_batch_stride;
     const float* bias;
     const float* residual;
     const float* aux;
     float* colsum;
     int act, aux_mode, atomic, split_k;
     float alpha;
+    float drop_p, drop_scale;
+    unsigned long long drop_seed;
     int m_tiles, n_tiles, total_items;
 };
 
@@ -342,6 +344,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
             const long long base_off = (long long)cbatch * p.c_batch_stride;
             const int row0 = m_blk * BM + q * 32;
             const bool use_bias = p.bias != nullptr && split == 0;
+            const int bslot = p.b_batch_idx ? p.b_batch_idx[batch] : (p.b_batched ? batch : 0);
+            const float* bias_ptr = p.bias ? p.bias + (long long)bslot * p.bias_batch_stride : nullptr;
 #pragma unroll 1
             for (int c = 0; c < BN / 32; ++c) {
                 float v[32];
@@ -359,7 +363,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
                 for (int j = 0; j < 32; ++j) stg[lane * 33 + j] = v[j];
                 __syncwarp();
                 const bool col_ok = col < p.n;
-                const float bias_v = (use_bias && col_ok) ? p.bias[col] : 0.0f;
+                const float bias_v = (use_bias && col_ok) ? bias_ptr[col] : 0.0f;
                 float csum = 0.0f;
 #pragma unroll 4
                 for (int r = 0; r < 32; ++r) {
@@ -371,6 +375,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
                     if (p.out_pre) p.out_pre[off] = x;
                     x = apply_act(x, p.act);
                     if (p.aux_mode) x *= apply_dact(p.aux[off], p.aux_mode);
+                    if (p.drop_p > 0.0f)
+                        x = hash_uniform(p.drop_seed, (unsigned long long)off) < p.drop_p ? 0.0f : x * p.drop_scale;
                     if (p.residual) x += p.residual[off];
                     csum += x;
                     if (p.out_f32) {
@@ -498,7 +504,7 @@ extern "C" int b2t_gemm(const b2t_gemm_args* a, b2t_stream stream_) {
     B2T_CHECK_ARG(a->m_per_batch > 0 && a->batches > 0 && a->n > 0 && a->k > 0, "b2t_gemm: bad sizes m=%d batches=%d n=%d k=%d",
                   a->m_per_batch, a->batches, a->n, a->k);
     B2T_CHECK_ARG(a->split_k >= 1, "b2t_gemm: split_k must be >= 1");
-    B2T_CHECK_ARG(a->split_k == 1 || (a->atomic && a->act == 0 && !a->out_hi && !a->out_pre && !a->aux_mode && !a->residual &&
+    B2T_CHECK_ARG(a->split_k == 1 || (a->atomic && a->act == 0 && !a->out_hi && !a->out_pre && !a->aux_mode && !a->residual && a->drop_p == 0.0f &&
                                       !a->colsum && a->out_f32),
                   "b2t_gemm: split_k > 1 needs atomic fp32 output and a linear epilogue");
     B2T_CHECK_ARG(!a->k_spans_batches || (a->a_mn_major && a->b_mn_major),
@@ -531,6 +537,7 @@ extern "C" int b2t_gemm(const b2t_gemm_args* a, b2t_stream stream_) {
     kp.out_lo = (bf16*)a->out_lo;
     kp.ldc = a->ldc;
     kp.c_batch_stride = a->c_batch_stride;
+    kp.bias_batch_stride = a->bias_batch_stride;
     kp.bias = a->bias;
     kp.residual = a->residual;
     kp.aux = a->aux;
@@ -540,6 +547,10 @@ extern "C" int b2t_gemm(const b2t_gemm_args* a, b2t_stream stream_) {
     kp.atomic = a->atomic;
     kp.split_k = a->split_k;
     kp.alpha = a->alpha;
+    B2T_CHECK_ARG(a->drop_p >= 0.0f && a->drop_p < 1.0f, "b2t_gemm: drop_p must be in [0, 1)");
+    kp.drop_p = a->drop_p;
+    kp.drop_scale = 1.0f / (1.0f - a->drop_p);
+    kp.drop_seed = a->drop_seed;
 
     int bn = a->block_n;
     if (bn == 0) bn = a->n <= 64 ? 64 : 128;

@@ -1,0 +1,568 @@
+// Persistent recurrent GRU kernels (forward and backward), replacing the cuDNN nn.GRU call of
+// src/model/brain_feature_extractor.py:39-47,61-65.  The input projections x.W_ih^T + b_ih of
+// every layer run beforehand as tcgen05 GEMMs (b2t_gemm; layer 0 through the unfold view); this
+// file holds only the strictly sequential part: T' dependent steps of h.W_hh^T + gates.
+//
+// One thread-block CLUSTER of CS = H/32 CTAs owns one (direction, group of 16 trials) for the
+// whole sequence.  CTA `rank` owns hidden units [32*rank, 32*rank+32) and keeps its slice of
+// W_hh resident for all T' steps: the bf16 "hi" halves live in REGISTERS as mma fragments, the
+// "lo" halves in shared memory (bf16x3 split: hi.hi + hi.lo + lo.hi, fp32 accumulate, so the
+// recurrence keeps ~fp32 accuracy over 118 dependent steps).  Per step:
+//   forward : gh[16, 96] = h[16, H] . W_slice^T on mma.sync (M=16 trials), gate math for the 32
+//             own units, the new h slice is pushed to every CTA of the cluster through
+//             distributed shared memory, one barrier.cluster per step.
+//   backward: gate derivatives for the own units, partial dh[16, H] = dgh[16, 96] . W_slice on
+//             mma.sync, partial sums scattered to the owning CTAs through DSMEM (reduce-scatter),
+//             one barrier.cluster per step.  dW_hh / dW_ih / bias gradients are big GEMMs over
+//             the stored gate gradients afterwards (b2t_gemm), not per-step work.
+// Clusters are independent (no grid-wide barrier), so any number of them may be resident.
+#include "common.cuh"
+#include "../../include/b2t_sm100.h"
+
+namespace {
+
+constexpr int RB = 16;   // trials per cluster == mma M
+constexpr int U = 32;    // hidden units per CTA
+constexpr int NCOL = 3 * U;
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t local_smem_addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_smem_addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void st_cluster_v4(uint32_t addr, uint4 v) {
+    asm volatile("st.shared::cluster.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+                 : "memory");
+}
+__device__ __forceinline__ void st_cluster_v2f(uint32_t addr, float a, float b) {
+    asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(addr), "f"(a), "f"(b) : "memory");
+}
+__device__ __forceinline__ void mma_bf16_16816(float* c, const uint32_t* a, uint32_t b0, uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t pack_bf16(bf16 lo_half, bf16 hi_half) {
+    __nv_bfloat162 p = __halves2bfloat162(lo_half, hi_half);
+    return *reinterpret_cast<uint32_t*>(&p);
+}
+__device__ __forceinline__ void split_pair(float x0, float x1, uint32_t& hi, uint32_t& lo) {
+    bf16 h0, l0, h1, l1;
+    split_bf16(x0, h0, l0);
+    split_bf16(x1, h1, l1);
+    hi = pack_bf16(h0, h1);
+    lo = pack_bf16(l0, l1);
+}
+__device__ __forceinline__ float sigmoid_acc(float x) { return 1.0f / (1.0f + expf(-x)); }
+__device__ __forceinline__ float keep_scale(float p, unsigned long long seed, unsigned long long off) {
+    if (p <= 0.0f) return 1.0f;
+    return hash_uniform(seed, off) < p ? 0.0f : 1.0f / (1.0f - p);
+}
+
+struct GruFwdArgs {
+    const float* gi;      // [M, ndir*3H]  x.W_ih^T + b_ih, gate order r,z,n per direction
+    const float* w_hh;    // [ndir][3H][H]
+    const float* b_hh;    // [ndir][3H]
+    const float* h0;      // [ndir][H] or null (zeros)
+    float* out;           // [M, ndir*H]
+    bf16* out_hi;         // [M, ndir*H]  (inter-layer dropout applied)
+    bf16* out_lo;
+    float* save_r;        // [ndir][M][H]   (null in inference)
+    float* save_z;
+    float* save_n;
+    float* save_ghn;
+    bf16* hprev_hi;       // [ndir][M][H]   h entering each step (operand of the dW_hh GEMM)
+    bf16* hprev_lo;
+    int B, T, ndir;
+    float drop_p;
+    unsigned long long seed;
+};
+
+template <int H>
+struct FwdSmem {
+    static constexpr int KSTEPS = H / 16;
+    static constexpr int HP = H + 8;   // padded bf16 pitch: conflict-free A-fragment loads
+    static constexpr size_t WLO = (size_t)12 * KSTEPS * 32 * 8;
+    static constexpr size_t HBUF = (size_t)2 * 2 * RB * HP * 2;
+    static constexpr size_t GH = (size_t)RB * (NCOL + 1) * 4;
+    static constexpr size_t HOWN = (size_t)RB * U * 4;
+    static constexpr size_t STAGE = (size_t)2 * RB * U * 2;
+    static constexpr size_t TOTAL = WLO + HBUF + GH + HOWN + STAGE;
+};
+
+template <int H>
+__global__ void __launch_bounds__(384, 1) gru_fwd_kernel(const GruFwdArgs p) {
+    using S = FwdSmem<H>;
+    constexpr int KSTEPS = S::KSTEPS, HP = S::HP, CS = H / U;
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint2* wlo = reinterpret_cast<uint2*>(smem);                       // [12][KSTEPS][32]
+    bf16* hbuf = reinterpret_cast<bf16*>(smem + S::WLO);               // [2 buf][2 hi/lo][RB][HP]
+    float* gh_s = reinterpret_cast<float*>(smem + S::WLO + S::HBUF);   // [RB][NCOL+1]
+    float* hown = reinterpret_cast<float*>(smem + S::WLO + S::HBUF + S::GH);             // [RB][U]
+    bf16* stage = reinterpret_cast<bf16*>(smem + S::WLO + S::HBUF + S::GH + S::HOWN);    // [2][RB][U]
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int g = lane >> 2, tq = lane & 3;
+    const uint32_t rank = cluster_ctarank();
+    const int cluster_id = blockIdx.x / CS;
+    const int dir = cluster_id % p.ndir, group = cluster_id / p.ndir;
+    const int row0 = group * RB, u0 = (int)rank * U;
+    const long M = (long)p.B * p.T;
+    const int T = p.T;
+
+    // ---- resident weights: this warp's 8 gate columns, all K ---------------------------------
+    const int gate = warp >> 2, ntile = warp & 3;
+    uint32_t bhi[KSTEPS][2];
+    {
+        const int col = gate * H + u0 + ntile * 8 + g;   // row of W_hh
+        const float* wr = p.w_hh + ((long)dir * 3 * H + col) * H;
+#pragma unroll
+        for (int ks = 0; ks < KSTEPS; ++ks) {
+            uint32_t l0, l1;
+            split_pair(wr[ks * 16 + 2 * tq], wr[ks * 16 + 2 * tq + 1], bhi[ks][0], l0);
+            split_pair(wr[ks * 16 + 2 * tq + 8], wr[ks * 16 + 2 * tq + 9], bhi[ks][1], l1);
+            wlo[(warp * KSTEPS + ks) * 32 + lane] = make_uint2(l0, l1);
+        }
+    }
+    const float bias_c0 = p.b_hh[(long)dir * 3 * H + gate * H + u0 + ntile * 8 + 2 * tq];
+    const float bias_c1 = p.b_hh[(long)dir * 3 * H + gate * H + u0 + ntile * 8 + 2 * tq + 1];
+
+    // ---- initial state ----------------------------------------------------------------------
+    for (int i = tid; i < RB * H; i += blockDim.x) {
+        const int r = i / H, k = i - r * H;
+        const float v = p.h0 ? p.h0[(long)dir * H + k] : 0.0f;
+        bf16 hh, ll;
+        split_bf16(v, hh, ll);
+        hbuf[(0 * 2 + 0) * RB * HP + r * HP + k] = hh;
+        hbuf[(0 * 2 + 1) * RB * HP + r * HP + k] = ll;
+    }
+    for (int i = tid; i < RB * U; i += blockDim.x) hown[i] = p.h0 ? p.h0[(long)dir * H + u0 + (i % U)] : 0.0f;
+    __syncthreads();
+    cluster_sync_all();
+
+    // gate-phase items: threads 0..255 own unit (tid % 32) for rows tid/32 and tid/32 + 8
+    const int gu = tid & 31, gr = tid >> 5;
+    const int gdim = p.ndir * 3 * H;
+
+    for (int s = 0; s < T; ++s) {
+        const int t = dir == 0 ? s : T - 1 - s;
+        const int cur = s & 1;
+        // prefetch the input projections of this step for the gate phase
+        float gi_v[2][3];
+        if (tid < 256) {
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const int b = row0 + gr + 8 * j;
+#pragma unroll
+                for (int q = 0; q < 3; ++q)
+                    gi_v[j][q] = b < p.B ? p.gi[((long)b * T + t) * gdim + dir * 3 * H + q * H + u0 + gu] : 0.0f;
+            }
+        }
+        // ---- gh = h . W_slice^T (bf16x3) ----
+        {
+            const bf16* hh = hbuf + (cur * 2 + 0) * RB * HP;
+            const bf16* hl = hbuf + (cur * 2 + 1) * RB * HP;
+            float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f}, acc2[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int ks = 0; ks < KSTEPS; ++ks) {
+                uint32_t ah[4], al[4];
+                const int k0 = ks * 16 + 2 * tq;
+                ah[0] = *reinterpret_cast<const uint32_t*>(hh + g * HP + k0);
+                ah[1] = *reinterpret_cast<const uint32_t*>(hh + (g + 8) * HP + k0);
+                ah[2] = *reinterpret_cast<const uint32_t*>(hh + g * HP + k0 + 8);
+                ah[3] = *reinterpret_cast<const uint32_t*>(hh + (g + 8) * HP + k0 + 8);
+                al[0] = *reinterpret_cast<const uint32_t*>(hl + g * HP + k0);
+                al[1] = *reinterpret_cast<const uint32_t*>(hl + (g + 8) * HP + k0);
+                al[2] = *reinterpret_cast<const uint32_t*>(hl + g * HP + k0 + 8);
+                al[3] = *reinterpret_cast<const uint32_t*>(hl + (g + 8) * HP + k0 + 8);
+                const uint2 bl = wlo[(warp * KSTEPS + ks) * 32 + lane];
+                mma_bf16_16816(acc0, ah, bhi[ks][0], bhi[ks][1]);
+                mma_bf16_16816(acc1, ah, bl.x, bl.y);
+                mma_bf16_16816(acc2, al, bhi[ks][0], bhi[ks][1]);
+            }
+            const int cidx = warp * 8 + 2 * tq;   // == gate*32 + ntile*8 + n
+            gh_s[g * (NCOL + 1) + cidx] = acc0[0] + acc1[0] + acc2[0] + bias_c0;
+            gh_s[g * (NCOL + 1) + cidx + 1] = acc0[1] + acc1[1] + acc2[1] + bias_c1;
+            gh_s[(g + 8) * (NCOL + 1) + cidx] = acc0[2] + acc1[2] + acc2[2] + bias_c0;
+            gh_s[(g + 8) * (NCOL + 1) + cidx + 1] = acc0[3] + acc1[3] + acc2[3] + bias_c1;
+        }
+        __syncthreads();
+        // ---- gates for the own 32 units (brain_feature_extractor.py nn.GRU equations, App. A.2) ----
+        if (tid < 256) {
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const int row = gr + 8 * j;
+                const int b = row0 + row;
+                const float gh_r = gh_s[row * (NCOL + 1) + gu];
+                const float gh_z = gh_s[row * (NCOL + 1) + U + gu];
+                const float gh_n = gh_s[row * (NCOL + 1) + 2 * U + gu];
+                const float r = sigmoid_acc(gi_v[j][0] + gh_r);
+                const float z = sigmoid_acc(gi_v[j][1] + gh_z);
+                const float n = tanhf(gi_v[j][2] + r * gh_n);
+                const float hp = hown[row * U + gu];
+                const float hn = (1.0f - z) * n + z * hp;
+                hown[row * U + gu] = hn;
+                bf16 hh, ll;
+                split_bf16(hn, hh, ll);
+                stage[row * U + gu] = hh;
+                stage[RB * U + row * U + gu] = ll;
+                if (b < p.B) {
+                    const long m = (long)b * T + t;
+                    const long oo = m * (p.ndir * H) + dir * H + u0 + gu;
+                    p.out[oo] = hn;
+                    if (p.out_hi) {
+                        const float hd = hn * keep_scale(p.drop_p, p.seed, (unsigned long long)oo);
+                        bf16 dh_, dl_;
+                        split_bf16(hd, dh_, dl_);
+                        p.out_hi[oo] = dh_;
+                        if (p.out_lo) p.out_lo[oo] = dl_;
+                    }
+                    if (p.save_r) {
+                        const long so = ((long)dir * M + m) * H + u0 + gu;
+                        p.save_r[so] = r;
+                        p.save_z[so] = z;
+                        p.save_n[so] = n;
+                        p.save_ghn[so] = gh_n;
+                        bf16 ph, pl;
+                        split_bf16(hp, ph, pl);
+                        p.hprev_hi[so] = ph;
+                        if (p.hprev_lo) p.hprev_lo[so] = pl;
+                    }
+                }
+            }
+        }
+        __syncthreads();
+        // ---- push the new h slice (bf16 hi, lo) to every CTA of the cluster ----
+        {
+            const int nxt = cur ^ 1;
+            for (int idx = tid; idx < 128 * CS; idx += blockDim.x) {
+                const int dest = idx >> 7, c = idx & 127;
+                const int which = c >> 6, row = (c & 63) >> 2, ch = c & 3;
+                const uint4 v = *reinterpret_cast<const uint4*>(stage + which * RB * U + row * U + ch * 8);
+                bf16* dst = hbuf + (nxt * 2 + which) * RB * HP + row * HP + u0 + ch * 8;
+                st_cluster_v4(map_to_cta((uint32_t)__cvta_generic_to_shared(dst), (uint32_t)dest), v);
+            }
+        }
+        cluster_sync_all();
+    }
+}
+
+struct GruBwdArgs {
+    const float* dout;     // [M, ndir*H]  gradient w.r.t. the layer output (pre-dropout form is derived here)
+    const float* out;      // [M, ndir*H]  forward output (h_t), gives h_{t-1}
+    const float* w_hh;     // [ndir][3H][H]
+    const float* h0;       // [ndir][H] or null
+    const float* save_r;   // [ndir][M][H]
+    const float* save_z;
+    const float* save_n;
+    const float* save_ghn;
+    float* dgi;            // [M, ndir*3H]  gradient w.r.t. the input projections
+    bf16* dgi_hi;          // [M, ndir*3H]
+    bf16* dgi_lo;
+    bf16* dgh_hi;          // [ndir][M][3H]  gradient w.r.t. h.W_hh^T + b_hh (operand of the dW_hh GEMM)
+    bf16* dgh_lo;
+    float* dghn;           // [ndir][M][H]   its n-gate part in fp32 (b_hh gradient)
+    float* dh0;            // [ndir][H] += sum over trials (learnable initial state) or null
+    int B, T, ndir;
+    float drop_p;
+    unsigned long long seed;
+};
+
+template <int H>
+struct BwdSmem {
+    static constexpr int CS = H / U;
+    static constexpr int NWARP_MMA = CS;                 // warp w produces the partials of CTA w's units
+    static constexpr int THREADS = CS * 32 < 256 ? 256 : CS * 32;
+    static constexpr int AP = NCOL + 8;                  // padded bf16 pitch of the dgh operand
+    static constexpr size_t WLO = (size_t)NWARP_MMA * 24 * 32 * 8;
+    static constexpr size_t RECV = (size_t)2 * CS * RB * U * 4;
+    static constexpr size_t AOP = (size_t)2 * RB * AP * 2;
+    static constexpr size_t DHZ = (size_t)RB * U * 4;
+    static constexpr size_t TOTAL = WLO + RECV + AOP + DHZ;
+};
+
+template <int H>
+__global__ void __launch_bounds__(BwdSmem<H>::THREADS, 1) gru_bwd_kernel(const GruBwdArgs p) {
+    using S = BwdSmem<H>;
+    constexpr int CS = S::CS, AP = S::AP;
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint2* wlo = reinterpret_cast<uint2*>(smem);                                   // [CS warps][4 nt][6 ks][32]
+    float* recv = reinterpret_cast<float*>(smem + S::WLO);                          // [2][CS src][RB][U]
+    bf16* aop = reinterpret_cast<bf16*>(smem + S::WLO + S::RECV);                   // [2 hi/lo][RB][AP]
+    float* dhz = reinterpret_cast<float*>(smem + S::WLO + S::RECV + S::AOP);        // [RB][U]
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int g = lane >> 2, tq = lane & 3;
+    const uint32_t rank = cluster_ctarank();
+    const int cluster_id = blockIdx.x / CS;
+    const int dir = cluster_id % p.ndir, group = cluster_id / p.ndir;
+    const int row0 = group * RB, u0 = (int)rank * U;
+    const long M = (long)p.B * p.T;
+    const int T = p.T;
+
+    // ---- resident weights: B[k = own gate column kk, n = unit of destination CTA `warp`] = W_hh[col(kk)][unit]
+    uint32_t bhi[4][6][2];
+    if (warp < CS) {
+        const float* wd = p.w_hh + (long)dir * 3 * H * H;
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) {
+            const int unit = warp * U + nt * 8 + g;
+#pragma unroll
+            for (int ks = 0; ks < 6; ++ks) {
+                float w[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const int kk = ks * 16 + 2 * tq + (e & 1) + (e >> 1) * 8;
+                    const int col = (kk / U) * H + u0 + (kk % U);
+                    w[e] = wd[(long)col * H + unit];
+                }
+                uint32_t l0, l1;
+                split_pair(w[0], w[1], bhi[nt][ks][0], l0);
+                split_pair(w[2], w[3], bhi[nt][ks][1], l1);
+                wlo[((warp * 4 + nt) * 6 + ks) * 32 + lane] = make_uint2(l0, l1);
+            }
+        }
+    }
+    for (int i = tid; i < RB * U; i += blockDim.x) dhz[i] = 0.0f;
+    for (int i = tid; i < 2 * CS * RB * U; i += blockDim.x) recv[i] = 0.0f;
+    __syncthreads();
+    cluster_sync_all();
+
+    const int odim = p.ndir * H, gdim = p.ndir * 3 * H;
+    for (int s = 0; s < T; ++s) {
+        const int t = dir == 0 ? T - 1 - s : s;           // reverse of the forward order
+        const int tprev = dir == 0 ? t - 1 : t + 1;       // time index of the h that entered step t
+        const int cur = s & 1;
+        // ---- gate derivatives for the own units ----
+        for (int item = tid; item < RB * U; item += blockDim.x) {
+            const int row = item / U, uu = item % U;
+            const int b = row0 + row;
+            float dar = 0.f, daz = 0.f, dan = 0.f, dghn_v = 0.f, carry = 0.f;
+            if (b < p.B) {
+                float rec = dhz[item];
+#pragma unroll 4
+                for (int src = 0; src < CS; ++src) rec += recv[((cur * CS + src) * RB + row) * U + uu];
+                const long m = (long)b * T + t;
+                const long oo = m * odim + dir * H + u0 + uu;
+                const float dh = rec + p.dout[oo] * keep_scale(p.drop_p, p.seed, (unsigned long long)oo);
+                const long so = ((long)dir * M + m) * H + u0 + uu;
+                const float r = p.save_r[so], z = p.save_z[so], n = p.save_n[so], ghn = p.save_ghn[so];
+                float hp;
+                if (tprev >= 0 && tprev < T) hp = p.out[((long)b * T + tprev) * odim + dir * H + u0 + uu];
+                else hp = p.h0 ? p.h0[(long)dir * H + u0 + uu] : 0.0f;
+                const float dn = dh * (1.0f - z);
+                const float dz = dh * (hp - n);
+                carry = dh * z;
+                dan = dn * (1.0f - n * n);
+                dar = dan * ghn * r * (1.0f - r);
+                daz = dz * z * (1.0f - z);
+                dghn_v = dan * r;
+                const long go = m * gdim + dir * 3 * H + u0 + uu;
+                p.dgi[go] = dar;
+                p.dgi[go + H] = daz;
+                p.dgi[go + 2 * H] = dan;
+                bf16 hh, ll;
+                const long ho = ((long)dir * M + m) * 3 * H + u0 + uu;
+                split_bf16(dar, hh, ll);
+                p.dgi_hi[go] = hh;
+                p.dgh_hi[ho] = hh;
+                if (p.dgi_lo) { p.dgi_lo[go] = ll; p.dgh_lo[ho] = ll; }
+                split_bf16(daz, hh, ll);
+                p.dgi_hi[go + H] = hh;
+                p.dgh_hi[ho + H] = hh;
+                if (p.dgi_lo) { p.dgi_lo[go + H] = ll; p.dgh_lo[ho + H] = ll; }
+                split_bf16(dan, hh, ll);
+                p.dgi_hi[go + 2 * H] = hh;
+                if (p.dgi_lo) p.dgi_lo[go + 2 * H] = ll;
+                split_bf16(dghn_v, hh, ll);
+                p.dgh_hi[ho + 2 * H] = hh;
+                if (p.dgh_lo) p.dgh_lo[ho + 2 * H] = ll;
+                p.dghn[so] = dghn_v;
+            }
+            dhz[item] = carry;
+            bf16 hh, ll;
+            split_bf16(dar, hh, ll);
+            aop[row * AP + uu] = hh;
+            aop[RB * AP + row * AP + uu] = ll;
+            split_bf16(daz, hh, ll);
+            aop[row * AP + U + uu] = hh;
+            aop[RB * AP + row * AP + U + uu] = ll;
+            split_bf16(dghn_v, hh, ll);
+            aop[row * AP + 2 * U + uu] = hh;
+            aop[RB * AP + row * AP + 2 * U + uu] = ll;
+        }
+        __syncthreads();
+        // ---- partial dh[16, units of CTA `warp`] = dgh[16, 96 own columns] . W_slice, scattered to its owner ----
+        if (warp < CS) {
+            const bf16* ah_ = aop;
+            const bf16* al_ = aop + RB * AP;
+            float acc[4][4];
+#pragma unroll
+            for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+                for (int e = 0; e < 4; ++e) acc[nt][e] = 0.0f;
+#pragma unroll
+            for (int ks = 0; ks < 6; ++ks) {
+                uint32_t ah[4], al[4];
+                const int k0 = ks * 16 + 2 * tq;
+                ah[0] = *reinterpret_cast<const uint32_t*>(ah_ + g * AP + k0);
+                ah[1] = *reinterpret_cast<const uint32_t*>(ah_ + (g + 8) * AP + k0);
+                ah[2] = *reinterpret_cast<const uint32_t*>(ah_ + g * AP + k0 + 8);
+                ah[3] = *reinterpret_cast<const uint32_t*>(ah_ + (g + 8) * AP + k0 + 8);
+                al[0] = *reinterpret_cast<const uint32_t*>(al_ + g * AP + k0);
+                al[1] = *reinterpret_cast<const uint32_t*>(al_ + (g + 8) * AP + k0);
+                al[2] = *reinterpret_cast<const uint32_t*>(al_ + g * AP + k0 + 8);
+                al[3] = *reinterpret_cast<const uint32_t*>(al_ + (g + 8) * AP + k0 + 8);
+#pragma unroll
+                for (int nt = 0; nt < 4; ++nt) {
+                    const uint2 bl = wlo[((warp * 4 + nt) * 6 + ks) * 32 + lane];
+                    mma_bf16_16816(acc[nt], ah, bhi[nt][ks][0], bhi[nt][ks][1]);
+                    mma_bf16_16816(acc[nt], ah, bl.x, bl.y);
+                    mma_bf16_16816(acc[nt], al, bhi[nt][ks][0], bhi[nt][ks][1]);
+                }
+            }
+            const int nxt = cur ^ 1;
+            float* slot = recv + ((nxt * CS + (int)rank) * RB) * U;   // [RB][U] slot of source `rank` in the owner
+#pragma unroll
+            for (int nt = 0; nt < 4; ++nt) {
+                const uint32_t a0 = map_to_cta((uint32_t)__cvta_generic_to_shared(slot + g * U + nt * 8 + 2 * tq), (uint32_t)warp);
+                const uint32_t a1 =
+                    map_to_cta((uint32_t)__cvta_generic_to_shared(slot + (g + 8) * U + nt * 8 + 2 * tq), (uint32_t)warp);
+                st_cluster_v2f(a0, acc[nt][0], acc[nt][1]);
+                st_cluster_v2f(a1, acc[nt][2], acc[nt][3]);
+            }
+        }
+        cluster_sync_all();
+    }
+    // gradient w.r.t. the initial state (only consumed when hidden_start is learnable)
+    if (p.dh0) {
+        const int cur = T & 1;
+        for (int item = tid; item < RB * U; item += blockDim.x) {
+            const int row = item / U, uu = item % U;
+            if (row0 + row < p.B) {
+                float rec = dhz[item];
+                for (int src = 0; src < CS; ++src) rec += recv[((cur * CS + src) * RB + row) * U + uu];
+                atomicAdd(p.dh0 + (long)dir * H + u0 + uu, rec);
+            }
+        }
+    }
+}
+
+template <int H>
+int launch_fwd(const GruFwdArgs& a, cudaStream_t stream) {
+    constexpr int CS = H / U;
+    const int groups = (a.B + RB - 1) / RB;
+    auto kern = gru_fwd_kernel<H>;
+    static bool attr = false;
+    if (!attr) {
+        B2T_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FwdSmem<H>::TOTAL));
+        if (CS > 8) B2T_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        attr = true;
+    }
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(CS * groups * a.ndir);
+    cfg.blockDim = dim3(384);
+    cfg.dynamicSmemBytes = FwdSmem<H>::TOTAL;
+    cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = CS;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    B2T_CUDA(cudaLaunchKernelEx(&cfg, kern, a));
+    return 0;
+}
+
+template <int H>
+int launch_bwd(const GruBwdArgs& a, cudaStream_t stream) {
+    constexpr int CS = H / U;
+    const int groups = (a.B + RB - 1) / RB;
+    auto kern = gru_bwd_kernel<H>;
+    static bool attr = false;
+    if (!attr) {
+        B2T_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BwdSmem<H>::TOTAL));
+        if (CS > 8) B2T_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        attr = true;
+    }
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(CS * groups * a.ndir);
+    cfg.blockDim = dim3(BwdSmem<H>::THREADS);
+    cfg.dynamicSmemBytes = BwdSmem<H>::TOTAL;
+    cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = CS;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    B2T_CUDA(cudaLaunchKernelEx(&cfg, kern, a));
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int b2t_gru_supported_hidden(int H) { return (H == 32 || H == 64 || H == 128 || H == 256 || H == 512) ? 1 : 0; }
+
+extern "C" int b2t_gru_fwd(const float* gi, const float* w_hh, const float* b_hh, const float* h0, float* out, void* out_hi,
+                           void* out_lo, float* save_r, float* save_z, float* save_n, float* save_ghn, void* hprev_hi,
+                           void* hprev_lo, int B, int T, int H, int ndir, float drop_p, uint64_t seed, b2t_stream stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    B2T_CHECK_ARG(gi && w_hh && b_hh && out, "b2t_gru_fwd: null pointer");
+    B2T_CHECK_ARG(B > 0 && T > 0 && (ndir == 1 || ndir == 2), "b2t_gru_fwd: bad sizes");
+    B2T_CHECK_ARG(b2t_gru_supported_hidden(H), "b2t_gru_fwd: hidden size %d unsupported (32/64/128/256/512)", H);
+    B2T_CHECK_ARG(!save_r || (save_z && save_n && save_ghn && hprev_hi), "b2t_gru_fwd: incomplete save set");
+    B2T_CHECK_ARG(drop_p >= 0.0f && drop_p < 1.0f, "b2t_gru_fwd: drop_p");
+    GruFwdArgs a;
+    a.gi = gi; a.w_hh = w_hh; a.b_hh = b_hh; a.h0 = h0; a.out = out;
+    a.out_hi = (bf16*)out_hi; a.out_lo = (bf16*)out_lo;
+    a.save_r = save_r; a.save_z = save_z; a.save_n = save_n; a.save_ghn = save_ghn;
+    a.hprev_hi = (bf16*)hprev_hi; a.hprev_lo = (bf16*)hprev_lo;
+    a.B = B; a.T = T; a.ndir = ndir; a.drop_p = drop_p; a.seed = seed;
+    switch (H) {
+        case 32: return launch_fwd<32>(a, stream);
+        case 64: return launch_fwd<64>(a, stream);
+        case 128: return launch_fwd<128>(a, stream);
+        case 256: return launch_fwd<256>(a, stream);
+        default: return launch_fwd<512>(a, stream);
+    }
+}
+
+extern "C" int b2t_gru_bwd(const float* dout, const float* out, const float* w_hh, const float* h0, const float* save_r,
+                           const float* save_z, const float* save_n, const float* save_ghn, float* dgi, void* dgi_hi,
+                           void* dgi_lo, void* dgh_hi, void* dgh_lo, float* dghn, float* dh0, int B, int T, int H, int ndir,
+                           float drop_p, uint64_t seed, b2t_stream stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    B2T_CHECK_ARG(dout && out && w_hh && save_r && save_z && save_n && save_ghn && dgi && dgi_hi && dgh_hi && dghn,
+                  "b2t_gru_bwd: null pointer");
+    B2T_CHECK_ARG((dgi_lo == nullptr) == (dgh_lo == nullptr), "b2t_gru_bwd: lo outputs must both be set or both NULL");
+    B2T_CHECK_ARG(B > 0 && T > 0 && (ndir == 1 || ndir == 2), "b2t_gru_bwd: bad sizes");
+    B2T_CHECK_ARG(b2t_gru_supported_hidden(H), "b2t_gru_bwd: hidden size %d unsupported (32/64/128/256/512)", H);
+    GruBwdArgs a;
+    a.dout = dout; a.out = out; a.w_hh = w_hh; a.h0 = h0;
+    a.save_r = save_r; a.save_z = save_z; a.save_n = save_n; a.save_ghn = save_ghn;
+    a.dgi = dgi; a.dgi_hi = (bf16*)dgi_hi; a.dgi_lo = (bf16*)dgi_lo;
+    a.dgh_hi = (bf16*)dgh_hi; a.dgh_lo = (bf16*)dgh_lo; a.dghn = dghn; a.dh0 = dh0;
+    a.B = B; a.T = T; a.ndir = ndir; a.drop_p = drop_p; a.seed = seed;
+    switch (H) {
+        case 32: return launch_bwd<32>(a, stream);
+        case 64: return launch_bwd<64>(a, stream);
+        case 128: return launch_bwd<128>(a, stream);
+        case 256: return launch_bwd<256>(a, stream);
+        default: return launch_bwd<512>(a, stream);
+    }
+}

@@ -1,0 +1,270 @@
+// LayerNorm forward/backward (one warp per row, row held in registers: one HBM read, one write),
+// plus the small HBM-bound helpers that sit between GEMMs: dropout(+split), column sums.
+// Replaces nn.LayerNorm / nn.Dropout calls of transformers modeling_wav2vec2.py:690-693,592-609
+// and modeling_wav2vec2_conformer.py:577-631.
+#include "common.cuh"
+#include "../../include/b2t_sm100.h"
+
+namespace {
+
+template <int MAXP>
+__global__ void __launch_bounds__(256) ln_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                                                     const float* __restrict__ beta, float eps, float* __restrict__ y,
+                                                     bf16* __restrict__ y_hi, bf16* __restrict__ y_lo,
+                                                     float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows,
+                                                     int n, float drop_p, unsigned long long seed) {
+    const int lane = threadIdx.x & 31;
+    const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int nwarps = (gridDim.x * blockDim.x) >> 5;
+    const float inv_n = 1.0f / (float)n;
+    const float drop_scale = 1.0f / (1.0f - drop_p);
+    for (int row = warp_global; row < rows; row += nwarps) {
+        const float* xr = x + (long)row * n;
+        float v[MAXP];
+        float s = 0.0f;
+#pragma unroll
+        for (int i = 0; i < MAXP; ++i) {
+            const int c = lane + 32 * i;
+            v[i] = c < n ? xr[c] : 0.0f;
+            s += v[i];
+        }
+        const float mean = warp_sum(s) * inv_n;
+        float q = 0.0f;
+#pragma unroll
+        for (int i = 0; i < MAXP; ++i) {
+            const int c = lane + 32 * i;
+            const float d = c < n ? v[i] - mean : 0.0f;
+            q += d * d;
+        }
+        const float rstd = rsqrtf(warp_sum(q) * inv_n + eps);
+        if (lane == 0) {
+            if (mean_out) mean_out[row] = mean;
+            if (rstd_out) rstd_out[row] = rstd;
+        }
+#pragma unroll
+        for (int i = 0; i < MAXP; ++i) {
+            const int c = lane + 32 * i;
+            if (c < n) {
+                const long off = (long)row * n + c;
+                float o = (v[i] - mean) * rstd * gamma[c] + beta[c];
+                if (drop_p > 0.0f) o = hash_uniform(seed, (unsigned long long)off) < drop_p ? 0.0f : o * drop_scale;
+                if (y) y[off] = o;
+                if (y_hi) {
+                    bf16 h, l;
+                    split_bf16(o, h, l);
+                    y_hi[off] = h;
+                    if (y_lo) y_lo[off] = l;
+                }
+            }
+        }
+    }
+}
+
+// dy may carry the forward's output dropout (drop_p/seed over the same [rows,n] offsets).
+// dx = LN'(x)^T dy_eff ; dgamma += sum dy_eff*xhat ; dbeta += sum dy_eff
+// optional: dx_hi/lo = (dx [* branch dropout mask]) as the A operand of the upstream GEMMs,
+//           dcol += column sums of that masked dx (bias gradient of the upstream Linear)
+template <int MAXP>
+__global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ x,
+                                                     const float* __restrict__ gamma, const float* __restrict__ mean_in,
+                                                     const float* __restrict__ rstd_in, float* __restrict__ dx,
+                                                     bf16* __restrict__ dx_hi, bf16* __restrict__ dx_lo,
+                                                     float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                     float* __restrict__ dcol, int rows, int n, float out_drop_p,
+                                                     unsigned long long out_seed, float br_drop_p,
+                                                     unsigned long long br_seed) {
+    extern __shared__ float sacc[];   // [3][n]
+    for (int i = threadIdx.x; i < 3 * n; i += blockDim.x) sacc[i] = 0.0f;
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int nwarps = (gridDim.x * blockDim.x) >> 5;
+    const float inv_n = 1.0f / (float)n;
+    const float out_scale = 1.0f / (1.0f - out_drop_p), br_scale = 1.0f / (1.0f - br_drop_p);
+    float ag[MAXP], ab[MAXP], ac[MAXP];
+#pragma unroll
+    for (int i = 0; i < MAXP; ++i) ag[i] = ab[i] = ac[i] = 0.0f;
+    for (int row = warp_global; row < rows; row += nwarps) {
+        const float mean = mean_in[row], rstd = rstd_in[row];
+        float xh[MAXP], g[MAXP];
+        float s1 = 0.0f, s2 = 0.0f;
+#pragma unroll
+        for (int i = 0; i < MAXP; ++i) {
+            const int c = lane + 32 * i;
+            xh[i] = 0.0f;
+            g[i] = 0.0f;
+            if (c < n) {
+                const long off = (long)row * n + c;
+                float d = dy[off];
+                if (out_drop_p > 0.0f)
+                    d = hash_uniform(out_seed, (unsigned long long)off) < out_drop_p ? 0.0f : d * out_scale;
+                xh[i] = (x[off] - mean) * rstd;
+                ag[i] += d * xh[i];
+                ab[i] += d;
+                g[i] = d * gamma[c];
+                s1 += g[i];
+                s2 += g[i] * xh[i];
+            }
+        }
+        s1 = warp_sum(s1) * inv_n;
+        s2 = warp_sum(s2) * inv_n;
+#pragma unroll
+        for (int i = 0; i < MAXP; ++i) {
+            const int c = lane + 32 * i;
+            if (c < n) {
+                const long off = (long)row * n + c;
+                const float o = rstd * (g[i] - s1 - xh[i] * s2);
+                if (dx) dx[off] = o;
+                if (dx_hi || dcol) {
+                    float ob = o;
+                    if (br_drop_p > 0.0f)
+                        ob = hash_uniform(br_seed, (unsigned long long)off) < br_drop_p ? 0.0f : o * br_scale;
+                    ac[i] += ob;
+                    if (dx_hi) {
+                        bf16 h, l;
+                        split_bf16(ob, h, l);
+                        dx_hi[off] = h;
+                        if (dx_lo) dx_lo[off] = l;
+                    }
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < MAXP; ++i) {
+        const int c = lane + 32 * i;
+        if (c < n) {
+            atomicAdd(&sacc[c], ag[i]);
+            atomicAdd(&sacc[n + c], ab[i]);
+            atomicAdd(&sacc[2 * n + c], ac[i]);
+        }
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < n; c += blockDim.x) {
+        if (dgamma) atomicAdd(dgamma + c, sacc[c]);
+        if (dbeta) atomicAdd(dbeta + c, sacc[n + c]);
+        if (dcol) atomicAdd(dcol + c, sacc[2 * n + c]);
+    }
+}
+
+// y = dropout(x) (same hash mask contract as the GEMM epilogue) with optional fp32 / hi / lo outputs;
+// p == 0 degenerates to a plain split.  Also the backward (apply to the incoming gradient).
+__global__ void dropout_kernel(const float* __restrict__ x, float* __restrict__ y, bf16* __restrict__ hi,
+                               bf16* __restrict__ lo, long n, float p, unsigned long long seed) {
+    const float scale = 1.0f / (1.0f - p);
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+        float v = x[i];
+        if (p > 0.0f) v = hash_uniform(seed, (unsigned long long)i) < p ? 0.0f : v * scale;
+        if (y) y[i] = v;
+        if (hi) {
+            bf16 h, l;
+            split_bf16(v, h, l);
+            hi[i] = h;
+            if (lo) lo[i] = l;
+        }
+    }
+}
+
+// out[c] += sum_r x[r, c]; x row stride ld.  grid (col tiles of 32, row slabs); 32x8 threads
+__global__ void colsum_kernel(const float* __restrict__ x, float* __restrict__ out, long rows, int n, long ld,
+                              long rows_per_block) {
+    __shared__ float part[8][33];
+    const int c = blockIdx.x * 32 + threadIdx.x;
+    const long r0 = (long)blockIdx.y * rows_per_block;
+    const long r1 = r0 + rows_per_block < rows ? r0 + rows_per_block : rows;
+    float acc = 0.0f;
+    if (c < n)
+        for (long r = r0 + threadIdx.y; r < r1; r += 8) acc += x[r * ld + c];
+    part[threadIdx.y][threadIdx.x] = acc;
+    __syncthreads();
+    if (threadIdx.y == 0 && c < n) {
+        float s = 0.0f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s += part[j][threadIdx.x];
+        atomicAdd(out + c, s);
+    }
+}
+
+__global__ void axpby_kernel(const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ out, long n,
+                             float alpha, float beta_) {
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
+        out[i] = alpha * a[i] + (b ? beta_ * b[i] : 0.0f);
+}
+
+inline int grid_for(long n, int block, int cap_mult = 16) {
+    long g = (n + block - 1) / block;
+    const long cap = 148L * cap_mult;
+    return (int)(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+}  // namespace
+
+#define LN_DISPATCH(n, CALL)                       \
+    do {                                           \
+        const int per = ((n) + 31) / 32;           \
+        if (per <= 2) { CALL(2); }                 \
+        else if (per <= 8) { CALL(8); }            \
+        else if (per <= 24) { CALL(24); }          \
+        else { CALL(32); }                         \
+    } while (0)
+
+extern "C" int b2t_layernorm_fwd(const float* x, const float* gamma, const float* beta, float eps, float* y, void* y_hi,
+                                 void* y_lo, float* mean, float* rstd, int rows, int n, float drop_p, uint64_t seed,
+                                 b2t_stream stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    B2T_CHECK_ARG(x && gamma && beta && (y || y_hi) && rows > 0 && n > 0 && n <= 1024, "b2t_layernorm_fwd: bad arguments (n=%d)", n);
+    B2T_CHECK_ARG(drop_p >= 0.0f && drop_p < 1.0f, "b2t_layernorm_fwd: drop_p");
+    const int grid = grid_for((long)rows * 32, 256, 8);
+#define CALL(P)                                                                                                          \
+    ln_fwd_kernel<P><<<grid, 256, 0, stream>>>(x, gamma, beta, eps, y, (bf16*)y_hi, (bf16*)y_lo, mean, rstd, rows, n, drop_p, \
+                                               (unsigned long long)seed)
+    LN_DISPATCH(n, CALL);
+#undef CALL
+    B2T_CHECK_LAUNCH("b2t_layernorm_fwd");
+    return 0;
+}
+
+extern "C" int b2t_layernorm_bwd(const float* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
+                                 float* dx, void* dx_hi, void* dx_lo, float* dgamma, float* dbeta, float* dcol, int rows,
+                                 int n, float out_drop_p, uint64_t out_seed, float br_drop_p, uint64_t br_seed,
+                                 b2t_stream stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    B2T_CHECK_ARG(dy && x && gamma && mean && rstd && rows > 0 && n > 0 && n <= 1024, "b2t_layernorm_bwd: bad arguments");
+    const int grid = grid_for((long)rows * 32, 256, 2);
+    const size_t smem = 3 * (size_t)n * sizeof(float);
+#define CALL(P)                                                                                                       \
+    ln_bwd_kernel<P><<<grid, 256, smem, stream>>>(dy, x, gamma, mean, rstd, dx, (bf16*)dx_hi, (bf16*)dx_lo, dgamma, dbeta, \
+                                                  dcol, rows, n, out_drop_p, (unsigned long long)out_seed, br_drop_p,  \
+                                                  (unsigned long long)br_seed)
+    LN_DISPATCH(n, CALL);
+#undef CALL
+    B2T_CHECK_LAUNCH("b2t_layernorm_bwd");
+    return 0;
+}
+
+extern "C" int b2t_dropout(const float* x, float* y, void* hi, void* lo, int64_t n, float p, uint64_t seed,
+                           b2t_stream stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    B2T_CHECK_ARG(x && (y || hi) && n > 0 && p >= 0.0f && p < 1.0f, "b2t_dropout: bad arguments");
+    dropout_kernel<<<grid_for(n, 256), 256, 0, stream>>>(x, y, (bf16*)hi, (bf16*)lo, n, p, (unsigned long long)seed);
+    B2T_CHECK_LAUNCH("b2t_dropout");
+    return 0;
+}
+
+extern "C" int b2t_colsum(const float* x, float* out, int64_t rows, int n, int64_t ld, b2t_stream stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    B2T_CHECK_ARG(x && out && rows > 0 && n > 0 && ld >= n, "b2t_colsum: bad arguments");
+    const long rpb = 256;
+    dim3 grid((n + 31) / 32, (unsigned)((rows + rpb - 1) / rpb));
+    colsum_kernel<<<grid, dim3(32, 8), 0, stream>>>(x, out, rows, n, ld, rpb);
+    B2T_CHECK_LAUNCH("b2t_colsum");
+    return 0;
+}
+
+extern "C" int b2t_axpby(const float* a, const float* b, float* out, int64_t n, float alpha, float beta, b2t_stream stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    B2T_CHECK_ARG(a && out && n > 0, "b2t_axpby: bad arguments");
+    axpby_kernel<<<grid_for(n, 256), 256, 0, stream>>>(a, b, out, n, alpha, beta);
+    B2T_CHECK_LAUNCH("b2t_axpby");
+    return 0;
+}

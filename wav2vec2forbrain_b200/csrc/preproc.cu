@@ -1,0 +1,148 @@
+// Stage 1 of the path (b2p2t_model.py:138-167): [optional augmentation] -> Gaussian smoothing.
+// The day affine + softsign that follow run as a batched tcgen05 GEMM with a softsign epilogue
+// (b2t_gemm, b_batch_idx = day), the unfold is never materialised (unfold view of b2t_gemm).
+//
+// HBM-bound stencil: one CTA = one trial x TT frames x all channels; the (TT + taps - 1) x C
+// input window is staged once in shared memory with coalesced float4 loads, every output
+// frame then reads its `taps` neighbours from smem.  Algorithmic traffic: 4 B read + 4 B write
+// (bf16 hi+lo) per element.
+#include "common.cuh"
+#include "../../include/b2t_sm100.h"
+
+namespace {
+
+constexpr int TT = 32;   // output frames per CTA
+
+__device__ __forceinline__ float gauss_from_hash(unsigned long long seed, unsigned long long idx) {
+    // Box-Muller on two counter-based uniforms
+    const float u1 = fmaxf(hash_uniform(seed, 2 * idx), 1e-7f);
+    const float u2 = hash_uniform(seed, 2 * idx + 1);
+    return sqrtf(-2.0f * __logf(u1)) * __cosf(6.28318530717958647692f * u2);
+}
+
+// x [B,T,C] fp32; taps [C, ntaps] (the registered buffer gaussian_smoother.weight [C,1,ntaps]);
+// y = sum_k taps[c][k] * xa[b, t + k - pad_left, c], zero outside [0,T)
+// xa = x + white_sd*N(0,1) per element + offset_sd*N(0,1) per (b,c)   (train_loop.py:46-62, intended form)
+__global__ void __launch_bounds__(256) smooth_fwd_kernel(const float* __restrict__ x, const float* __restrict__ taps,
+                                                         float* __restrict__ y, bf16* __restrict__ y_hi,
+                                                         bf16* __restrict__ y_lo, int T, int C, int ntaps, int pad_left,
+                                                         float white_sd, float offset_sd, unsigned long long seed) {
+    extern __shared__ float win[];   // [(TT + ntaps - 1)][C]
+    const int b = blockIdx.y;
+    const int t0 = blockIdx.x * TT;
+    const int rows = TT + ntaps - 1;
+    const float* xb = x + (long)b * T * C;
+    const int c4n = C >> 2;
+    for (int i = threadIdx.x; i < rows * c4n; i += blockDim.x) {
+        const int r = i / c4n, c4 = i - r * c4n;
+        const int t = t0 + r - pad_left;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (t >= 0 && t < T) {
+            v = *reinterpret_cast<const float4*>(xb + (long)t * C + c4 * 4);
+            if (white_sd > 0.0f || offset_sd > 0.0f) {
+                float* pv = reinterpret_cast<float*>(&v);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int c = c4 * 4 + j;
+                    if (white_sd > 0.0f) pv[j] += white_sd * gauss_from_hash(seed, ((unsigned long long)b * T + t) * C + c);
+                    if (offset_sd > 0.0f)
+                        pv[j] += offset_sd * gauss_from_hash(seed ^ 0x5851F42D4C957F2Dull, (unsigned long long)b * C + c);
+                }
+            }
+        }
+        *reinterpret_cast<float4*>(win + r * C + c4 * 4) = v;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < TT * c4n; i += blockDim.x) {
+        const int r = i / c4n, c4 = i - r * c4n;
+        const int t = t0 + r;
+        if (t >= T) break;
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int k = 0; k < ntaps; ++k) {
+            const float4 v = *reinterpret_cast<const float4*>(win + (r + k) * C + c4 * 4);
+            acc[0] = fmaf(taps[(c4 * 4 + 0) * ntaps + k], v.x, acc[0]);
+            acc[1] = fmaf(taps[(c4 * 4 + 1) * ntaps + k], v.y, acc[1]);
+            acc[2] = fmaf(taps[(c4 * 4 + 2) * ntaps + k], v.z, acc[2]);
+            acc[3] = fmaf(taps[(c4 * 4 + 3) * ntaps + k], v.w, acc[3]);
+        }
+        const long off = ((long)b * T + t) * C + c4 * 4;
+        if (y) *reinterpret_cast<float4*>(y + off) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+        if (y_hi) {
+            bf16 h[4], l[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) split_bf16(acc[j], h[j], l[j]);
+            __nv_bfloat162 p0 = __halves2bfloat162(h[0], h[1]), p1 = __halves2bfloat162(h[2], h[3]);
+            uint2 o;
+            o.x = *reinterpret_cast<uint32_t*>(&p0);
+            o.y = *reinterpret_cast<uint32_t*>(&p1);
+            *reinterpret_cast<uint2*>(y_hi + off) = o;
+            if (y_lo) {
+                p0 = __halves2bfloat162(l[0], l[1]);
+                p1 = __halves2bfloat162(l[2], l[3]);
+                o.x = *reinterpret_cast<uint32_t*>(&p0);
+                o.y = *reinterpret_cast<uint32_t*>(&p1);
+                *reinterpret_cast<uint2*>(y_lo + off) = o;
+            }
+        }
+    }
+}
+
+// dz = ds * softsign'(z) -> bf16 hi/lo (operand of the day-weight gradient GEMM) and
+// dbias[day_b][c] += sum_t dz[b,t,c]
+__global__ void __launch_bounds__(256) softsign_bwd_kernel(const float* __restrict__ ds, const float* __restrict__ z,
+                                                           const int* __restrict__ day, bf16* __restrict__ dz_hi,
+                                                           bf16* __restrict__ dz_lo, float* __restrict__ dbias, int T,
+                                                           int C, int rows_per_block) {
+    const int b = blockIdx.y;
+    const int t0 = blockIdx.x * rows_per_block;
+    const int d = day[b];
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        float acc = 0.0f;
+        for (int r = 0; r < rows_per_block; ++r) {
+            const int t = t0 + r;
+            if (t >= T) break;
+            const long off = ((long)b * T + t) * C + c;
+            const float den = 1.0f + fabsf(z[off]);
+            const float g = ds[off] / (den * den);
+            acc += g;
+            bf16 h, l;
+            split_bf16(g, h, l);
+            dz_hi[off] = h;
+            if (dz_lo) dz_lo[off] = l;
+        }
+        atomicAdd(dbias + (long)d * C + c, acc);
+    }
+}
+
+}  // namespace
+
+extern "C" int b2t_smooth_fwd(const float* x, const float* taps, float* y, void* y_hi, void* y_lo, int B, int T, int C,
+                              int ntaps, int pad_left, float white_sd, float offset_sd, uint64_t seed, b2t_stream stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    B2T_CHECK_ARG(x && taps && (y || y_hi), "b2t_smooth_fwd: null pointer");
+    B2T_CHECK_ARG(B > 0 && T > 0 && C > 0 && C % 4 == 0 && ntaps > 0 && pad_left >= 0 && pad_left < ntaps,
+                  "b2t_smooth_fwd: bad sizes B=%d T=%d C=%d taps=%d pad=%d", B, T, C, ntaps, pad_left);
+    const size_t smem = (size_t)(TT + ntaps - 1) * C * sizeof(float);
+    B2T_CHECK_ARG(smem <= 200 * 1024, "b2t_smooth_fwd: window of %zu bytes does not fit in shared memory", smem);
+    static bool attr = false;
+    if (!attr) {
+        B2T_CUDA(cudaFuncSetAttribute(smooth_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr = true;
+    }
+    dim3 grid((T + TT - 1) / TT, B);
+    smooth_fwd_kernel<<<grid, 256, smem, stream>>>(x, taps, y, (bf16*)y_hi, (bf16*)y_lo, T, C, ntaps, pad_left, white_sd,
+                                                   offset_sd, (unsigned long long)seed);
+    B2T_CHECK_LAUNCH("b2t_smooth_fwd");
+    return 0;
+}
+
+extern "C" int b2t_softsign_bwd(const float* ds, const float* z, const int32_t* day, void* dz_hi, void* dz_lo, float* dbias,
+                                int B, int T, int C, b2t_stream stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    B2T_CHECK_ARG(ds && z && day && dz_hi && dbias && B > 0 && T > 0 && C > 0, "b2t_softsign_bwd: bad arguments");
+    const int rows = 16;
+    dim3 grid((T + rows - 1) / rows, B);
+    softsign_bwd_kernel<<<grid, 256, 0, stream>>>(ds, z, day, (bf16*)dz_hi, (bf16*)dz_lo, dbias, T, C, rows);
+    B2T_CHECK_LAUNCH("b2t_softsign_bwd");
+    return 0;
+}

@@ -110,7 +110,8 @@ def gemm(a: Operand, b: Operand, *, m_per_batch: int, n: int, k: int, batches: i
          bias: Optional[Tensor] = None, residual: Optional[Tensor] = None, aux: Optional[Tensor] = None,
          colsum: Optional[Tensor] = None, act=None, aux_mode=None, atomic: bool = False, split_k: int = 1,
          alpha: float = 1.0, k_spans_batches: bool = False, a_batched: bool = False, b_batched: bool = False,
-         b_batch_idx: Optional[Tensor] = None, c_batch_idx: Optional[Tensor] = None, block_n: int = 0) -> None:
+         b_batch_idx: Optional[Tensor] = None, c_batch_idx: Optional[Tensor] = None, block_n: int = 0,
+         drop_p: float = 0.0, drop_seed: int = 0, bias_batch_stride: int = 0) -> None:
     """D = epilogue(alpha * A . B^T) on the tcgen05 GEMM (see b2t_gemm in include/b2t_sm100.h)."""
     _lib.ensure_device()
     g = GemmArgs()
@@ -132,6 +133,9 @@ def gemm(a: Operand, b: Operand, *, m_per_batch: int, n: int, k: int, batches: i
     g.split_k = split_k
     g.alpha = alpha
     g.block_n = block_n
+    g.drop_p = drop_p
+    g.drop_seed = drop_seed & 0xFFFFFFFFFFFFFFFF
+    g.bias_batch_stride = bias_batch_stride
     check(lib().b2t_gemm(ctypes.byref(g), stream()), "b2t_gemm")
     _count()
 
@@ -147,3 +151,215 @@ def gemm_simt(a: Tensor, b: Tensor, bias: Optional[Tensor] = None) -> Tensor:
           "b2t_gemm_simt")
     _count()
     return c
+
+
+# ---------------------------------------------------------------------------------------------
+# non-GEMM kernels
+# ---------------------------------------------------------------------------------------------
+c_uint64 = ctypes.c_uint64
+
+
+def _bf16_like(x: Tensor, enable: bool = True):
+    return torch.empty(x.shape, dtype=torch.bfloat16, device=x.device) if enable else None
+
+
+def smooth_fwd(x: Tensor, taps: Tensor, pad_left: int, three: bool = True, want_f32: bool = False,
+               white_sd: float = 0.0, offset_sd: float = 0.0, seed: int = 0):
+    """x [B,T,C] -> smoothed (y_f32 | None, y_hi, y_lo | None)."""
+    _lib.ensure_device()
+    B, T, C = x.shape
+    taps2 = taps.reshape(C, -1).contiguous()
+    y = torch.empty_like(x) if want_f32 else None
+    hi, lo = _bf16_like(x), _bf16_like(x, three)
+    check(lib().b2t_smooth_fwd(ptr(x), ptr(taps2), ptr(y), ptr(hi), ptr(lo), c_int(B), c_int(T), c_int(C),
+                               c_int(taps2.shape[1]), c_int(pad_left), c_float(white_sd), c_float(offset_sd),
+                               c_uint64(seed & 0xFFFFFFFFFFFFFFFF), stream()), "b2t_smooth_fwd")
+    _count()
+    return y, hi, lo
+
+
+def softsign_bwd(ds: Tensor, z: Tensor, day: Tensor, dbias: Tensor, three: bool = True):
+    B, T, C = ds.shape
+    hi, lo = _bf16_like(ds), _bf16_like(ds, three)
+    check(lib().b2t_softsign_bwd(ptr(ds), ptr(z), ptr(day), ptr(hi), ptr(lo), ptr(dbias), c_int(B), c_int(T), c_int(C),
+                                 stream()), "b2t_softsign_bwd")
+    _count()
+    return hi, lo
+
+
+def layernorm_fwd(x: Tensor, gamma: Tensor, beta: Tensor, eps: float, three: bool = True, want_f32: bool = True,
+                  want_split: bool = True, drop_p: float = 0.0, seed: int = 0):
+    """x [rows, n] -> (y | None, y_hi | None, y_lo | None, mean, rstd)."""
+    _lib.ensure_device()
+    rows, n = x.shape
+    y = torch.empty_like(x) if want_f32 else None
+    hi = _bf16_like(x, want_split)
+    lo = _bf16_like(x, want_split and three)
+    mean = torch.empty(rows, dtype=torch.float32, device=x.device)
+    rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
+    check(lib().b2t_layernorm_fwd(ptr(x), ptr(gamma), ptr(beta), c_float(eps), ptr(y), ptr(hi), ptr(lo), ptr(mean),
+                                  ptr(rstd), c_int(rows), c_int(n), c_float(drop_p), c_uint64(seed), stream()),
+          "b2t_layernorm_fwd")
+    _count()
+    return y, hi, lo, mean, rstd
+
+
+def layernorm_bwd(dy: Tensor, x: Tensor, gamma: Tensor, mean: Tensor, rstd: Tensor, dgamma: Tensor, dbeta: Tensor,
+                  dcol: Optional[Tensor] = None, three: bool = True, want_f32: bool = True, want_split: bool = True,
+                  out_drop_p: float = 0.0, out_seed: int = 0, br_drop_p: float = 0.0, br_seed: int = 0):
+    """-> (dx | None, dx_hi | None, dx_lo | None); dgamma/dbeta/dcol are accumulated into."""
+    rows, n = x.shape
+    dx = torch.empty_like(x) if want_f32 else None
+    hi = _bf16_like(x, want_split)
+    lo = _bf16_like(x, want_split and three)
+    check(lib().b2t_layernorm_bwd(ptr(dy), ptr(x), ptr(gamma), ptr(mean), ptr(rstd), ptr(dx), ptr(hi), ptr(lo),
+                                  ptr(dgamma), ptr(dbeta), ptr(dcol), c_int(rows), c_int(n), c_float(out_drop_p),
+                                  c_uint64(out_seed), c_float(br_drop_p), c_uint64(br_seed), stream()),
+          "b2t_layernorm_bwd")
+    _count()
+    return dx, hi, lo
+
+
+def dropout(x: Tensor, p: float, seed: int, three: bool = True, want_f32: bool = True, want_split: bool = False):
+    """y = dropout(x) (p == 0: identity / plain split) -> (y | None, hi | None, lo | None)."""
+    _lib.ensure_device()
+    assert x.is_contiguous()
+    y = torch.empty_like(x) if want_f32 else None
+    hi = _bf16_like(x, want_split)
+    lo = _bf16_like(x, want_split and three)
+    check(lib().b2t_dropout(ptr(x), ptr(y), ptr(hi), ptr(lo), c_int64(x.numel()), c_float(p), c_uint64(seed), stream()),
+          "b2t_dropout")
+    _count()
+    return y, hi, lo
+
+
+def colsum(x: Tensor, out: Tensor, n: Optional[int] = None, ld: Optional[int] = None, rows: Optional[int] = None) -> None:
+    """out[c] += sum_r x[r, c] over a [rows, n] view with row stride ld."""
+    x2 = x.reshape(-1, x.shape[-1])
+    rows = x2.shape[0] if rows is None else rows
+    n = x2.shape[1] if n is None else n
+    ld = x2.stride(0) if ld is None else ld
+    check(lib().b2t_colsum(ptr(x), ptr(out), c_int64(rows), c_int(n), c_int64(ld), stream()), "b2t_colsum")
+    _count()
+
+
+def axpby(a: Tensor, b: Optional[Tensor], alpha: float = 1.0, beta: float = 1.0, out: Optional[Tensor] = None) -> Tensor:
+    out = torch.empty_like(a) if out is None else out
+    check(lib().b2t_axpby(ptr(a), ptr(b), ptr(out), c_int64(a.numel()), c_float(alpha), c_float(beta), stream()), "b2t_axpby")
+    _count()
+    return out
+
+
+def attention_fwd(qkv: Tensor, B: int, T: int, H: int, d: int, three: bool = True, save_probs: bool = True,
+                  drop_p: float = 0.0, seed: int = 0, kv_lens: Optional[Tensor] = None, want_f32: bool = False):
+    """qkv [B*T, 3*H*d] (q | k | v) -> (ctx | None, ctx_hi, ctx_lo | None, probs | None)."""
+    _lib.ensure_device()
+    hd = H * d
+    probs = torch.empty(B, H, T, T, dtype=torch.float32, device=qkv.device) if save_probs else None
+    ctx = torch.empty(B * T, hd, dtype=torch.float32, device=qkv.device) if want_f32 else None
+    hi = torch.empty(B * T, hd, dtype=torch.bfloat16, device=qkv.device)
+    lo = torch.empty(B * T, hd, dtype=torch.bfloat16, device=qkv.device) if three else None
+    check(lib().b2t_attention_fwd(ptr(qkv), c_int64(qkv.stride(0)), c_int(0), c_int(hd), c_int(2 * hd), ptr(kv_lens),
+                                  ptr(probs), ptr(ctx), ptr(hi), ptr(lo), c_int64(hd), c_int(B), c_int(T), c_int(H),
+                                  c_int(d), c_float(d ** -0.5), c_float(drop_p), c_uint64(seed), stream()),
+          "b2t_attention_fwd")
+    _count()
+    return ctx, hi, lo, probs
+
+
+def attention_bwd(qkv: Tensor, probs: Tensor, dctx: Tensor, ds_ws: Tensor, B: int, T: int, H: int, d: int,
+                  three: bool = True, drop_p: float = 0.0, seed: int = 0):
+    """-> (dqkv fp32, dqkv_hi, dqkv_lo | None) packed like qkv."""
+    hd = H * d
+    dqkv = torch.empty_like(qkv)
+    hi, lo = _bf16_like(qkv), _bf16_like(qkv, three)
+    check(lib().b2t_attention_bwd(ptr(qkv), c_int64(qkv.stride(0)), c_int(0), c_int(hd), c_int(2 * hd), ptr(probs),
+                                  ptr(dctx), c_int64(dctx.stride(0)), ptr(ds_ws), ptr(dqkv), ptr(hi), ptr(lo), c_int(B),
+                                  c_int(T), c_int(H), c_int(d), c_float(d ** -0.5), c_float(drop_p), c_uint64(seed),
+                                  stream()), "b2t_attention_bwd")
+    _count()
+    return dqkv, hi, lo
+
+
+def gru_supported_hidden(H: int) -> bool:
+    return bool(lib().b2t_gru_supported_hidden(c_int(H)))
+
+
+def gru_fwd(gi: Tensor, w_hh: Tensor, b_hh: Tensor, h0: Optional[Tensor], B: int, T: int, H: int, ndir: int,
+            three: bool = True, training: bool = True, drop_p: float = 0.0, seed: int = 0):
+    """gi [B*T, ndir*3H]; w_hh [ndir,3H,H]; b_hh [ndir,3H]; h0 [ndir,H] | None.
+    -> dict(out, out_hi, out_lo, r, z, n, ghn, hprev_hi, hprev_lo)"""
+    _lib.ensure_device()
+    dev = gi.device
+    M = B * T
+    f32 = dict(dtype=torch.float32, device=dev)
+    b16 = dict(dtype=torch.bfloat16, device=dev)
+    res = {"out": torch.empty(M, ndir * H, **f32), "out_hi": torch.empty(M, ndir * H, **b16),
+           "out_lo": torch.empty(M, ndir * H, **b16) if three else None}
+    if training:
+        for k in ("r", "z", "n", "ghn"):
+            res[k] = torch.empty(ndir, M, H, **f32)
+        res["hprev_hi"] = torch.empty(ndir, M, H, **b16)
+        res["hprev_lo"] = torch.empty(ndir, M, H, **b16) if three else None
+    else:
+        for k in ("r", "z", "n", "ghn", "hprev_hi", "hprev_lo"):
+            res[k] = None
+    check(lib().b2t_gru_fwd(ptr(gi), ptr(w_hh), ptr(b_hh), ptr(h0), ptr(res["out"]), ptr(res["out_hi"]), ptr(res["out_lo"]),
+                            ptr(res["r"]), ptr(res["z"]), ptr(res["n"]), ptr(res["ghn"]), ptr(res["hprev_hi"]),
+                            ptr(res["hprev_lo"]), c_int(B), c_int(T), c_int(H), c_int(ndir), c_float(drop_p), c_uint64(seed),
+                            stream()), "b2t_gru_fwd")
+    _count()
+    return res
+
+
+def gru_bwd(dout: Tensor, fw: dict, w_hh: Tensor, h0: Optional[Tensor], dh0: Optional[Tensor], B: int, T: int, H: int,
+            ndir: int, three: bool = True, drop_p: float = 0.0, seed: int = 0):
+    """-> dict(dgi, dgi_hi, dgi_lo, dgh_hi, dgh_lo, dghn)"""
+    dev = dout.device
+    M = B * T
+    f32 = dict(dtype=torch.float32, device=dev)
+    b16 = dict(dtype=torch.bfloat16, device=dev)
+    res = {"dgi": torch.empty(M, ndir * 3 * H, **f32), "dgi_hi": torch.empty(M, ndir * 3 * H, **b16),
+           "dgi_lo": torch.empty(M, ndir * 3 * H, **b16) if three else None,
+           "dgh_hi": torch.empty(ndir, M, 3 * H, **b16), "dgh_lo": torch.empty(ndir, M, 3 * H, **b16) if three else None,
+           "dghn": torch.empty(ndir, M, H, **f32)}
+    check(lib().b2t_gru_bwd(ptr(dout), ptr(fw["out"]), ptr(w_hh), ptr(h0), ptr(fw["r"]), ptr(fw["z"]), ptr(fw["n"]),
+                            ptr(fw["ghn"]), ptr(res["dgi"]), ptr(res["dgi_hi"]), ptr(res["dgi_lo"]), ptr(res["dgh_hi"]),
+                            ptr(res["dgh_lo"]), ptr(res["dghn"]), ptr(dh0), c_int(B), c_int(T), c_int(H), c_int(ndir),
+                            c_float(drop_p), c_uint64(seed), stream()), "b2t_gru_bwd")
+    _count()
+    return res
+
+
+def ctc_fwd_bwd(logits: Tensor, targets: Tensor, input_lens: Tensor, target_lens: Tensor, want_grad: bool = True):
+    """logits [B,T,V] fp32, targets [B,S] int64, input_lens [B] int32, target_lens [B] int64.
+    -> (loss 0-dim, nll [B], dlogits [B,T,V] | None)"""
+    _lib.ensure_device()
+    B, T, V = logits.shape
+    S = targets.shape[1]
+    lib().b2t_ctc_workspace_floats.restype = ctypes.c_int64
+    nws = lib().b2t_ctc_workspace_floats(c_int(B), c_int(T), c_int(S))
+    ws = torch.empty(nws, dtype=torch.float32, device=logits.device)
+    nll = torch.empty(B, dtype=torch.float32, device=logits.device)
+    loss = torch.zeros((), dtype=torch.float32, device=logits.device)
+    grad = torch.empty_like(logits) if want_grad else None
+    assert targets.dtype == torch.int64 and target_lens.dtype == torch.int64 and input_lens.dtype == torch.int32
+    assert targets.is_contiguous() and logits.stride(2) == 1
+    check(lib().b2t_ctc_fwd_bwd(ptr(logits), c_int64(logits.stride(1)), c_int64(logits.stride(0)), ptr(targets), c_int(S),
+                                ptr(input_lens), ptr(target_lens), ptr(ws), ptr(nll), ptr(loss), ptr(grad), c_int(B),
+                                c_int(T), c_int(V), c_int(1), stream()), "b2t_ctc_fwd_bwd")
+    _count()
+    return loss, nll, grad
+
+
+def greedy_decode(logits: Tensor):
+    """-> (argmax [B,T] int32, ids [B,T] int32 collapsed/no blanks/0-padded, lens [B] int32)"""
+    _lib.ensure_device()
+    B, T, V = logits.shape
+    am = torch.empty(B, T, dtype=torch.int32, device=logits.device)
+    ids = torch.empty(B, T, dtype=torch.int32, device=logits.device)
+    lens = torch.empty(B, dtype=torch.int32, device=logits.device)
+    check(lib().b2t_greedy_decode(ptr(logits), c_int64(logits.stride(1)), c_int64(logits.stride(0)), ptr(am), ptr(ids),
+                                  ptr(lens), c_int(B), c_int(T), c_int(V), stream()), "b2t_greedy_decode")
+    _count()
+    return am, ids, lens
