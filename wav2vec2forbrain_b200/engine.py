@@ -1,0 +1,634 @@
+"""Forward / backward schedule of the b2p2t_gru+w2v hot path over the C-ABI kernels.
+
+This is the host-side replacement of W2VBrainEncoderModel.forward + loss.backward()
+(src/model/w2v_custom_feat_extractor.py:65-123, src/train/train_loop.py:67-70): one explicit
+kernel schedule with hand-derived backward, instead of ~2000 autograd nodes of library calls.
+All activations are fp32 master copies plus bf16 (hi[, lo]) operand copies written by the
+producing kernel's epilogue; weights are split once per optimizer step.
+
+`ops` is looked up through the module global so the CPU test-suite can substitute an emulator of
+the C ABI (tests/abi_emulator.py) and check this schedule against the oracle without a GPU; the
+product never does.
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, List, Optional
+
+import torch
+
+from . import ops as _real_ops
+from .config import BrainEncoderConfig, W2VConfig, NEURAL_DIM
+
+ops = _real_ops
+Tensor = torch.Tensor
+
+
+def _mix(seed: int, site: int) -> int:
+    """per-site dropout seed (splitmix-style, host side)."""
+    z = (seed * 0x9E3779B97F4A7C15 + site * 0xD1B54A32D192ED03 + 0x632BE59BD9B4E019) & 0xFFFFFFFFFFFFFFFF
+    z ^= z >> 31
+    return (z * 0x94D049BB133111EB) & 0xFFFFFFFFFFFFFFFF
+
+
+class Weights:
+    """fp32 parameters + cached bf16 operand copies, keyed by parameter version."""
+
+    def __init__(self, three: bool):
+        self.three = three
+        self._cache: Dict[str, tuple] = {}
+
+    def get(self, key: str, versions: tuple, build):
+        hit = self._cache.get(key)
+        if hit is not None and hit[0] == versions:
+            return hit[1]
+        val = build()
+        self._cache[key] = (versions, val)
+        return val
+
+
+def _ver(*ts) -> tuple:
+    return tuple((t.data_ptr(), t._version) for t in ts if t is not None)
+
+
+def _split_k_for(m: int, n: int, k_blocks: int, bn: int = 128) -> int:
+    tiles = ((m + 127) // 128) * ((n + bn - 1) // bn)
+    if tiles >= 96:
+        return 1
+    return max(1, min(148 // tiles, max(1, k_blocks // 4), 16))
+
+
+class Engine:
+    def __init__(self, be: BrainEncoderConfig, w2v: W2VConfig, precision: str = "bf16x3"):
+        assert precision in ("bf16x3", "bf16")
+        self.be, self.w2v = be, w2v
+        self.three = precision == "bf16x3"
+        self.precision = precision
+        self.weights = Weights(self.three)
+        if be.nonlinearity != "softsign":
+            raise NotImplementedError("input_layer_nonlinearity other than softsign")  # b2p2t_model.py:107
+        if be.fc_act not in ("gelu", "silu", "swish"):
+            raise NotImplementedError(f"encoder_fc_activation_function={be.fc_act}")
+
+    # ------------------------------------------------------------------------------------------
+    # helpers
+    # ------------------------------------------------------------------------------------------
+    def _w(self, P, name: str):
+        """bf16 operand copy of a [N, K] weight (serves forward as K-major and dgrad as MN-major)."""
+        w = P[name]
+        return self.weights.get(name, _ver(w), lambda: ops.split(w, self.three))
+
+    def _w_cat(self, P, key: str, names: List[str], unfold=None):
+        """several [N_i, K] weights stacked along N into one operand (QKV, both GRU directions)."""
+        ws = [P[n] for n in names]
+
+        def build():
+            n_tot = sum(w.shape[0] for w in ws)
+            k = ws[0].shape[1]
+            hi = torch.empty(n_tot, k, dtype=torch.bfloat16, device=ws[0].device)
+            lo = torch.empty_like(hi) if self.three else None
+            r = 0
+            for w in ws:
+                if unfold is None:
+                    h, l = ops.split(w, self.three)
+                else:
+                    h, l = ops.permute_unfold_cols(w, unfold[0], unfold[1], self.three)
+                hi[r:r + w.shape[0]].copy_(h)
+                if lo is not None:
+                    lo[r:r + w.shape[0]].copy_(l)
+                r += w.shape[0]
+            return hi, lo
+        return self.weights.get(key, _ver(*ws), build)
+
+    @staticmethod
+    def _cat_vec(P, names: List[str]) -> Optional[Tensor]:
+        vs = [P.get(n) for n in names]
+        if any(v is None for v in vs):
+            return None
+        return torch.cat([v.reshape(-1) for v in vs])
+
+    def _linear_fwd(self, a_hi, a_lo, w_hl, bias, M, N, K, **kw):
+        """[M,K] x [N,K]^T with epilogue; outputs selected through kw (want_f32 / want_split / want_pre)."""
+        dev = a_hi.device
+        want_f32 = kw.pop("want_f32", True)
+        want_split = kw.pop("want_split", False)
+        want_pre = kw.pop("want_pre", False)
+        out = torch.empty(M, N, dtype=torch.float32, device=dev) if want_f32 else None
+        pre = torch.empty(M, N, dtype=torch.float32, device=dev) if want_pre else None
+        hi = torch.empty(M, N, dtype=torch.bfloat16, device=dev) if want_split else None
+        lo = torch.empty(M, N, dtype=torch.bfloat16, device=dev) if (want_split and self.three) else None
+        ops.gemm(ops.kmajor(a_hi, a_lo), ops.kmajor(w_hl[0], w_hl[1]), m_per_batch=M, n=N, k=K, out_f32=out, out_pre=pre,
+                 out_hi=hi, out_lo=lo, bias=bias, **kw)
+        return out, pre, hi, lo
+
+    def _wgrad(self, dy_hi, dy_lo, x_hi, x_lo, N, K, M, out: Optional[Tensor] = None) -> Tensor:
+        """dW[N,K] = dY[M,N]^T . X[M,K]  (both operands row-major, contracted over rows)."""
+        kb = (M + 63) // 64
+        sk = _split_k_for(N, K, kb)
+        if out is None:
+            out = (torch.zeros if sk > 1 else torch.empty)(N, K, dtype=torch.float32, device=dy_hi.device)
+        ops.gemm(ops.mnmajor(dy_hi, dy_lo), ops.mnmajor(x_hi, x_lo), m_per_batch=N, n=K, k=M, out_f32=out,
+                 atomic=sk > 1, split_k=sk)
+        return out
+
+    def _dgrad(self, dy_hi, dy_lo, w_hl, M, N, K, **kw):
+        """dX[M,K] = dY[M,N] . W[N,K]"""
+        dev = dy_hi.device
+        want_f32 = kw.pop("want_f32", True)
+        want_split = kw.pop("want_split", False)
+        out = torch.empty(M, K, dtype=torch.float32, device=dev) if want_f32 else None
+        hi = torch.empty(M, K, dtype=torch.bfloat16, device=dev) if want_split else None
+        lo = torch.empty(M, K, dtype=torch.bfloat16, device=dev) if (want_split and self.three) else None
+        ops.gemm(ops.kmajor(dy_hi, dy_lo), ops.mnmajor(w_hl[0], w_hl[1]), m_per_batch=M, n=K, k=N, out_f32=out, out_hi=hi,
+                 out_lo=lo, **kw)
+        return out, hi, lo
+
+    # ------------------------------------------------------------------------------------------
+    # brain encoder   (b2p2t_model.py:138-183, brain_feature_extractor.py:56-68)
+    # ------------------------------------------------------------------------------------------
+    def brain_forward(self, P, x: Tensor, day: Tensor, training: bool, seed: int, aug=(0.0, 0.0)):
+        be = self.be
+        three = self.three
+        B, T, C = x.shape
+        assert C == NEURAL_DIM
+        S: dict = {"B": B, "T": T}
+        pre = "brain_encoder."
+        taps = P[pre + "gaussian_smoother.weight"]
+        ntaps = taps.shape[-1]
+        _, y_hi, y_lo = ops.smooth_fwd(x, taps, pad_left=(ntaps - 1) // 2, three=three, white_sd=aug[0], offset_sd=aug[1],
+                                       seed=_mix(seed, 1))
+        # day affine + softsign: z = y . W[day] + b[day]  (x.W, not x.W^T: the B operand is MN-major W[day])
+        dw_hl = self._w(P, pre + "day_weights")
+        dev = x.device
+        z = torch.empty(B, T, C, dtype=torch.float32, device=dev) if training else None
+        s_hi = torch.empty(B, T, C, dtype=torch.bfloat16, device=dev)
+        s_lo = torch.empty(B, T, C, dtype=torch.bfloat16, device=dev) if three else None
+        ops.gemm(ops.kmajor(y_hi, y_lo), ops.mnmajor(dw_hl[0], dw_hl[1]), m_per_batch=T, batches=B, n=C, k=C, out_pre=z,
+                 out_hi=s_hi, out_lo=s_lo, a_batched=True, b_batch_idx=day, bias=P[pre + "day_bias"], bias_batch_stride=C,
+                 act="softsign")
+        S.update(y_hi=y_hi, y_lo=y_lo, z=z, s_hi=s_hi, s_lo=s_lo, day=day)
+
+        KL, ST = be.unfold_len, be.unfold_stride
+        Tp = (T - KL) // ST + 1
+        M = B * Tp
+        H, ndir, L = be.gru_hidden, be.ndir, be.gru_layers
+        e = pre + "neural_decoder.encoder."
+        sfx = [""] + (["_reverse"] if ndir == 2 else [])
+        S["Tp"] = Tp
+        S["gru"] = []
+        in_hi, in_lo = None, None
+        for l in range(L):
+            names = [e + f"gru.weight_ih_l{l}{s}" for s in sfx]
+            b_ih = self._cat_vec(P, [e + f"gru.bias_ih_l{l}{s}" for s in sfx]) if be.bias else None
+            gi = torch.empty(M, ndir * 3 * H, dtype=torch.float32, device=dev)
+            if l == 0:
+                w_hl = self._w_cat(P, f"gru_ih_l0_cat", names, unfold=(C, KL))
+                ops.gemm(ops.unfold_view(s_hi, s_lo, KL, ST), ops.kmajor(w_hl[0], w_hl[1]), m_per_batch=Tp, batches=B,
+                         n=ndir * 3 * H, k=C * KL, out_f32=gi, a_batched=True, bias=b_ih)
+            else:
+                w_hl = self._w_cat(P, f"gru_ih_l{l}_cat", names)
+                ops.gemm(ops.kmajor(in_hi, in_lo), ops.kmajor(w_hl[0], w_hl[1]), m_per_batch=M, n=ndir * 3 * H, k=ndir * H,
+                         out_f32=gi, bias=b_ih)
+            w_hh = torch.stack([P[e + f"gru.weight_hh_l{l}{s}"] for s in sfx])
+            if be.bias:
+                b_hh = torch.stack([P[e + f"gru.bias_hh_l{l}{s}"] for s in sfx])
+            else:
+                b_hh = torch.zeros(ndir, 3 * H, dtype=torch.float32, device=dev)
+            h0 = P[e + "hidden_start"][l * ndir:(l + 1) * ndir].contiguous() if be.learnable_h0 else None
+            p_drop = be.dropout if (training and l < L - 1) else 0.0
+            fw = ops.gru_fwd(gi, w_hh, b_hh, h0, B, Tp, H, ndir, three=three, training=training, drop_p=p_drop,
+                             seed=_mix(seed, 100 + l))
+            fw.update(w_hh=w_hh, h0=h0, drop_p=p_drop, seed=_mix(seed, 100 + l), in_hi=in_hi, in_lo=in_lo)
+            S["gru"].append(fw)
+            in_hi, in_lo = fw["out_hi"], fw["out_lo"]
+        # FC stack (nn_helper.py:31-49): Linear, act, ..., Linear
+        sizes = [ndir * H] + list(be.fc_hidden) + [be.out_size]
+        S["fc"] = []
+        a_hi, a_lo = in_hi, in_lo
+        feats = None
+        for i in range(len(sizes) - 1):
+            last = i == len(sizes) - 2
+            w_hl = self._w(P, e + f"fc.{2 * i}.weight")
+            bias = P[e + f"fc.{2 * i}.bias"]
+            if last:
+                feats, _, _, _ = self._linear_fwd(a_hi, a_lo, w_hl, bias, M, sizes[i + 1], sizes[i])
+                S["fc"].append(dict(a_hi=a_hi, a_lo=a_lo, pre=None))
+            else:
+                _, prea, hi, lo = self._linear_fwd(a_hi, a_lo, w_hl, bias, M, sizes[i + 1], sizes[i], want_f32=False,
+                                                   want_split=True, want_pre=training, act=be.fc_act)
+                S["fc"].append(dict(a_hi=a_hi, a_lo=a_lo, pre=prea))
+                a_hi, a_lo = hi, lo
+        return feats, S
+
+    def brain_backward(self, P, S: dict, dfeats: Tensor, G: Dict[str, Tensor]) -> None:
+        """dfeats [M, out_size] -> parameter gradients of the brain encoder written into G."""
+        be = self.be
+        three = self.three
+        B, T, Tp = S["B"], S["T"], S["Tp"]
+        M = B * Tp
+        H, ndir, L = be.gru_hidden, be.ndir, be.gru_layers
+        C = NEURAL_DIM
+        pre = "brain_encoder."
+        e = pre + "neural_decoder.encoder."
+        sfx = [""] + (["_reverse"] if ndir == 2 else [])
+        dev = dfeats.device
+        sizes = [ndir * H] + list(be.fc_hidden) + [be.out_size]
+        # ---- FC stack ----
+        _, d_hi, d_lo = ops.dropout(dfeats, 0.0, 0, three=three, want_f32=False, want_split=True)
+        d_f32 = dfeats
+        for i in reversed(range(len(sizes) - 1)):
+            st = S["fc"][i]
+            wname = e + f"fc.{2 * i}.weight"
+            G[wname] = self._wgrad(d_hi, d_lo, st["a_hi"], st["a_lo"], sizes[i + 1], sizes[i], M)
+            if d_f32 is not None:
+                db = torch.zeros(sizes[i + 1], dtype=torch.float32, device=dev)
+                ops.colsum(d_f32, db)
+                G[e + f"fc.{2 * i}.bias"] = db
+            w_hl = self._w(P, wname)
+            if i > 0:
+                # gradient w.r.t. the previous Linear's pre-activation, its column sums = that bias gradient
+                db_prev = torch.zeros(sizes[i], dtype=torch.float32, device=dev)
+                _, d_hi, d_lo = self._dgrad(d_hi, d_lo, w_hl, M, sizes[i + 1], sizes[i], want_f32=False, want_split=True,
+                                            aux=S["fc"][i - 1]["pre"], aux_mode=be.fc_act, colsum=db_prev)
+                G[e + f"fc.{2 * (i - 1)}.bias"] = db_prev
+                d_f32 = None
+            else:
+                dout, _, _ = self._dgrad(d_hi, d_lo, w_hl, M, sizes[i + 1], sizes[i])
+        # ---- GRU stack ----
+        for l in reversed(range(L)):
+            fw = S["gru"][l]
+            dh0 = torch.zeros(ndir, H, dtype=torch.float32, device=dev) if be.learnable_h0 else None
+            bw = ops.gru_bwd(dout, fw, fw["w_hh"], fw["h0"], dh0, B, Tp, H, ndir, three=three, drop_p=fw["drop_p"], seed=fw["seed"])
+            if dh0 is not None:
+                G.setdefault(e + "hidden_start", torch.zeros_like(P[e + "hidden_start"]))[l * ndir:(l + 1) * ndir] = dh0
+            # recurrent weights / biases
+            for d, s in enumerate(sfx):
+                G[e + f"gru.weight_hh_l{l}{s}"] = self._wgrad(bw["dgh_hi"][d], None if bw["dgh_lo"] is None else bw["dgh_lo"][d],
+                                                              fw["hprev_hi"][d],
+                                                              None if fw["hprev_lo"] is None else fw["hprev_lo"][d], 3 * H, H, M)
+            db_ih = torch.zeros(ndir * 3 * H, dtype=torch.float32, device=dev)
+            ops.colsum(bw["dgi"], db_ih)
+            dbn = torch.zeros(ndir * H, dtype=torch.float32, device=dev)
+            ops.colsum(bw["dghn"].reshape(ndir * M, H), dbn[:H], rows=M)
+            if ndir == 2:
+                ops.colsum(bw["dghn"][1], dbn[H:], rows=M)
+            if be.bias:
+                for d, s in enumerate(sfx):
+                    seg = db_ih[d * 3 * H:(d + 1) * 3 * H]
+                    G[e + f"gru.bias_ih_l{l}{s}"] = seg
+                    G[e + f"gru.bias_hh_l{l}{s}"] = torch.cat([seg[:2 * H], dbn[d * H:(d + 1) * H]])
+            names = [e + f"gru.weight_ih_l{l}{s}" for s in sfx]
+            if l > 0:
+                w_hl = self._w_cat(P, f"gru_ih_l{l}_cat", names)
+                dw = self._wgrad(bw["dgi_hi"], bw["dgi_lo"], fw["in_hi"], fw["in_lo"], ndir * 3 * H, ndir * H, M)
+                for d, n_ in enumerate(names):
+                    G[n_] = dw[d * 3 * H:(d + 1) * 3 * H]
+                dout, _, _ = self._dgrad(bw["dgi_hi"], bw["dgi_lo"], w_hl, M, ndir * 3 * H, ndir * H)
+            else:
+                KL, ST = be.unfold_len, be.unfold_stride
+                w_hl = self._w_cat(P, "gru_ih_l0_cat", names, unfold=(C, KL))
+                dgi_hi3 = bw["dgi_hi"].view(B, Tp, ndir * 3 * H)
+                dgi_lo3 = bw["dgi_lo"].view(B, Tp, ndir * 3 * H) if bw["dgi_lo"] is not None else None
+                dwp = torch.zeros(ndir * 3 * H, C * KL, dtype=torch.float32, device=dev)
+                kb = B * ((Tp + 63) // 64)
+                sk = _split_k_for(ndir * 3 * H, C * KL, kb)
+                uv = ops.unfold_view(S["s_hi"], S["s_lo"], KL, ST, mn_major=True)
+                ops.gemm(ops.mnmajor(dgi_hi3, dgi_lo3), uv, m_per_batch=ndir * 3 * H, n=C * KL, k=Tp, out_f32=dwp,
+                         k_spans_batches=True, atomic=True, split_k=sk)
+                dw = ops.unpermute_unfold_cols(dwp, C, KL)
+                for d, n_ in enumerate(names):
+                    G[n_] = dw[d * 3 * H:(d + 1) * 3 * H]
+                # ds: dgrad folded through the overlapping unfold view (red.add)
+                ds = torch.zeros(B, T, C, dtype=torch.float32, device=dev)
+                ops.gemm(ops.kmajor(dgi_hi3, dgi_lo3), ops.mnmajor(w_hl[0], w_hl[1]), m_per_batch=Tp, batches=B, n=C * KL,
+                         k=ndir * 3 * H, out_f32=ds, a_batched=True, atomic=True, ldc=ST * C, c_batch_stride=T * C)
+        # ---- softsign + day affine ----
+        dbias = torch.zeros_like(P[pre + "day_bias"])
+        dz_hi, dz_lo = ops.softsign_bwd(ds, S["z"], S["day"], dbias, three=three)
+        G[pre + "day_bias"] = dbias
+        dW = torch.zeros_like(P[pre + "day_weights"])
+        ops.gemm(ops.mnmajor(S["y_hi"], S["y_lo"]), ops.mnmajor(dz_hi, dz_lo), m_per_batch=C, batches=B, n=C, k=T, out_f32=dW,
+                 a_batched=True, b_batched=True, c_batch_idx=S["day"], c_batch_stride=C * C, atomic=True)
+        G[pre + "day_weights"] = dW
+
+    # ------------------------------------------------------------------------------------------
+    # wav2vec2 encoder (post-LN and stable-LN)   transformers modeling_wav2vec2.py:668-803
+    # ------------------------------------------------------------------------------------------
+    def _posconv_forward(self, P, q: str, x: Tensor, B: int, T: int, training: bool):
+        cfg = self.w2v
+        three = self.three
+        D, K, G = cfg.hidden, cfg.pos_conv_k, cfg.pos_conv_groups
+        Cg = D // G
+        CP = ops.POSCONV_CP
+        pad = K // 2
+        Tpad = T + K
+        gk, v = self._posconv_params(P, q)
+        wg_hi, wg_lo, norm = self.weights.get(q + "pos_conv", _ver(gk, v),
+                                              lambda: ops.posconv_pack_weight(gk, v, G, three))
+        xg_hi, xg_lo = ops.posconv_pack_input(x, B, T, G, pad, Tpad, three)
+        M = B * T
+        out = torch.empty(M, D, dtype=torch.float32, device=x.device)
+        pre = torch.empty(M, D, dtype=torch.float32, device=x.device) if training else None
+        bias = P[q + "pos_conv_embed.conv.bias"]
+        for g in range(G):
+            a = ops.unfold_view(xg_hi[g], None if xg_lo is None else xg_lo[g], K, 1)
+            a.d1 = T   # conv output has T+1 frames, the last one is dropped (Wav2Vec2SamePadLayer)
+            wsl = slice(g * Cg, (g + 1) * Cg)
+            ops.gemm(a, ops.kmajor(wg_hi[wsl], None if wg_lo is None else wg_lo[wsl]), m_per_batch=T, batches=B, n=Cg,
+                     k=K * CP, out_f32=out[:, g * Cg:], out_pre=None if pre is None else pre[:, g * Cg:], ldc=D,
+                     c_batch_stride=T * D, a_batched=True, bias=bias[wsl], act="gelu", residual=x[:, g * Cg:], block_n=64)
+        return out, dict(xg_hi=xg_hi, xg_lo=xg_lo, pre=pre, norm=norm, Tpad=Tpad, pad=pad)
+
+    @staticmethod
+    def _posconv_params(P, q: str):
+        k0 = q + "pos_conv_embed.conv.parametrizations.weight.original0"
+        if k0 in P:
+            return P[k0], P[q + "pos_conv_embed.conv.parametrizations.weight.original1"]
+        return P[q + "pos_conv_embed.conv.weight_g"], P[q + "pos_conv_embed.conv.weight_v"]
+
+    def _posconv_backward(self, P, q: str, st: dict, dsum: Tensor, B: int, T: int, G_: Dict[str, Tensor]) -> Tensor:
+        """dsum = gradient w.r.t. (x + gelu(conv(x))).  Returns the gradient w.r.t. x."""
+        cfg = self.w2v
+        three = self.three
+        D, K, G = cfg.hidden, cfg.pos_conv_k, cfg.pos_conv_groups
+        Cg = D // G
+        CP = ops.POSCONV_CP
+        M = B * T
+        dev = dsum.device
+        gk, v = self._posconv_params(P, q)
+        wg_hi, wg_lo, norm = self.weights.get(q + "pos_conv", _ver(gk, v), lambda: ops.posconv_pack_weight(gk, v, G, three))
+        dpre, dp_hi, dp_lo = ops.act_bwd(dsum, st["pre"], "gelu", three=three, want_f32=True, want_split=True)
+        db = torch.zeros(D, dtype=torch.float32, device=dev)
+        ops.colsum(dpre, db)
+        G_[q + "pos_conv_embed.conv.bias"] = db
+        Tpad = st["Tpad"]
+        dxg = torch.zeros(G, B, Tpad, CP, dtype=torch.float32, device=dev)
+        dwg = torch.zeros(D, K * CP, dtype=torch.float32, device=dev)
+        dp_hi3 = dp_hi.view(B, T, D)
+        dp_lo3 = dp_lo.view(B, T, D) if dp_lo is not None else None
+        for g in range(G):
+            wsl = slice(g * Cg, (g + 1) * Cg)
+            # A: [B, T, Cg] slice of dpre (row stride D); TMA needs 16-byte aligned base and strides
+            if (g * Cg) % 8 == 0 and D % 8 == 0:
+                a_k = ops.Operand(dp_hi3[:, :, g * Cg:], None if dp_lo3 is None else dp_lo3[:, :, g * Cg:], Cg, T, B, D, T * D)
+            else:
+                cpad = (Cg + 7) // 8 * 8
+                th = torch.zeros(B, T, cpad, dtype=torch.bfloat16, device=dev)
+                th[:, :, :Cg].copy_(dp_hi3[:, :, wsl])
+                tl = None
+                if dp_lo3 is not None:
+                    tl = torch.zeros(B, T, cpad, dtype=torch.bfloat16, device=dev)
+                    tl[:, :, :Cg].copy_(dp_lo3[:, :, wsl])
+                a_k = ops.Operand(th, tl, Cg, T, B, cpad, T * cpad)
+            # dgrad into the padded group-major input through the overlapping view
+            ops.gemm(a_k, ops.mnmajor(wg_hi[wsl], None if wg_lo is None else wg_lo[wsl]), m_per_batch=T, batches=B, n=K * CP,
+                     k=Cg, out_f32=dxg[g], a_batched=True, atomic=True, ldc=CP, c_batch_stride=Tpad * CP)
+            # wgrad: dwg[o, k*CP+i] = sum_{b,t} dpre[b,t,o] * xg[b, t+k, i]
+            uv = ops.unfold_view(st["xg_hi"][g], None if st["xg_lo"] is None else st["xg_lo"][g], K, 1, mn_major=True)
+            uv.d1 = T
+            ops.gemm(a_k.as_mn(), uv, m_per_batch=Cg, n=K * CP, k=T, out_f32=dwg[wsl], k_spans_batches=True, atomic=True,
+                     split_k=max(1, min(8, B)))
+        dg, dv = ops.posconv_weight_bwd(dwg, gk, v, norm)
+        k0 = q + "pos_conv_embed.conv.parametrizations.weight.original0"
+        if k0 in P:
+            G_[k0], G_[q + "pos_conv_embed.conv.parametrizations.weight.original1"] = dg, dv
+        else:
+            G_[q + "pos_conv_embed.conv.weight_g"], G_[q + "pos_conv_embed.conv.weight_v"] = dg, dv
+        dx = dsum.clone()
+        ops.posconv_unpack_dx(dxg, dx, B, T, G, st["pad"], Tpad)
+        return dx
+
+    def w2v_base_forward(self, P, feats: Tensor, B: int, T: int, training: bool, seed: int, skip_layers=()):
+        cfg = self.w2v
+        three = self.three
+        D, F, NH = cfg.hidden, cfg.ffn, cfg.heads
+        hd = D // NH
+        M = B * T
+        q = "w2v_encoder.wav2vec2.encoder."
+        tr = training
+        p_h = cfg.hidden_dropout if tr else 0.0
+        p_att = cfg.attention_dropout if tr else 0.0
+        p_act = cfg.activation_dropout if tr else 0.0
+        S: dict = {"B": B, "T": T, "layers": [], "skip": set(skip_layers)}
+        xs, S["posconv"] = self._posconv_forward(P, q, feats, B, T, training)
+        S["xs"] = xs
+        if not cfg.stable_ln:
+            h, h_hi, h_lo, mean, rstd = ops.layernorm_fwd(xs, P[q + "layer_norm.weight"], P[q + "layer_norm.bias"], cfg.ln_eps,
+                                                          three=three, drop_p=p_h, seed=_mix(seed, 200))
+            S["ln0"] = (mean, rstd)
+        else:
+            h, h_hi, h_lo = ops.dropout(xs, p_h, _mix(seed, 200), three=three, want_f32=True, want_split=False)
+        for i in range(cfg.layers):
+            if i in S["skip"]:
+                S["layers"].append(None)
+                continue
+            Lq = q + f"layers.{i}."
+            st: dict = {"seed": seed}
+            wqkv = self._w_cat(P, Lq + "qkv", [Lq + "attention.q_proj.weight", Lq + "attention.k_proj.weight",
+                                               Lq + "attention.v_proj.weight"])
+            bqkv = self._cat_vec(P, [Lq + "attention.q_proj.bias", Lq + "attention.k_proj.bias", Lq + "attention.v_proj.bias"])
+            if cfg.stable_ln:
+                _, a_hi, a_lo, m1, r1 = ops.layernorm_fwd(h, P[Lq + "layer_norm.weight"], P[Lq + "layer_norm.bias"], cfg.ln_eps,
+                                                          three=three, want_f32=False)
+                st.update(ln1=(m1, r1), ln1_in=h)
+            else:
+                a_hi, a_lo = h_hi, h_lo
+            st.update(in_hi=a_hi, in_lo=a_lo)
+            qkv, _, _, _ = self._linear_fwd(a_hi, a_lo, wqkv, bqkv, M, 3 * D, D)
+            _, c_hi, c_lo, probs = ops.attention_fwd(qkv, B, T, NH, hd, three=three, save_probs=training, drop_p=p_att,
+                                                     seed=_mix(seed, 1000 + 10 * i + 1))
+            st.update(qkv=qkv, probs=probs, c_hi=c_hi, c_lo=c_lo)
+            u, _, _, _ = self._linear_fwd(c_hi, c_lo, self._w(P, Lq + "attention.out_proj.weight"),
+                                          P[Lq + "attention.out_proj.bias"], M, D, D, residual=h, drop_p=p_h,
+                                          drop_seed=_mix(seed, 1000 + 10 * i + 2))
+            if cfg.stable_ln:
+                _, h1_hi, h1_lo, m2, r2 = ops.layernorm_fwd(u, P[Lq + "final_layer_norm.weight"], P[Lq + "final_layer_norm.bias"],
+                                                            cfg.ln_eps, three=three, want_f32=False)
+                res2 = u
+            else:
+                h1, h1_hi, h1_lo, m2, r2 = ops.layernorm_fwd(u, P[Lq + "layer_norm.weight"], P[Lq + "layer_norm.bias"],
+                                                             cfg.ln_eps, three=three)
+                res2 = h1
+            st.update(u=u, ln2=(m2, r2), h1_hi=h1_hi, h1_lo=h1_lo)
+            _, pre1, f_hi, f_lo = self._linear_fwd(h1_hi, h1_lo, self._w(P, Lq + "feed_forward.intermediate_dense.weight"),
+                                                   P[Lq + "feed_forward.intermediate_dense.bias"], M, F, D, want_f32=False,
+                                                   want_split=True, want_pre=training, act=cfg.hidden_act, drop_p=p_act,
+                                                   drop_seed=_mix(seed, 1000 + 10 * i + 3))
+            st.update(pre1=pre1, f_hi=f_hi, f_lo=f_lo)
+            u2, _, _, _ = self._linear_fwd(f_hi, f_lo, self._w(P, Lq + "feed_forward.output_dense.weight"),
+                                           P[Lq + "feed_forward.output_dense.bias"], M, D, F, residual=res2, drop_p=p_h,
+                                           drop_seed=_mix(seed, 1000 + 10 * i + 4))
+            if cfg.stable_ln:
+                h = u2
+            else:
+                h, h_hi, h_lo, m3, r3 = ops.layernorm_fwd(u2, P[Lq + "final_layer_norm.weight"],
+                                                          P[Lq + "final_layer_norm.bias"], cfg.ln_eps, three=three)
+                st.update(u2=u2, ln3=(m3, r3))
+            S["layers"].append(st)
+        if cfg.stable_ln:
+            hin = h
+            h, h_hi, h_lo, mf, rf = ops.layernorm_fwd(hin, P[q + "layer_norm.weight"], P[q + "layer_norm.bias"], cfg.ln_eps,
+                                                      three=three)
+            S["lnf"] = (mf, rf, hin)
+        S["p"] = (p_h, p_att, p_act)
+        S["seed"] = seed
+        return h, S
+
+    def w2v_base_backward(self, P, S: dict, dh: Tensor, G: Dict[str, Tensor]) -> Tensor:
+        """dh = gradient w.r.t. the encoder output [M, D]; returns the gradient w.r.t. feats."""
+        cfg = self.w2v
+        three = self.three
+        D, F, NH = cfg.hidden, cfg.ffn, cfg.heads
+        hd = D // NH
+        B, T = S["B"], S["T"]
+        M = B * T
+        dev = dh.device
+        q = "w2v_encoder.wav2vec2.encoder."
+        p_h, p_att, p_act = S["p"]
+        seed = S["seed"]
+
+        def zeros(n):
+            return torch.zeros(n, dtype=torch.float32, device=dev)
+
+        ds_ws = torch.empty(B, NH, T, T, dtype=torch.float32, device=dev)
+        if cfg.stable_ln:
+            mf, rf, hin = S["lnf"]
+            G[q + "layer_norm.weight"], G[q + "layer_norm.bias"] = zeros(D), zeros(D)
+            dh, _, _ = ops.layernorm_bwd(dh, hin, P[q + "layer_norm.weight"], mf, rf, G[q + "layer_norm.weight"],
+                                         G[q + "layer_norm.bias"], three=three, want_split=False)
+        for i in reversed(range(cfg.layers)):
+            st = S["layers"][i]
+            if st is None:
+                continue
+            Lq = q + f"layers.{i}."
+            s2, s3, s4, s1 = (_mix(seed, 1000 + 10 * i + k) for k in (2, 3, 4, 1))
+            # ---- FFN block ----
+            db2 = zeros(D)
+            if cfg.stable_ln:
+                # u2 = u + drop(FFN(LN(u)));  dh is d(u2)
+                du2 = dh
+                _, g_hi, g_lo = ops.dropout(du2, p_h, s4, three=three, want_f32=False, want_split=True)
+                ops.colsum(ops.dropout(du2, p_h, s4, three=three)[0] if p_h > 0 else du2, db2)
+            else:
+                m3, r3 = st["ln3"]
+                G[Lq + "final_layer_norm.weight"], G[Lq + "final_layer_norm.bias"] = zeros(D), zeros(D)
+                du2, g_hi, g_lo = ops.layernorm_bwd(dh, st["u2"], P[Lq + "final_layer_norm.weight"], m3, r3,
+                                                    G[Lq + "final_layer_norm.weight"], G[Lq + "final_layer_norm.bias"], db2,
+                                                    three=three, br_drop_p=p_h, br_seed=s4)
+            G[Lq + "feed_forward.output_dense.bias"] = db2
+            G[Lq + "feed_forward.output_dense.weight"] = self._wgrad(g_hi, g_lo, st["f_hi"], st["f_lo"], D, F, M)
+            db1 = zeros(F)
+            _, dp_hi, dp_lo = self._dgrad(g_hi, g_lo, self._w(P, Lq + "feed_forward.output_dense.weight"), M, D, F,
+                                          want_f32=False, want_split=True, aux=st["pre1"], aux_mode=cfg.hidden_act,
+                                          drop_p=p_act, drop_seed=s3, colsum=db1)
+            G[Lq + "feed_forward.intermediate_dense.bias"] = db1
+            G[Lq + "feed_forward.intermediate_dense.weight"] = self._wgrad(dp_hi, dp_lo, st["h1_hi"], st["h1_lo"], F, D, M)
+            w1 = self._w(P, Lq + "feed_forward.intermediate_dense.weight")
+            m2, r2 = st["ln2"]
+            dbo = zeros(D)
+            if cfg.stable_ln:
+                # d(LN2 out) -> LN2 backward on u, plus the residual du2
+                dl, _, _ = self._dgrad(dp_hi, dp_lo, w1, M, F, D)
+                G[Lq + "final_layer_norm.weight"], G[Lq + "final_layer_norm.bias"] = zeros(D), zeros(D)
+                dxl, _, _ = ops.layernorm_bwd(dl, st["u"], P[Lq + "final_layer_norm.weight"], m2, r2,
+                                              G[Lq + "final_layer_norm.weight"], G[Lq + "final_layer_norm.bias"], three=three,
+                                              want_split=False)
+                du = ops.axpby(dxl, du2)
+                _, b_hi, b_lo = ops.dropout(du, p_h, s2, three=three, want_f32=False, want_split=True)
+                ops.colsum(ops.dropout(du, p_h, s2, three=three)[0] if p_h > 0 else du, dbo)
+            else:
+                dh1, _, _ = self._dgrad(dp_hi, dp_lo, w1, M, F, D, residual=du2)
+                G[Lq + "layer_norm.weight"], G[Lq + "layer_norm.bias"] = zeros(D), zeros(D)
+                du, b_hi, b_lo = ops.layernorm_bwd(dh1, st["u"], P[Lq + "layer_norm.weight"], m2, r2, G[Lq + "layer_norm.weight"],
+                                                   G[Lq + "layer_norm.bias"], dbo, three=three, br_drop_p=p_h, br_seed=s2)
+            # ---- attention block ----
+            G[Lq + "attention.out_proj.bias"] = dbo
+            G[Lq + "attention.out_proj.weight"] = self._wgrad(b_hi, b_lo, st["c_hi"], st["c_lo"], D, D, M)
+            dctx, _, _ = self._dgrad(b_hi, b_lo, self._w(P, Lq + "attention.out_proj.weight"), M, D, D)
+            dqkv, dq_hi, dq_lo = ops.attention_bwd(st["qkv"], st["probs"], dctx, ds_ws, B, T, NH, hd, three=three,
+                                                   drop_p=p_att, seed=s1)
+            dbq = zeros(3 * D)
+            ops.colsum(dqkv, dbq)
+            dwq = self._wgrad(dq_hi, dq_lo, st["in_hi"], st["in_lo"], 3 * D, D, M)
+            for j, nm in enumerate(("q_proj", "k_proj", "v_proj")):
+                G[Lq + f"attention.{nm}.weight"] = dwq[j * D:(j + 1) * D]
+                G[Lq + f"attention.{nm}.bias"] = dbq[j * D:(j + 1) * D]
+            wqkv = self._w_cat(P, Lq + "qkv", [Lq + "attention.q_proj.weight", Lq + "attention.k_proj.weight",
+                                               Lq + "attention.v_proj.weight"])
+            if cfg.stable_ln:
+                dl, _, _ = self._dgrad(dq_hi, dq_lo, wqkv, M, 3 * D, D)
+                m1, r1 = st["ln1"]
+                G[Lq + "layer_norm.weight"], G[Lq + "layer_norm.bias"] = zeros(D), zeros(D)
+                dxl, _, _ = ops.layernorm_bwd(dl, st["ln1_in"], P[Lq + "layer_norm.weight"], m1, r1, G[Lq + "layer_norm.weight"],
+                                              G[Lq + "layer_norm.bias"], three=three, want_split=False)
+                dh = ops.axpby(dxl, du)
+            else:
+                dh, _, _ = self._dgrad(dq_hi, dq_lo, wqkv, M, 3 * D, D, residual=du)
+        # ---- encoder input: [LN ->] dropout, positional conv ----
+        if not cfg.stable_ln:
+            mean, rstd = S["ln0"]
+            G[q + "layer_norm.weight"], G[q + "layer_norm.bias"] = zeros(D), zeros(D)
+            dxs, _, _ = ops.layernorm_bwd(dh, S["xs"], P[q + "layer_norm.weight"], mean, rstd, G[q + "layer_norm.weight"],
+                                          G[q + "layer_norm.bias"], three=three, want_split=False, out_drop_p=p_h,
+                                          out_seed=_mix(seed, 200))
+        else:
+            dxs = ops.dropout(dh, p_h, _mix(seed, 200), three=three)[0] if p_h > 0 else dh
+        return self._posconv_backward(P, q, S["posconv"], dxs, B, T, G)
+
+    # ------------------------------------------------------------------------------------------
+    # lm_head + CTC     (w2v_custom_feat_extractor.py:149-152, 59, 81-90)
+    # ------------------------------------------------------------------------------------------
+    def head_forward(self, P, h: Tensor, B: int, T: int, training: bool, seed: int):
+        cfg = self.w2v
+        p_f = cfg.final_dropout if training else 0.0
+        hd, hd_hi, hd_lo = ops.dropout(h, p_f, _mix(seed, 300), three=self.three, want_f32=True, want_split=True)
+        logits, _, _, _ = self._linear_fwd(hd_hi, hd_lo, self._w(P, "w2v_encoder.lm_head.weight"),
+                                           P["w2v_encoder.lm_head.bias"], B * T, cfg.vocab, cfg.hidden, block_n=64)
+        return logits.view(B, T, cfg.vocab), hd, dict(hd_hi=hd_hi, hd_lo=hd_lo, p_f=p_f, seed=_mix(seed, 300), B=B, T=T)
+
+    def head_backward(self, P, S: dict, dlogits: Tensor, G: Dict[str, Tensor]) -> Tensor:
+        cfg = self.w2v
+        B, T = S["B"], S["T"]
+        M = B * T
+        d2 = dlogits.reshape(M, cfg.vocab)
+        _, d_hi, d_lo = ops.dropout(d2, 0.0, 0, three=self.three, want_f32=False, want_split=True)
+        db = torch.zeros(cfg.vocab, dtype=torch.float32, device=d2.device)
+        ops.colsum(d2, db)
+        G["w2v_encoder.lm_head.bias"] = db
+        G["w2v_encoder.lm_head.weight"] = self._wgrad(d_hi, d_lo, S["hd_hi"], S["hd_lo"], cfg.vocab, cfg.hidden, M)
+        dh, _, _ = self._dgrad(d_hi, d_lo, self._w(P, "w2v_encoder.lm_head.weight"), M, cfg.vocab, cfg.hidden,
+                               drop_p=S["p_f"], drop_seed=S["seed"])
+        return dh
+
+    # ------------------------------------------------------------------------------------------
+    # whole model
+    # ------------------------------------------------------------------------------------------
+    def processed_lens(self, input_lens: Tensor) -> Tensor:
+        """b2p2t_model.py:170-173: trunc((len - kernel) / stride) as int32."""
+        be = self.be
+        return ((input_lens - be.unfold_len) / be.unfold_stride).to(torch.int32)
+
+    def forward(self, P, x: Tensor, day: Tensor, training: bool, seed: int = 0, skip_layers=(), aug=(0.0, 0.0)):
+        """-> (logits [B,T',V], hidden [B,T',D], feats [B*T', D], saved)"""
+        feats, Sb = self.brain_forward(P, x, day, training, seed, aug)
+        B, Tp = Sb["B"], Sb["Tp"]
+        if self.w2v.kind == "base":
+            h, Se = self.w2v_base_forward(P, feats, B, Tp, training, seed, skip_layers)
+        else:
+            from . import conformer
+            h, Se = conformer.forward(self, P, feats, B, Tp, training, seed, skip_layers)
+        logits, hd, Sh = self.head_forward(P, h, B, Tp, training, seed)
+        return logits, hd.view(B, Tp, -1), feats, dict(brain=Sb, enc=Se, head=Sh)
+
+    def backward(self, P, saved: dict, dlogits: Tensor, dfeats_extra: Optional[Tensor] = None) -> Dict[str, Tensor]:
+        G: Dict[str, Tensor] = {}
+        dh = self.head_backward(P, saved["head"], dlogits, G)
+        if self.w2v.kind == "base":
+            dfeats = self.w2v_base_backward(P, saved["enc"], dh, G)
+        else:
+            from . import conformer
+            dfeats = conformer.backward(self, P, saved["enc"], dh, G)
+        if dfeats_extra is not None:
+            dfeats = ops.axpby(dfeats, dfeats_extra)
+        self.brain_backward(P, saved["brain"], dfeats, G)
+        return G

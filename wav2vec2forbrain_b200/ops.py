@@ -363,3 +363,58 @@ def greedy_decode(logits: Tensor):
                                   ptr(lens), c_int(B), c_int(T), c_int(V), stream()), "b2t_greedy_decode")
     _count()
     return am, ids, lens
+
+
+POSCONV_CP = 64   # channels per group after padding (one 128-byte swizzle row)
+
+
+def posconv_pack_input(x: Tensor, B: int, T: int, G: int, pad_left: int, Tp: int, three: bool = True):
+    """x [B*T, D] -> xg (hi, lo) [G, B, Tp, 64]."""
+    _lib.ensure_device()
+    D = x.shape[-1]
+    hi = torch.empty(G, B, Tp, POSCONV_CP, dtype=torch.bfloat16, device=x.device)
+    lo = torch.empty_like(hi) if three else None
+    check(lib().b2t_posconv_pack_input(ptr(x), ptr(hi), ptr(lo), c_int(B), c_int(T), c_int(D), c_int(G), c_int(pad_left),
+                                       c_int(Tp), stream()), "b2t_posconv_pack_input")
+    _count()
+    return hi, lo
+
+
+def posconv_pack_weight(g: Tensor, v: Tensor, G: int, three: bool = True):
+    """weight_norm(g [1,1,K], v [D,Cg,K]) -> (wg_hi, wg_lo [D, K*64], norm [K])."""
+    _lib.ensure_device()
+    D, Cg, K = v.shape
+    norm = torch.empty(K, dtype=torch.float32, device=v.device)
+    hi = torch.empty(D, K * POSCONV_CP, dtype=torch.bfloat16, device=v.device)
+    lo = torch.empty_like(hi) if three else None
+    check(lib().b2t_posconv_pack_weight(ptr(g), ptr(v), ptr(norm), ptr(hi), ptr(lo), c_int(D), c_int(Cg), c_int(K), c_int(G),
+                                        stream()), "b2t_posconv_pack_weight")
+    _count(2)
+    return hi, lo, norm
+
+
+def posconv_unpack_dx(dxg: Tensor, dx: Tensor, B: int, T: int, G: int, pad_left: int, Tp: int) -> None:
+    D = dx.shape[-1]
+    check(lib().b2t_posconv_unpack_dx(ptr(dxg), ptr(dx), c_int(B), c_int(T), c_int(D), c_int(G), c_int(pad_left), c_int(Tp),
+                                      stream()), "b2t_posconv_unpack_dx")
+    _count()
+
+
+def posconv_weight_bwd(dwg: Tensor, g: Tensor, v: Tensor, norm: Tensor):
+    D, Cg, K = v.shape
+    dg = torch.empty_like(g)
+    dv = torch.empty_like(v)
+    check(lib().b2t_posconv_weight_bwd(ptr(dwg), ptr(g), ptr(v), ptr(norm), ptr(dg), ptr(dv), c_int(D), c_int(Cg), c_int(K),
+                                       stream()), "b2t_posconv_weight_bwd")
+    _count()
+    return dg, dv
+
+
+def act_bwd(dy: Tensor, pre: Tensor, mode, three: bool = True, want_f32: bool = False, want_split: bool = True):
+    out = torch.empty_like(dy) if want_f32 else None
+    hi = _bf16_like(dy, want_split)
+    lo = _bf16_like(dy, want_split and three)
+    check(lib().b2t_act_bwd(ptr(dy), ptr(pre), ptr(out), ptr(hi), ptr(lo), c_int64(dy.numel()), c_int(ACT[mode]), stream()),
+          "b2t_act_bwd")
+    _count()
+    return out, hi, lo
