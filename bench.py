@@ -1,0 +1,356 @@
+#!/usr/bin/env python
+"""Benchmark of the b2p2t_gru+w2v training hot path (BASELINE.json metric: train trials/sec).
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--workload base|frozen|conformer]
+
+One "step" = the reference's per-batch training step (src/train/train_loop.py:44-78):
+optimizer.zero_grad -> model.forward(batch) -> loss.backward() -> [grad all-reduce] -> Adam.step,
+on one synthetic batch of the shape BASELINE.json names (256-ch features, T=500, 40-char targets).
+
+N=1 workload = BASELINE.json configs[1]: b2p2t_gru+w2v full fine-tuning, GRU 3x512 bidirectional +
+FC[256] + wav2vec2-base architecture (random init), batch 64.  N>1: same per-GPU batch (weak
+scaling), NCCL gradient all-reduce overlapped with backward.
+
+`--impl reference` times the reference's own CPU implementation of the same step (the oracle port,
+oracle/b2t_oracle.py — the reference is pure PyTorch and /root/reference does not exist on the GPU
+box) on the host cores, on a bounded sample (8 trials per step) of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import torch
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, REPO)
+
+T_FRAMES, S_TARGET, N_CH = 500, 40, 256
+
+# algorithmic forward GFLOP per trial at T=500; training = 3x forward
+GF_TRAIN = {"base": 91.18, "frozen": 69.50, "conformer": 440.66}
+
+
+def read_peaks():
+    path = os.path.join(REPO, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return {"hbm_gbs": p["hbm_gbs"], "bf16_tflops_sustained": p["bf16_tflops_sustained"], "source": "measured"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+
+
+def make_host_batch(B, seed=1234, pin=False):
+    g = torch.Generator().manual_seed(seed)
+    b = {
+        "input": torch.randn(B, T_FRAMES, N_CH, generator=g),
+        "day_idxs": torch.randint(0, 24, (B,), generator=g),
+        "target": torch.randint(4, 32, (B, S_TARGET), generator=g),
+        "input_lens": torch.full((B,), T_FRAMES, dtype=torch.long),
+        "target_lens": torch.full((B,), S_TARGET, dtype=torch.long),
+    }
+    if pin:
+        b = {k: v.pin_memory() for k, v in b.items()}
+    return b
+
+
+# ---------------------------------------------------------------------------------------------
+# reference arm / cpu baseline: the oracle port on the host cores
+# ---------------------------------------------------------------------------------------------
+def oracle_step_fn(workload: str, B: int):
+    from oracle import b2t_oracle as O
+    be = O.BrainEncoderCfg(out_size=1024 if workload == "conformer" else 768, dropout=0.45)
+    w2v = O.conformer_large_cfg() if workload == "conformer" else O.base_cfg()
+    w2v.hidden_dropout = w2v.attention_dropout = w2v.activation_dropout = w2v.final_dropout = 0.1
+    sd = O.make_state_dict(be, w2v, seed=42)
+    params = {k: (v.clone().requires_grad_(not O.is_buffer(k)) if v.is_floating_point() else v) for k, v in sd.items()}
+    brain = [v for k, v in params.items() if k.startswith("brain_encoder.") and v.requires_grad]
+    w2vp = [v for k, v in params.items() if k.startswith("w2v_encoder.") and v.requires_grad]
+    groups = [{"params": brain, "lr": 1e-4}]
+    if workload != "frozen":
+        groups.append({"params": w2vp, "lr": 1e-5})
+    opt = torch.optim.Adam(groups, weight_decay=1e-4)
+    batch = make_host_batch(B)
+
+    def step():
+        opt.zero_grad()
+        out = O.forward(batch, params, be, w2v, training=True, gru_impl="aten")
+        out.loss.backward()
+        opt.step()
+        return out.loss.item()
+    return step
+
+
+def time_oracle(workload: str, steps: int, warmup: int, B: int = 8):
+    torch.set_num_threads(os.cpu_count() or 1)
+    step = oracle_step_fn(workload, B)
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = time.perf_counter() - t0
+    return B * steps / dt, dt / steps * 1e3
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    B = 8
+    steps = max(1, min(args.steps, 20))
+    warmup = max(1, min(args.warmup, 3))
+    tps, ms = time_oracle(args.workload, steps, warmup, B)
+    cores = os.cpu_count() or 1
+    line = {
+        "impl": "reference", "metric": "train trials/sec", "value": tps, "unit": "trials/s", "n_gpus": args.gpus,
+        "steps": steps, "warmup": warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args.workload, args.gpus, 64 if args.workload != "conformer" else 32),
+        "cpu_baseline": {"value": tps, "unit": "trials/s", "cores": cores, "kind": "port",
+                         "sample": f"{steps} steps of {B} trials (T=500) of the same workload, torch CPU fp32, all host threads"},
+        "e2e": {"value": tps, "unit": "trials/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+
+
+def workload_config(workload: str, n_gpus: int, per_gpu_batch: int):
+    names = {
+        "base": "b2p2t_gru+w2v full fine-tuning, wav2vec2-base arch (BASELINE.json configs[1])",
+        "frozen": "b2p2t_gru+w2v frozen_w2v (BASELINE.json configs[2])",
+        "conformer": "b2p2t_gru+w2v_conformer, wav2vec2-conformer-rope-large arch (BASELINE.json configs[3]/[4])",
+    }
+    return {"workload": names[workload], "per_gpu_batch": per_gpu_batch, "global_batch": per_gpu_batch * n_gpus,
+            "T": T_FRAMES, "channels": N_CH, "target_len": S_TARGET, "gru": "3x512 bidirectional", "fc": [256],
+            "parallelism": f"dp{n_gpus}", "l2": "per-step working set (weights+activations, several GB) exceeds the 126 MB L2"}
+
+
+# ---------------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------------
+def build_model(workload: str, precision: str):
+    from wav2vec2forbrain_b200 import models
+    a = models.BrainEncoderArgs(encoder_gru_hidden_size=512, encoder_num_gru_layers=3, encoder_fc_hidden_sizes=(256,),
+                                gaussian_smooth_width=1.5, encoder_dropout=0.45)
+    torch.manual_seed(42)
+    if workload == "conformer":
+        ckpt = "facebook/wav2vec2-conformer-rope-large-960h-ft"
+        brain = models.bfe_w_preprocessing_from_config(a, None, ckpt, precision=precision)
+        model = models.W2VConformerBrainEncoderModel(brain, ckpt, precision=precision)
+    else:
+        ckpt = "facebook/wav2vec2-base-960h"
+        brain = models.bfe_w_preprocessing_from_config(a, None, ckpt, precision=precision)
+        model = models.W2VBrainEncoderModel(a, brain, ckpt, None, True, precision=precision)
+    model = model.cuda()
+    model.train()
+    brain_p = list(model.brain_encoder.parameters())
+    groups = [{"params": brain_p, "lr": 1e-4}]
+    if workload != "frozen":
+        groups.append({"params": list(model.w2v_encoder.parameters()), "lr": 1e-5})   # b2t_gru_w2v_experiment.py:111-145
+    opt = torch.optim.Adam(groups, weight_decay=1e-4, fused=True)
+    return model, opt
+
+
+def to_device_batch(models, hb, device):
+    b = models.B2tSampleBatch(hb["input"].to(device, non_blocking=True), hb["target"].to(device, non_blocking=True))
+    b.day_idxs = hb["day_idxs"].to(device, non_blocking=True)
+    b.input_lens = hb["input_lens"].to(device, non_blocking=True)
+    b.target_lens = hb["target_lens"].to(device, non_blocking=True)
+    return b
+
+
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                                       "-i", str(gpu_index)], stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        rows = []
+        with open(self.f.name) as fh:
+            for line in fh:
+                parts = [x.strip() for x in line.split(",")]
+                if len(parts) >= 9:
+                    rows.append(parts)
+        os.unlink(self.f.name)
+        if not rows:
+            return out
+        sm = sorted(float(r[1]) for r in rows if r[1].replace(".", "").isdigit())
+        if sm:
+            out["sm_mhz"] = sm[len(sm) // 2]
+        try:
+            out["sm_max_mhz"] = float(rows[0][2])
+        except ValueError:
+            pass
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for i, nm in enumerate(names):
+            if any(r[5 + i].lower().startswith("active") for r in rows):
+                out["reasons"].append(nm)
+        out["samples"] = len(rows)
+        return out
+
+
+def run_ours(args):
+    import torch.distributed as dist
+    from wav2vec2forbrain_b200 import dist as bdist, models, ops
+    rank, local_rank, world = bdist.env_rank_world()
+    multi = world > 1
+    if multi:
+        bdist.init_process_group("nccl")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    workload, precision = args.workload, args.precision
+    B = args.batch or (32 if workload == "conformer" else (128 if workload == "frozen" else 64))
+    model, opt = build_model(workload, precision)
+    dp = None
+    if multi:
+        dp = bdist.DataParallel(model)
+        dp.attach_optimizer(opt)
+    hb = make_host_batch(B, seed=1234 + rank, pin=True)
+    batch = to_device_batch(models, hb, dev)
+    torch.cuda.synchronize()
+
+    def step(bt):
+        opt.zero_grad(set_to_none=True)
+        out = model.forward(bt)
+        out.loss.backward()
+        opt.step()          # DP: pre-hook waits for the bucketed all-reduce
+        return out
+
+    def barrier():
+        if multi:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step(batch)
+    # ---- device-resident timing ----
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    l0 = ops.LAUNCHES
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step(batch)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = ops.LAUNCHES - l0
+    clocks = sampler.stop() if sampler else None
+    # ---- end-to-end timing: pinned host batch -> device every step, loss read back every step ----
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        bt = to_device_batch(models, hb, dev)
+        out = step(bt)
+        _ = out.loss.item()
+    barrier()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    h2d = sum(hb[k].numel() * hb[k].element_size() for k in ("input", "target", "day_idxs", "target_lens"))
+    t = torch.tensor([ms, e2e_ms], device=dev, dtype=torch.float64)
+    if multi:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = t.tolist()
+    if rank != 0:
+        return
+    tps = B * world * args.steps / (ms / 1e3)
+    e2e_tps = B * world * args.steps / (e2e_ms / 1e3)
+    peaks = read_peaks()
+    roof = gemm_roofline(model, opt, batch, step, peaks) if not args.no_roofline else None
+    line = {
+        "metric": "train trials/sec", "value": tps, "unit": "trials/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16x3 (3-term bf16 split operands, fp32 accumulate)" if precision == "bf16x3" else "bf16",
+        "data": "synthetic", "config": workload_config(workload, world, B),
+        "e2e": {"value": e2e_tps, "unit": "trials/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
+        "gpu_launches": launches, "clocks": clocks,
+        "step_roofline_frac": tps / world * GF_TRAIN[workload] / (peaks["bf16_tflops_sustained"] * 1e3),
+    }
+    if roof is not None:
+        line["roofline"] = roof
+    if world == 1 and not args.no_cpu_baseline:
+        v, _ = time_oracle(workload, steps=2, warmup=1, B=8)
+        line["cpu_baseline"] = {"value": v, "unit": "trials/s", "cores": os.cpu_count() or 1, "kind": "port",
+                                "sample": "2 steps of 8 trials (T=500) of the same workload, torch CPU fp32, all host threads"}
+    print(json.dumps(line))
+
+
+def gemm_roofline(model, opt, batch, step, peaks):
+    """CUDA-event time of every tcgen05 GEMM launch of one training step vs its algorithmic FLOPs."""
+    from wav2vec2forbrain_b200 import engine, ops
+    real = ops.gemm
+    rec = []
+
+    def timed_gemm(a, b, **kw):
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        real(a, b, **kw)
+        e.record()
+        k_eff = kw["k"] * (a.d2 if kw.get("k_spans_batches") else 1)
+        rec.append((s, e, 2.0 * kw["m_per_batch"] * kw.get("batches", 1) * kw["n"] * k_eff))
+    ops.gemm = timed_gemm
+    try:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        step(batch)
+        rec.clear()
+        e0.record()
+        step(batch)
+        e1.record()
+        torch.cuda.synchronize()
+    finally:
+        ops.gemm = real
+    t_ms = sum(s.elapsed_time(e) for s, e, _ in rec)
+    flops = sum(f for _, _, f in rec)
+    step_ms = e0.elapsed_time(e1)
+    achieved = flops / (t_ms * 1e-3) / 1e12
+    peak = peaks["bf16_tflops_sustained"]
+    return {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05/TMA, all launches of one step)", "achieved": achieved,
+            "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
+            "peak_source": peaks["source"] + " (sustained cuBLAS bf16)", "launches": len(rec), "gemm_ms_per_step": t_ms,
+            "gemm_share_of_step": t_ms / step_ms,
+            "note": "algorithmic FLOPs (2MNK); the bf16x3 mode issues 3 MMAs per algorithmic MAC"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=None, choices=["base", "frozen", "conformer"])
+    ap.add_argument("--precision", default="bf16x3", choices=["bf16x3", "bf16"])
+    ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.workload is None:
+        args.workload = "base"
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,131 @@
+"""Drop-in boundary: model classes with the reference's constructor/forward/state_dict contract, on the GPU."""
+import pytest
+import torch
+
+from tests.golden_util import golden_grad, load_case, rel_l2
+
+pytestmark = pytest.mark.gpu
+
+
+def build_from_golden(name):
+    from wav2vec2forbrain_b200 import models
+    from wav2vec2forbrain_b200.config import W2VConfig
+    rec, _, _, sd, batch = load_case(name)
+    be, w = rec["be"], rec["w2v"]
+    ck = "golden/" + name
+
+    def factory(**kw):
+        d = dict(kind=w["kind"], hidden=w["hidden"], layers=w["layers"], heads=w["heads"], ffn=w["ffn"], vocab=w["vocab"],
+                 pos_conv_k=w["pos_conv_k"], pos_conv_groups=w["pos_conv_groups"], dw_kernel=w["dw_kernel"],
+                 hidden_act="gelu" if w["kind"] == "base" else "swish", hidden_dropout=0.0, attention_dropout=0.0,
+                 activation_dropout=0.0, final_dropout=0.0, conv_dropout=0.0, layerdrop=0.0)
+        d.update(kw)
+        return W2VConfig(**d)
+    models.register_architecture(ck, factory, be["out_size"])
+    args = models.BrainEncoderArgs(encoder_gru_hidden_size=be["gru_hidden"], encoder_num_gru_layers=be["gru_layers"],
+                                   encoder_bidirectional=be["bidirectional"], encoder_fc_hidden_sizes=tuple(be["fc_hidden"]),
+                                   encoder_learnable_inital_state=be["learnable_h0"], gaussian_smooth_width=be["smooth_sigma"],
+                                   encoder_dropout=0.0, w2v_do_stable_layer_norm=w["stable_ln"])
+    brain = models.bfe_w_preprocessing_from_config(args, None, ck)
+    if w["kind"] == "base":
+        m = models.W2VBrainEncoderModel(args, brain, ck, None, True).cuda()
+    else:
+        m = models.W2VConformerBrainEncoderModel(brain, ck).cuda()
+    return m, rec, sd, batch, models
+
+
+def make_batch(models, batch):
+    b = models.B2tSampleBatch(batch["input"], batch["target"])
+    b.day_idxs, b.input_lens, b.target_lens = batch["day_idxs"], batch["input_lens"], batch["target_lens"]
+    return b.cuda()
+
+
+@pytest.mark.parametrize("name", ["tiny_base", "tiny_base_stable_ln", "tiny_base_h0_uni"])
+def test_state_dict_and_training_step(name):
+    m, rec, sd, batch, models = build_from_golden(name)
+    assert {k: tuple(v.shape) for k, v in m.state_dict().items()} == rec["state_dict_keys"]
+    res = m.load_state_dict(sd, strict=True)
+    assert not res.missing_keys and not res.unexpected_keys
+    m.train()
+    out = m.forward(make_batch(models, batch))
+    assert isinstance(out.metrics["ctc_loss"], float)
+    out.loss.backward()
+    assert rel_l2(out.logits.detach().cpu(), rec["logits_train"]) < 2e-4
+    assert abs(out.loss.item() - rec["loss_train"].item()) < 2e-4 * abs(rec["loss_train"].item())
+    assert torch.equal(out.logit_lens.cpu(), rec["logit_lens"])
+    got = {k: p.grad for k, p in m.named_parameters() if p.grad is not None}
+    assert sorted(k for k, p in m.named_parameters() if p.grad is None) == rec["params_without_grad"]
+    gmax = max(rec["grad_norm"].values())
+    for k in got:
+        ref, sl = golden_grad(rec, k)
+        err = (sl(got[k].cpu()).double() - ref.double()).norm().item()
+        assert err <= 1e-3 * ref.double().norm().item() + 1e-6 * gmax, k
+    # eval mode / no_grad path, greedy decode ids identical to the reference's argmax
+    m.eval()
+    with torch.no_grad():
+        ev = m.forward(make_batch(models, batch))
+    assert rel_l2(ev.logits.cpu(), rec["logits_eval"]) < 2e-4
+    assert torch.equal(ev.logits.argmax(-1).cpu().to(torch.int16), rec["argmax_eval"])
+    # sub-module calls used by the analysis helpers (latent_analysis_util.py:196-201)
+    with torch.no_grad():
+        enc = m.brain_encoder.forward(make_batch(models, batch))
+        lg, hid = m.w2v_encoder.forward(enc.logits)
+    assert rel_l2(enc.logits.cpu(), rec["features"]) < 2e-4
+    assert rel_l2(lg.cpu(), rec["logits_eval"]) < 2e-4
+
+
+def test_adam_step_moves_only_trained_parameters():
+    m, rec, sd, batch, models = build_from_golden("tiny_base")
+    m.load_state_dict(sd, strict=True)
+    before = {k: v.detach().clone() for k, v in m.named_parameters()}
+    opt = torch.optim.Adam([{"params": m.brain_encoder.parameters(), "lr": 1e-3},
+                            {"params": m.w2v_encoder.parameters(), "lr": 1e-4}], weight_decay=1e-4)
+    m.train()
+    for _ in range(2):
+        opt.zero_grad()
+        out = m.forward(make_batch(models, batch))
+        out.loss.backward()
+        torch.nn.utils.clip_grad_norm_(m.parameters(), 10.0)
+        opt.step()
+    moved = {k for k, v in m.named_parameters() if not torch.equal(v, before[k])}
+    assert moved == {k for k in before} - set(rec["params_without_grad"])
+
+
+def test_dropout_training_is_finite_and_seeded():
+    """train mode with the reference's dropout probabilities: masks differ per step, loss stays finite,
+    gradient check of the whole dropout-aware backward by a directional finite difference."""
+    from wav2vec2forbrain_b200 import engine, ops
+    from tests.engine_util import product_configs
+    from dataclasses import replace
+    rec, _, _, sd, batch = load_case("tiny_base")
+    be, w2v = product_configs(rec)
+    be = replace(be, dropout=0.3)
+    w2v = replace(w2v, hidden_dropout=0.1, attention_dropout=0.1, activation_dropout=0.1, final_dropout=0.1)
+    eng = engine.Engine(be, w2v, "bf16x3")
+    P = {k: v.cuda() for k, v in sd.items()}
+    x, day = batch["input"].cuda(), batch["day_idxs"].to("cuda", torch.int32)
+    lens = eng.processed_lens(batch["input_lens"]).cuda()
+    tg, tl = batch["target"].cuda(), batch["target_lens"].cuda()
+
+    def loss_at(Pd, seed):
+        logits, _, _, saved = eng.forward(Pd, x, day, True, seed)
+        loss, _, dl = ops.ctc_fwd_bwd(logits, tg, lens, tl)
+        return loss, saved, dl
+    l1, saved, dl = loss_at(P, 5)
+    l1b, _, _ = loss_at(P, 5)
+    l2, _, _ = loss_at(P, 6)
+    assert torch.isfinite(l1) and l1.item() == l1b.item() and l1.item() != l2.item()
+    G = eng.backward(P, saved, dl)
+    # directional derivative along the gradient of a few parameter tensors
+    keys = ["brain_encoder.day_weights", "brain_encoder.neural_decoder.encoder.gru.weight_hh_l0",
+            "w2v_encoder.wav2vec2.encoder.layers.0.feed_forward.intermediate_dense.weight",
+            "w2v_encoder.wav2vec2.encoder.layers.1.attention.q_proj.weight", "w2v_encoder.lm_head.weight"]
+    for k in keys:
+        g = G[k]
+        eps = 1e-2 / g.norm().item()
+        Pp, Pm = dict(P), dict(P)
+        Pp[k] = P[k] + eps * g
+        Pm[k] = P[k] - eps * g
+        fd = (loss_at(Pp, 5)[0].item() - loss_at(Pm, 5)[0].item()) / (2 * eps)
+        an = (g * g).sum().item()
+        assert abs(fd - an) < 0.05 * abs(an) + 1e-7, (k, fd, an)

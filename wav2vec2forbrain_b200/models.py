@@ -70,6 +70,38 @@ class B2TModel(nn.Module):
         raise NotImplementedError
 
 
+class _LazyMetrics(dict):
+    """`metrics` dict of ModelOutput whose float values are materialised (device->host sync) only
+    when somebody reads them.  The reference calls ctc_loss.item() inside forward
+    (w2v_custom_feat_extractor.py:94), a stream sync per step that readers who never look at the
+    metrics should not pay for; readers (evaluator.track_batch) see plain floats."""
+
+    def set_lazy(self, key, tensor):
+        dict.__setitem__(self, key, tensor)
+
+    def _mat(self, key):
+        v = dict.__getitem__(self, key)
+        if isinstance(v, Tensor):
+            v = v.item()
+            dict.__setitem__(self, key, v)
+        return v
+
+    def __getitem__(self, key):
+        return self._mat(key)
+
+    def get(self, key, default=None):
+        return self._mat(key) if key in self else default
+
+    def items(self):
+        return [(k, self._mat(k)) for k in list(self.keys())]
+
+    def values(self):
+        return [self._mat(k) for k in list(self.keys())]
+
+    def __repr__(self):
+        return repr(dict(self.items()))
+
+
 # ---------------------------------------------------------------------------------------------
 # shared runtime state: one Engine per top-level model, dropout / LayerDrop seeds
 # ---------------------------------------------------------------------------------------------
@@ -512,9 +544,9 @@ class _TopModel(B2TModel):
         if target_lens is not None and logit_lens is not None:
             ctc_loss = _CTCFn.apply(logits, targets.to(logits.device), logit_lens.to(logits.device),
                                     target_lens.to(logits.device))
-        metrics = {}
+        metrics = _LazyMetrics()
         if ctc_loss is not None:
-            metrics["ctc_loss"] = ctc_loss.item()
+            metrics.set_lazy("ctc_loss", ctc_loss.detach())
         return ModelOutput(logits, metrics, loss=ctc_loss, logit_lens=logit_lens if with_hidden else None,
                            hidden_states=hidden if with_hidden else None)
 
