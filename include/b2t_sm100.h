@@ -77,6 +77,9 @@ typedef struct {
     uint64_t drop_seed;
     /* bias row of batch b = bias + slot(b) * bias_batch_stride, slot = b_batch_idx[b] or b (0: shared) */
     int64_t  bias_batch_stride;
+    /* value is multiplied by out_scale after act / act'(aux) / dropout and before the residual
+     * (the conformer's half-step feed-forward, modeling_wav2vec2_conformer.py:602,625); 0 reads as 1 */
+    float    out_scale;
 } b2t_gemm_args;
 
 int b2t_gemm(const b2t_gemm_args* args, b2t_stream stream);

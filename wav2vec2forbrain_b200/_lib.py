@@ -40,6 +40,7 @@ class GemmArgs(ctypes.Structure):
         ("act", c_int32), ("aux_mode", c_int32), ("atomic", c_int32), ("split_k", c_int32),
         ("alpha", c_float), ("block_n", c_int32),
         ("drop_p", c_float), ("drop_seed", ctypes.c_uint64), ("bias_batch_stride", c_int64),
+        ("out_scale", c_float),
     ]
 
 

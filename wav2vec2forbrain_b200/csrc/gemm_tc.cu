@@ -11,9 +11,10 @@
 //   warp 1      allocates TMEM; one lane issues tcgen05.mma (M=128, N=BN, K=16) per k-step and
 //               term into a double-buffered fp32 accumulator in TMEM; tcgen05.commit releases
 //               smem slots ("empty" barriers) and publishes finished accumulators ("tmem_full")
-//   warps 2-5   epilogue: tcgen05.ld 32 lanes x 32 columns -> registers -> smem transpose so a
-//               warp touches 128 contiguous bytes of every output row -> fused bias /
-//               activation / act'(aux) / residual / column sums / bf16 hi-lo split / red.add
+//   warps 2-9   epilogue: tcgen05.ld 32 lanes x 32 columns -> registers; a thread owns one output
+//               row and 32 consecutive columns, so every global access is a 16-byte vector ->
+//               fused bias / activation / act'(aux) / dropout / residual / bf16 hi-lo split /
+//               red.add.v4 / column sums (shuffle transpose-reduce)
 // Operands may be K-major (row-major [rows, K]) or MN-major (row-major [K, rows]); both are
 // described as 3-D strided views so that (a) batches never share a tile row, (b) the GRU
 // layer-0 / pos-conv "unfold" is an overlapping-stride view instead of an im2col copy.
@@ -25,8 +26,8 @@ namespace {
 constexpr int BM = 128;
 constexpr int BK = 64;          // 64 bf16 = 128 B = one swizzle-128B row
 constexpr int UMMA_K = 16;
-constexpr int NUM_THREADS = 192;
-constexpr int EPI_STAGE_FLOATS = 32 * 33;
+constexpr int NUM_THREADS = 320;       // warp 0 TMA, warp 1 MMA, warps 2-9 epilogue
+constexpr int NUM_EPI_WARPS = 8;
 constexpr int SMEM_LIMIT = 227 * 1024;
 
 struct KParams {
@@ -45,7 +46,8 @@ struct KParams {
     float* colsum;
     int act, aux_mode, atomic, split_k;
     float alpha;
-    float drop_p, drop_scale;
+    float drop_p, drop_scale, out_scale;
+    int vec4;
     unsigned long long drop_seed;
     int m_tiles, n_tiles, total_items;
 };
@@ -140,7 +142,7 @@ struct Cfg {
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = (NTERMS == 3 ? 2 : 1) * (A_BYTES + B_BYTES);
-    static constexpr int EPI_BYTES = 4 * EPI_STAGE_FLOATS * 4;
+    static constexpr int EPI_BYTES = 0;      // the epilogue works from registers
     static constexpr int AUX_BYTES = 1024;   // barriers + tmem pointer
     static constexpr int STAGES_RAW = (SMEM_LIMIT - 1024 - EPI_BYTES - AUX_BYTES) / STAGE_BYTES;
     static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
@@ -165,6 +167,150 @@ __device__ __forceinline__ float apply_dact(float a, int mode) {
     return 1.0f;
 }
 
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+// Sum the 32 registers of every lane across the 32 lanes of the warp; lane j ends with the total
+// of register j (recursive halving: 31 shuffles instead of 32 x 5).
+__device__ __forceinline__ float warp_transpose_sum(float (&v)[32], int lane) {
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+        const bool upper = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < off; ++i) {
+            const float keep = upper ? v[i + off] : v[i];
+            const float send = upper ? v[i] : v[i + off];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        }
+    }
+    return v[0];
+}
+
+// Fused epilogue on 32 consecutive columns of one output row held in registers.
+// off0 = element offset of (row, col0) in the output layout; nvalid = columns of this chunk
+// inside N (a multiple of 4 on the VEC path).  VEC: every pointer / ldc is 16-byte friendly.
+template <bool VEC>
+__device__ __forceinline__ void epi_chunk(const KParams& p, float (&v)[32], long long off0, int col0, int nvalid,
+                                          bool row_ok, const float* bias_ptr, int lane) {
+    float res[32], aux[32];
+    if (row_ok) {
+        if (p.residual) {
+#pragma unroll
+            for (int g = 0; g < 8; ++g) {
+                if (g * 4 < nvalid) {
+                    if (VEC) {
+                        const float4 t = *reinterpret_cast<const float4*>(p.residual + off0 + g * 4);
+                        res[g * 4] = t.x, res[g * 4 + 1] = t.y, res[g * 4 + 2] = t.z, res[g * 4 + 3] = t.w;
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) res[g * 4 + e] = g * 4 + e < nvalid ? p.residual[off0 + g * 4 + e] : 0.0f;
+                    }
+                }
+            }
+        }
+        if (p.aux_mode) {
+#pragma unroll
+            for (int g = 0; g < 8; ++g) {
+                if (g * 4 < nvalid) {
+                    if (VEC) {
+                        const float4 t = *reinterpret_cast<const float4*>(p.aux + off0 + g * 4);
+                        aux[g * 4] = t.x, aux[g * 4 + 1] = t.y, aux[g * 4 + 2] = t.z, aux[g * 4 + 3] = t.w;
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) aux[g * 4 + e] = g * 4 + e < nvalid ? p.aux[off0 + g * 4 + e] : 0.0f;
+                    }
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int g = 0; g < 8; ++g) {
+        if (g * 4 >= nvalid || !row_ok) {   // outside the matrix: contributes nothing to column sums
+#pragma unroll
+            for (int e = 0; e < 4; ++e) v[g * 4 + e] = 0.0f;
+            continue;
+        }
+        float x[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const int j = g * 4 + e;
+            x[e] = v[j] * p.alpha + (bias_ptr && j < nvalid ? bias_ptr[col0 + j] : 0.0f);
+        }
+        if (p.out_pre) {
+            if (VEC) {
+                *reinterpret_cast<float4*>(p.out_pre + off0 + g * 4) = make_float4(x[0], x[1], x[2], x[3]);
+            } else {
+#pragma unroll
+                for (int e = 0; e < 4; ++e)
+                    if (g * 4 + e < nvalid) p.out_pre[off0 + g * 4 + e] = x[e];
+            }
+        }
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const int j = g * 4 + e;
+            float y = apply_act(x[e], p.act);
+            if (p.aux_mode) y *= apply_dact(aux[j], p.aux_mode);
+            if (p.drop_p > 0.0f)
+                y = hash_uniform(p.drop_seed, (unsigned long long)(off0 + j)) < p.drop_p ? 0.0f : y * p.drop_scale;
+            y *= p.out_scale;
+            if (p.residual) y += res[j];
+            x[e] = (VEC || j < nvalid) ? y : 0.0f;
+            v[j] = x[e];
+        }
+        if (p.out_f32) {
+            float* o = p.out_f32 + off0 + g * 4;
+            if (VEC) {
+                if (p.atomic)
+                    red_add_v4(o, x[0], x[1], x[2], x[3]);
+                else
+                    *reinterpret_cast<float4*>(o) = make_float4(x[0], x[1], x[2], x[3]);
+            } else {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    if (g * 4 + e < nvalid) {
+                        if (p.atomic)
+                            atomicAdd(o + e, x[e]);
+                        else
+                            o[e] = x[e];
+                    }
+                }
+            }
+        }
+        if (p.out_hi) {
+            bf16 h[4], l[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) split_bf16(x[e], h[e], l[e]);
+            if (VEC) {
+                __nv_bfloat162 a = __halves2bfloat162(h[0], h[1]), b = __halves2bfloat162(h[2], h[3]);
+                uint2 w;
+                w.x = *reinterpret_cast<uint32_t*>(&a);
+                w.y = *reinterpret_cast<uint32_t*>(&b);
+                *reinterpret_cast<uint2*>(p.out_hi + off0 + g * 4) = w;
+                if (p.out_lo) {
+                    a = __halves2bfloat162(l[0], l[1]);
+                    b = __halves2bfloat162(l[2], l[3]);
+                    w.x = *reinterpret_cast<uint32_t*>(&a);
+                    w.y = *reinterpret_cast<uint32_t*>(&b);
+                    *reinterpret_cast<uint2*>(p.out_lo + off0 + g * 4) = w;
+                }
+            } else {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    if (g * 4 + e < nvalid) {
+                        p.out_hi[off0 + g * 4 + e] = h[e];
+                        if (p.out_lo) p.out_lo[off0 + g * 4 + e] = l[e];
+                    }
+                }
+            }
+        }
+    }
+    if (p.colsum) {   // warp-uniform
+        const float s = warp_transpose_sum(v, lane);
+        if (lane < nvalid) atomicAdd(p.colsum + col0 + lane, s);
+    }
+}
+
 template <int NTERMS, bool A_MN, bool B_MN, int BN>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ CUtensorMap tmAl,
@@ -173,9 +319,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
-    const uint32_t epi_base = smem_base + C::STAGES * C::STAGE_BYTES;
-    float* epi_gen = reinterpret_cast<float*>(smem_gen + C::STAGES * C::STAGE_BYTES);
-    const uint32_t bar_base = epi_base + C::EPI_BYTES;
+    const uint32_t bar_base = smem_base + C::STAGES * C::STAGE_BYTES + C::EPI_BYTES;
     // barrier layout: full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2], then tmem ptr
     auto full_bar = [&](int s) { return bar_base + 8u * s; };
     auto empty_bar = [&](int s) { return bar_base + 8u * (C::STAGES + s); };
@@ -201,7 +345,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(tfull_bar(s), 1);
-            mbar_init(tempty_bar(s), 4);
+            mbar_init(tempty_bar(s), NUM_EPI_WARPS);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -330,8 +474,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
         }
     } else {
         // ================================ epilogue ====================================
-        const int q = warp & 3;   // TMEM lane quadrant this warp may read
-        float* stg = epi_gen + (warp - 2) * EPI_STAGE_FLOATS;
+        // 8 warps: TMEM lane quadrant q = warp & 3 (hardware restriction), the two warps of a
+        // quadrant take alternate 32-column chunks.  A thread owns ONE output row (its TMEM lane)
+        // and 32 consecutive columns of it: all global traffic is 16-byte vectors on that row.
+        const int q = warp & 3;
+        const int half = (warp - 2) >> 2;
         int local_iter = 0;
         for (int item = blockIdx.x; item < p.total_items; item += gridDim.x, ++local_iter) {
             int split, batch, m_blk, n_blk;
@@ -341,58 +488,30 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
             mbar_wait(tfull_bar(acc), acc_phase);
             tc_fence_after();
             const int cbatch = p.c_batch_idx ? p.c_batch_idx[batch] : batch;
-            const long long base_off = (long long)cbatch * p.c_batch_stride;
-            const int row0 = m_blk * BM + q * 32;
-            const bool use_bias = p.bias != nullptr && split == 0;
+            const int row = m_blk * BM + q * 32 + lane;
+            const bool row_ok = row < p.m_per_batch;
+            const long long row_off = (long long)cbatch * p.c_batch_stride + (long long)row * p.ldc;
             const int bslot = p.b_batch_idx ? p.b_batch_idx[batch] : (p.b_batched ? batch : 0);
-            const float* bias_ptr = p.bias ? p.bias + (long long)bslot * p.bias_batch_stride : nullptr;
+            const float* bias_ptr =
+                (p.bias != nullptr && split == 0) ? p.bias + (long long)bslot * p.bias_batch_stride : nullptr;
 #pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
+            for (int c = half; c < BN / 32; c += 2) {
                 float v[32];
                 const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + c * 32);
                 tmem_ld_32x32(taddr, v);
-                if (c == BN / 32 - 1) {
-                    // accumulator fully drained into registers: hand the TMEM stage back
+                if (c + 2 >= BN / 32) {
+                    // this warp's share of the accumulator is in registers: hand the TMEM stage back
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(tempty_bar(acc));
                 }
-                const int col = n_blk * BN + c * 32 + lane;
-                if (n_blk * BN + c * 32 >= p.n) continue;   // warp-uniform
-#pragma unroll
-                for (int j = 0; j < 32; ++j) stg[lane * 33 + j] = v[j];
-                __syncwarp();
-                const bool col_ok = col < p.n;
-                const float bias_v = (use_bias && col_ok) ? bias_ptr[col] : 0.0f;
-                float csum = 0.0f;
-#pragma unroll 4
-                for (int r = 0; r < 32; ++r) {
-                    const int row = row0 + r;
-                    if (row >= p.m_per_batch) break;   // warp-uniform
-                    if (!col_ok) continue;
-                    float x = stg[r * 33 + lane] * p.alpha + bias_v;
-                    const long long off = base_off + (long long)row * p.ldc + col;
-                    if (p.out_pre) p.out_pre[off] = x;
-                    x = apply_act(x, p.act);
-                    if (p.aux_mode) x *= apply_dact(p.aux[off], p.aux_mode);
-                    if (p.drop_p > 0.0f)
-                        x = hash_uniform(p.drop_seed, (unsigned long long)off) < p.drop_p ? 0.0f : x * p.drop_scale;
-                    if (p.residual) x += p.residual[off];
-                    csum += x;
-                    if (p.out_f32) {
-                        if (p.atomic)
-                            atomicAdd(p.out_f32 + off, x);
-                        else
-                            p.out_f32[off] = x;
-                    }
-                    if (p.out_hi) {
-                        const bf16 h = __float2bfloat16_rn(x);
-                        p.out_hi[off] = h;
-                        if (p.out_lo) p.out_lo[off] = __float2bfloat16_rn(x - __bfloat162float(h));
-                    }
-                }
-                if (p.colsum && col_ok) atomicAdd(p.colsum + col, csum);
-                __syncwarp();
+                const int col0 = n_blk * BN + c * 32;
+                if (col0 >= p.n) continue;   // warp-uniform
+                const int nvalid = p.n - col0 < 32 ? p.n - col0 : 32;
+                if (p.vec4)
+                    epi_chunk<true>(p, v, row_off + col0, col0, nvalid, row_ok, bias_ptr, lane);
+                else
+                    epi_chunk<false>(p, v, row_off + col0, col0, nvalid, row_ok, bias_ptr, lane);
             }
         }
     }
@@ -551,6 +670,13 @@ extern "C" int b2t_gemm(const b2t_gemm_args* a, b2t_stream stream_) {
     kp.drop_p = a->drop_p;
     kp.drop_scale = 1.0f / (1.0f - a->drop_p);
     kp.drop_seed = a->drop_seed;
+    kp.out_scale = a->out_scale == 0.0f ? 1.0f : a->out_scale;
+    {
+        auto al16 = [](const void* q) { return q == nullptr || ((uintptr_t)q & 15) == 0; };
+        auto al8 = [](const void* q) { return q == nullptr || ((uintptr_t)q & 7) == 0; };
+        kp.vec4 = (a->n % 4 == 0) && (a->ldc % 4 == 0) && (a->c_batch_stride % 4 == 0) && al16(a->out_f32) &&
+                  al16(a->out_pre) && al16(a->residual) && al16(a->aux) && al8(a->out_hi) && al8(a->out_lo);
+    }
 
     int bn = a->block_n;
     if (bn == 0) bn = a->n <= 64 ? 64 : 128;
