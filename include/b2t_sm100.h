@@ -117,6 +117,8 @@ int b2t_softsign_bwd(const float* ds, const float* z, const int32_t* day, void* 
  * fwd: y = LN(x)*gamma+beta [then inverted dropout(drop_p, seed)], saves mean / rstd.
  * bwd: dy may carry that output dropout; writes dx (fp32), the branch copy dx*mask(br_drop) as
  *      bf16 hi/lo (operand of the upstream GEMMs) and accumulates dgamma, dbeta, dcol (+=).
+ *      dres (optional, same shape) is added to dx first (fp32 and branch copies): the gradient
+ *      that reaches x over the residual connection around a pre-LN branch.
  * ------------------------------------------------------------------------------------- */
 int b2t_layernorm_fwd(const float* x, const float* gamma, const float* beta, float eps, float* y, void* y_hi,
                       void* y_lo, float* mean, float* rstd, int rows, int n, float drop_p, uint64_t seed,
@@ -124,7 +126,7 @@ int b2t_layernorm_fwd(const float* x, const float* gamma, const float* beta, flo
 int b2t_layernorm_bwd(const float* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
                       float* dx, void* dx_hi, void* dx_lo, float* dgamma, float* dbeta, float* dcol, int rows,
                       int n, float out_drop_p, uint64_t out_seed, float br_drop_p, uint64_t br_seed,
-                      b2t_stream stream);
+                      const float* dres, b2t_stream stream);
 /* y = dropout(x) with the library's counter-based mask; outputs fp32 and/or bf16 hi/lo (p=0: split) */
 int b2t_dropout(const float* x, float* y, void* hi, void* lo, int64_t n, float p, uint64_t seed, b2t_stream stream);
 /* out[c] += sum_r x[r*ld + c] */

@@ -195,7 +195,7 @@ def layernorm_fwd(x, gamma, beta, eps, three=True, want_f32=True, want_split=Tru
 
 
 def layernorm_bwd(dy, x, gamma, mean, rstd, dgamma, dbeta, dcol=None, three=True, want_f32=True, want_split=True,
-                  out_drop_p=0.0, out_seed=0, br_drop_p=0.0, br_seed=0):
+                  out_drop_p=0.0, out_seed=0, br_drop_p=0.0, br_seed=0, dres=None):
     offs = torch.arange(x.numel()).view_as(x)
     d = dy.double() * _keep(out_drop_p, out_seed, offs)
     xh = (x.double() - mean.double()[:, None]) * rstd.double()[:, None]
@@ -204,6 +204,8 @@ def layernorm_bwd(dy, x, gamma, mean, rstd, dgamma, dbeta, dcol=None, three=True
     g = d * gamma.double()
     n = x.shape[1]
     dx = rstd.double()[:, None] * (g - g.mean(-1, keepdim=True) - xh * (g * xh).mean(-1, keepdim=True))
+    if dres is not None:
+        dx = dx + dres.double()
     br = dx * _keep(br_drop_p, br_seed, offs)
     if dcol is not None:
         dcol += br.sum(0).float()
@@ -408,3 +410,120 @@ def act_bwd(dy, pre, mode, three=True, want_f32=False, want_split=True):
     v = (dy.double() * _dact(pre.double(), mode)).float()
     hi, lo = _split_t(v, three) if want_split else (None, None)
     return (v if want_f32 else None), hi, lo
+
+
+# ---------------------------------------------------------------------------------------------
+# conformer kernels
+# ---------------------------------------------------------------------------------------------
+def rope_table(inv_freq, T, head_dim):
+    global LAUNCHES
+    LAUNCHES += 1
+    f = torch.arange(T, dtype=torch.float32)[:, None] * inv_freq.float()[None, :]
+    emb = torch.cat((f, f), dim=-1)
+    return emb.cos(), emb.sin()
+
+
+def _rot_half(v, hd):
+    r, n = v.shape
+    u = v.view(r, n // hd, hd)
+    half = hd // 2
+    return torch.cat((-u[..., half:], u[..., :half]), dim=-1).reshape(r, n)
+
+
+def layernorm_rope_fwd(x, gamma, beta, eps, cos, sin, T, head_dim, three=True):
+    global LAUNCHES
+    LAUNCHES += 1
+    xd = x.double()
+    mean = xd.mean(-1)
+    var = ((xd - mean[:, None]) ** 2).mean(-1)
+    rstd = 1.0 / torch.sqrt(var + eps)
+    y = ((xd - mean[:, None]) * rstd[:, None] * gamma.double() + beta.double()).float()
+    rows, n = x.shape
+    t = torch.arange(rows) % T
+    c = cos.double()[t].repeat(1, n // head_dim)
+    s = sin.double()[t].repeat(1, n // head_dim)
+    rot = (y.double() * c + _rot_half(y.double(), head_dim) * s).float()
+    y_hi, y_lo = _split_t(y, three)
+    r_hi, r_lo = _split_t(rot, three)
+    return y_hi, y_lo, r_hi, r_lo, mean.float(), rstd.float()
+
+
+def rope_bwd_add(d_rot, d_plain, cos, sin, T, head_dim):
+    global LAUNCHES
+    LAUNCHES += 1
+    rows, n = d_rot.shape
+    t = torch.arange(rows) % T
+    c = cos.double()[t].repeat(1, n // head_dim)
+    s = sin.double()[t].repeat(1, n // head_dim)
+    d = d_rot.double()
+    ys = d * s
+    u = ys.view(rows, n // head_dim, head_dim)
+    half = head_dim // 2
+    rt = torch.cat((u[..., half:], -u[..., :half]), dim=-1).reshape(rows, n)
+    out = d * c + rt
+    if d_plain is not None:
+        out = out + d_plain.double()
+    return out.float()
+
+
+def _glu(g):
+    D = g.shape[1] // 2
+    return g[:, :D].double() * torch.sigmoid(g[:, D:].double())
+
+
+def glu_dwconv_fwd(g, w, B, T, want_stats=True):
+    global LAUNCHES
+    LAUNCHES += 1
+    D = g.shape[1] // 2
+    K = w.shape[-1]
+    s = _glu(g).view(B, T, D).transpose(1, 2)
+    out = F.conv1d(s, w.double().view(D, 1, K), None, padding=(K - 1) // 2, groups=D).transpose(1, 2).reshape(B * T, D)
+    stats = torch.stack([out.sum(0), (out * out).sum(0)]) if want_stats else None
+    return out.float(), stats
+
+
+def bn_silu_fwd(x, stats, gamma, beta, eps, momentum, running_mean, running_var, num_batches_tracked, training, three=True):
+    global LAUNCHES
+    LAUNCHES += 1
+    M, D = x.shape
+    if training:
+        mean = stats[0] / M
+        var = (stats[1] / M - mean * mean).clamp_min(0.0)
+        running_mean.mul_(1 - momentum).add_(momentum * mean.float())
+        running_var.mul_(1 - momentum).add_(momentum * (var * M / max(M - 1, 1)).float())
+        if num_batches_tracked is not None:
+            num_batches_tracked += 1
+    else:
+        mean, var = running_mean.double(), running_var.double()
+    rstd = 1.0 / torch.sqrt(var + eps)
+    y = F.silu((x.double() - mean) * rstd * gamma.double() + beta.double()).float()
+    hi, lo = _split_t(y, three)
+    return hi, lo, mean.float(), rstd.float()
+
+
+def bn_silu_bwd_stats(ds, x, mean, rstd, gamma, beta):
+    global LAUNCHES
+    LAUNCHES += 1
+    xh = (x.double() - mean.double()) * rstd.double()
+    dbn = ds.double() * _dact(xh * gamma.double() + beta.double(), "silu")
+    return (dbn * xh).sum(0).float(), dbn.sum(0).float()
+
+
+def glu_dwconv_bwd(ds, x, g, w, mean, rstd, gamma, beta, dgamma, dbeta, B, T, training, three=True):
+    global LAUNCHES
+    LAUNCHES += 1
+    M, D = x.shape
+    K = w.shape[-1]
+    xh = (x.double() - mean.double()) * rstd.double()
+    dbn = ds.double() * _dact(xh * gamma.double() + beta.double(), "silu")
+    if training:
+        dx = gamma.double() * rstd.double() * (dbn - dbeta.double() / M - xh * dgamma.double() / M)
+    else:
+        dx = gamma.double() * rstd.double() * dbn
+    gl = g.detach().double().requires_grad_(True)
+    wl = w.detach().double().view(D, 1, K).requires_grad_(True)
+    s = (gl[:, :D] * torch.sigmoid(gl[:, D:])).view(B, T, D).transpose(1, 2)
+    out = F.conv1d(s, wl, None, padding=(K - 1) // 2, groups=D).transpose(1, 2).reshape(M, D)
+    out.backward(dx)
+    hi, lo = _split_t(gl.grad.float(), three)
+    return hi, lo, wl.grad.float().view_as(w)

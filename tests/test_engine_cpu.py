@@ -15,7 +15,7 @@ def engine_mod(monkeypatch):
     return engine
 
 
-@pytest.mark.parametrize("name", ["tiny_base", "tiny_base_h0_uni", "tiny_base_stable_ln"])
+@pytest.mark.parametrize("name", ["tiny_base", "tiny_base_h0_uni", "tiny_base_stable_ln", "tiny_conformer"])
 def test_engine_schedule_matches_reference(engine_mod, name):
     rec, _, _, sd, batch = load_case(name)
     logits, loss, lens, G, feats, _, _ = run_engine_train_step(engine_mod, rec, sd, batch, "cpu")

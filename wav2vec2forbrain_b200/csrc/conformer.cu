@@ -1,0 +1,455 @@
+// Conformer-specific kernels of the wav2vec2-conformer (RoPE) encoder block
+// (transformers modeling_wav2vec2_conformer.py:568-631): everything of the block that is not a
+// GEMM, LayerNorm or attention call.
+//
+//   R1  LayerNorm + rotary embedding in one pass (:466-471,509-527): the layer-normed state is
+//       written twice as bf16 hi/lo GEMM operands — rotated (A operand of the Q/K projection)
+//       and plain (A operand of the V projection) — without an fp32 round trip.
+//   V1  convolution module (:398-417) between the two pointwise GEMMs:
+//       GLU -> depthwise conv (k=31, pad 15) -> BatchNorm1d (train: batch statistics over all
+//       B*T' frames) -> SiLU, forward and backward.  HBM-bound: one CTA = one trial x 32
+//       channels x a time tile staged in shared memory with its halo.
+#include "common.cuh"
+#include "../../include/b2t_sm100.h"
+
+namespace {
+
+constexpr int DW_MAX_K = 33;     // depthwise kernel length supported (31 on the path)
+constexpr int DW_TT = 128;       // output frames per time tile
+constexpr int DW_CH = 32;        // channels per CTA (= warp width, lane = channel)
+constexpr int DW_ROWS = DW_TT + DW_MAX_K - 1;
+
+// cos/sin tables of Wav2Vec2ConformerRotaryPositionalEmbedding (:125-156): emb = cat(f, f), f = t * inv_freq
+__global__ void rope_table_kernel(const float* __restrict__ inv_freq, float* __restrict__ cos_t, float* __restrict__ sin_t,
+                                  int T, int half) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= T * half) return;
+    const int t = i / half, j = i - t * half;
+    const float f = (float)t * inv_freq[j];
+    const float c = cosf(f), s = sinf(f);
+    cos_t[t * 2 * half + j] = c;
+    cos_t[t * 2 * half + half + j] = c;
+    sin_t[t * 2 * half + j] = s;
+    sin_t[t * 2 * half + half + j] = s;
+}
+
+// one warp per row; the normalised row is parked in shared memory so that the rotary partner
+// (p +- hd/2 inside the head) can be read back whatever the head size
+template <int MAXP>
+__global__ void __launch_bounds__(256) ln_rope_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                                                          const float* __restrict__ beta, float eps,
+                                                          bf16* __restrict__ y_hi, bf16* __restrict__ y_lo,
+                                                          bf16* __restrict__ r_hi, bf16* __restrict__ r_lo,
+                                                          float* __restrict__ mean_out, float* __restrict__ rstd_out,
+                                                          const float* __restrict__ cos_t, const float* __restrict__ sin_t,
+                                                          int rows, int n, int T, int hd) {
+    extern __shared__ float srow[];   // [warps][n]
+    const int lane = threadIdx.x & 31;
+    const int wib = threadIdx.x >> 5;
+    float* buf = srow + (size_t)wib * n;
+    const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int nwarps = (gridDim.x * blockDim.x) >> 5;
+    const float inv_n = 1.0f / (float)n;
+    const int half = hd >> 1;
+    for (int row = warp_global; row < rows; row += nwarps) {
+        const float* xr = x + (long)row * n;
+        float v[MAXP];
+        float s = 0.0f;
+#pragma unroll
+        for (int i = 0; i < MAXP; ++i) {
+            const int c = lane + 32 * i;
+            v[i] = c < n ? xr[c] : 0.0f;
+            s += v[i];
+        }
+        const float mean = warp_sum(s) * inv_n;
+        float q = 0.0f;
+#pragma unroll
+        for (int i = 0; i < MAXP; ++i) {
+            const int c = lane + 32 * i;
+            const float d = c < n ? v[i] - mean : 0.0f;
+            q += d * d;
+        }
+        const float rstd = rsqrtf(warp_sum(q) * inv_n + eps);
+        if (lane == 0) {
+            mean_out[row] = mean;
+            rstd_out[row] = rstd;
+        }
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < MAXP; ++i) {
+            const int c = lane + 32 * i;
+            if (c < n) {
+                v[i] = (v[i] - mean) * rstd * gamma[c] + beta[c];
+                buf[c] = v[i];
+            }
+        }
+        __syncwarp();
+        const int t = row % T;
+#pragma unroll
+        for (int i = 0; i < MAXP; ++i) {
+            const int c = lane + 32 * i;
+            if (c < n) {
+                const long off = (long)row * n + c;
+                bf16 h, l;
+                split_bf16(v[i], h, l);
+                y_hi[off] = h;
+                if (y_lo) y_lo[off] = l;
+                const int p = c % hd;
+                const float rot = p < half ? -buf[c + half] : buf[c - half];
+                const float o = v[i] * cos_t[t * hd + p] + rot * sin_t[t * hd + p];
+                split_bf16(o, h, l);
+                r_hi[off] = h;
+                if (r_lo) r_lo[off] = l;
+            }
+        }
+        __syncwarp();
+    }
+}
+
+// du = d_rot * cos + R^T(d_rot * sin) + d_plain,  R^T(y)[p] = y[p + half] (p < half), -y[p - half] (p >= half)
+__global__ void rope_bwd_add_kernel(const float* __restrict__ d_rot, long ld_rot, const float* __restrict__ d_plain,
+                                    long ld_plain, float* __restrict__ out, const float* __restrict__ cos_t,
+                                    const float* __restrict__ sin_t, long rows, int n, int T, int hd) {
+    const int half = hd >> 1;
+    const long total = rows * n;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const long row = i / n;
+        const int c = (int)(i - row * n);
+        const int t = (int)(row % T);
+        const int p = c % hd;
+        const float* dr = d_rot + row * ld_rot;
+        const float* cs = cos_t + (long)t * hd;
+        const float* sn = sin_t + (long)t * hd;
+        float o = dr[c] * cs[p];
+        o += p < half ? dr[c + half] * sn[p + half] : -dr[c - half] * sn[p - half];
+        if (d_plain) o += d_plain[row * ld_plain + c];
+        out[i] = o;
+    }
+}
+
+__device__ __forceinline__ float sigmoid_acc(float x) { return 1.0f / (1.0f + expf(-x)); }
+__device__ __forceinline__ float silu_acc(float x) { return x * sigmoid_acc(x); }
+__device__ __forceinline__ float silu_acc_grad(float x) {
+    const float s = sigmoid_acc(x);
+    return s * (1.0f + x * (1.0f - s));
+}
+
+// GLU + depthwise conv forward + per-channel sum / sum of squares (BatchNorm batch statistics).
+// g [B*T, 2D] (pointwise_conv1 output: value | gate), w [D, K], out [B*T, D].
+// grid (ceil(D/32), B, ceil(T/DW_TT)), 256 threads: lane = channel, warp = frame phase.
+__global__ void __launch_bounds__(256) glu_dwconv_fwd_kernel(const float* __restrict__ g, const float* __restrict__ w,
+                                                             float* __restrict__ out, double* __restrict__ ssum,
+                                                             double* __restrict__ ssq, int T, int D, int K) {
+    __shared__ float s[DW_ROWS][DW_CH];
+    __shared__ float sw[DW_MAX_K][DW_CH];
+    __shared__ float red[2][8][DW_CH];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int c = blockIdx.x * DW_CH + lane;
+    const int b = blockIdx.y;
+    const int t0 = blockIdx.z * DW_TT;
+    const int pad = (K - 1) / 2;
+    const bool c_ok = c < D;
+    for (int k = warp; k < K; k += 8) sw[k][lane] = c_ok ? w[(long)c * K + k] : 0.0f;
+    const int nrows = DW_TT + K - 1;
+    for (int r = warp; r < nrows; r += 8) {
+        const int t = t0 - pad + r;
+        float v = 0.0f;
+        if (c_ok && t >= 0 && t < T) {
+            const float* gr = g + ((long)b * T + t) * 2 * D;
+            v = gr[c] * sigmoid_acc(gr[D + c]);
+        }
+        s[r][lane] = v;
+    }
+    __syncthreads();
+    float sum = 0.0f, sq = 0.0f;
+    for (int r = warp; r < DW_TT && t0 + r < T; r += 8) {
+        float acc = 0.0f;
+        for (int k = 0; k < K; ++k) acc = fmaf(sw[k][lane], s[r + k][lane], acc);
+        if (c_ok) out[((long)b * T + t0 + r) * D + c] = acc;
+        sum += acc;
+        sq += acc * acc;
+    }
+    if (ssum) {
+        red[0][warp][lane] = sum;
+        red[1][warp][lane] = sq;
+        __syncthreads();
+        if (warp == 0 && c_ok) {
+            double a = 0.0, q = 0.0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                a += (double)red[0][j][lane];
+                q += (double)red[1][j][lane];
+            }
+            atomicAdd(ssum + c, a);
+            atomicAdd(ssq + c, q);
+        }
+    }
+}
+
+// BatchNorm1d (train: batch statistics, running-stat update; eval: running statistics) + SiLU,
+// output as bf16 hi/lo operand of pointwise_conv2.  thread = channel, block rows [by*RPB, ...).
+constexpr int BN_RPB = 32;
+__global__ void __launch_bounds__(128) bn_silu_fwd_kernel(const float* __restrict__ x, const double* __restrict__ ssum,
+                                                          const double* __restrict__ ssq, const float* __restrict__ gamma,
+                                                          const float* __restrict__ beta, float eps, float momentum,
+                                                          float* __restrict__ running_mean, float* __restrict__ running_var,
+                                                          long long* __restrict__ nbt, float* __restrict__ mean_out,
+                                                          float* __restrict__ rstd_out, bf16* __restrict__ y_hi,
+                                                          bf16* __restrict__ y_lo, long M, int D, int training) {
+    const int c = blockIdx.x * 128 + threadIdx.x;
+    if (c >= D) return;
+    float mean, rstd;
+    if (training) {
+        const double m = ssum[c] / (double)M;
+        double var = ssq[c] / (double)M - m * m;
+        var = var < 0.0 ? 0.0 : var;
+        mean = (float)m;
+        rstd = (float)(1.0 / sqrt(var + (double)eps));
+        if (blockIdx.y == 0) {
+            const double unb = M > 1 ? var * (double)M / (double)(M - 1) : var;
+            running_mean[c] = (1.0f - momentum) * running_mean[c] + momentum * mean;
+            running_var[c] = (1.0f - momentum) * running_var[c] + momentum * (float)unb;
+            if (c == 0 && nbt) *nbt += 1;
+        }
+    } else {
+        mean = running_mean[c];
+        rstd = 1.0f / sqrtf(running_var[c] + eps);
+    }
+    if (blockIdx.y == 0) {
+        mean_out[c] = mean;
+        rstd_out[c] = rstd;
+    }
+    const float ga = gamma[c] * rstd, be = beta[c] - mean * gamma[c] * rstd;
+    const long r0 = (long)blockIdx.y * BN_RPB;
+    const long r1 = r0 + BN_RPB < M ? r0 + BN_RPB : M;
+    for (long r = r0; r < r1; ++r) {
+        const long off = r * D + c;
+        const float y = silu_acc(fmaf(x[off], ga, be));
+        bf16 h, l;
+        split_bf16(y, h, l);
+        y_hi[off] = h;
+        if (y_lo) y_lo[off] = l;
+    }
+}
+
+// backward, pass 1: dbn = ds * silu'(bn(x));  dbeta[c] += sum dbn,  dgamma[c] += sum dbn * xhat
+__global__ void __launch_bounds__(128) bn_silu_bwd_stats_kernel(const float* __restrict__ ds, const float* __restrict__ x,
+                                                                const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                                const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                                float* __restrict__ dgamma, float* __restrict__ dbeta, long M,
+                                                                int D) {
+    const int c = blockIdx.x * 128 + threadIdx.x;
+    if (c >= D) return;
+    const float mu = mean[c], rs = rstd[c], ga = gamma[c], be = beta[c];
+    const long r0 = (long)blockIdx.y * BN_RPB;
+    const long r1 = r0 + BN_RPB < M ? r0 + BN_RPB : M;
+    float sb = 0.0f, sg = 0.0f;
+    for (long r = r0; r < r1; ++r) {
+        const long off = r * D + c;
+        const float xh = (x[off] - mu) * rs;
+        const float dbn = ds[off] * silu_acc_grad(fmaf(xh, ga, be));
+        sb += dbn;
+        sg += dbn * xh;
+    }
+    atomicAdd(dbeta + c, sb);
+    atomicAdd(dgamma + c, sg);
+}
+
+// backward, pass 2 (fused): BatchNorm+SiLU backward -> depthwise-conv backward (input and weight
+// gradients) -> GLU backward, written as the bf16 hi/lo operand dg [B*T, 2D] of the
+// pointwise_conv1 wgrad / dgrad GEMMs.  Same tiling as the forward kernel.
+__global__ void __launch_bounds__(256) glu_dwconv_bwd_kernel(const float* __restrict__ ds, const float* __restrict__ x,
+                                                             const float* __restrict__ g, const float* __restrict__ w,
+                                                             const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                             const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                             const float* __restrict__ dgamma, const float* __restrict__ dbeta,
+                                                             bf16* __restrict__ dg_hi, bf16* __restrict__ dg_lo,
+                                                             float* __restrict__ dw, int T, int D, int K, long M,
+                                                             int training) {
+    extern __shared__ float dyn[];
+    float (*dd)[DW_CH] = reinterpret_cast<float (*)[DW_CH]>(dyn);                       // d(dwconv out), with halo
+    float (*s)[DW_CH] = reinterpret_cast<float (*)[DW_CH]>(dyn + DW_ROWS * DW_CH);      // glu, with halo
+    float (*sw)[DW_CH] = reinterpret_cast<float (*)[DW_CH]>(dyn + 2 * DW_ROWS * DW_CH);
+    float (*acc_w)[DW_CH] = reinterpret_cast<float (*)[DW_CH]>(dyn + (2 * DW_ROWS + DW_MAX_K) * DW_CH);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int c = blockIdx.x * DW_CH + lane;
+    const int b = blockIdx.y;
+    const int t0 = blockIdx.z * DW_TT;
+    const int pad = (K - 1) / 2;
+    const bool c_ok = c < D;
+    for (int k = warp; k < K; k += 8) {
+        sw[k][lane] = c_ok ? w[(long)c * K + k] : 0.0f;
+        acc_w[k][lane] = 0.0f;
+    }
+    float mu = 0.0f, rs = 0.0f, ga = 0.0f, be = 0.0f, mdb = 0.0f, mdg = 0.0f;
+    if (c_ok) {
+        mu = mean[c], rs = rstd[c], ga = gamma[c], be = beta[c];
+        if (training) {
+            mdb = dbeta[c] / (float)M;
+            mdg = dgamma[c] / (float)M;
+        }
+    }
+    // rows r <-> frame t = t0 - (K-1-pad) + r for dd (needs [t - (K-1-pad), t + pad]) ; keep one
+    // common origin t0 - pad' with pad' = K - 1 - pad... for odd K pad' == pad.
+    const int nrows = DW_TT + K - 1;
+    for (int r = warp; r < nrows; r += 8) {
+        const int t = t0 - pad + r;
+        float dv = 0.0f, sv = 0.0f;
+        if (c_ok && t >= 0 && t < T) {
+            const long row = (long)b * T + t;
+            const float xh = (x[row * D + c] - mu) * rs;
+            const float dbn = ds[row * D + c] * silu_acc_grad(fmaf(xh, ga, be));
+            dv = ga * rs * (dbn - mdb - xh * mdg);
+            const float* gr = g + row * 2 * D;
+            sv = gr[c] * sigmoid_acc(gr[D + c]);
+        }
+        dd[r][lane] = dv;
+        s[r][lane] = sv;
+    }
+    __syncthreads();
+    // out[t] = sum_k w[k] s[t + k - pad]  =>  d s[u] = sum_k w[k] d out[u - k + pad]
+    //                                        d w[k] = sum_t d out[t] s[t + k - pad]
+    float wacc[DW_MAX_K];
+#pragma unroll
+    for (int k = 0; k < DW_MAX_K; ++k) wacc[k] = 0.0f;
+    for (int r = warp; r < DW_TT && t0 + r < T; r += 8) {
+        // frame t = t0 + r sits at smem row r + pad
+        float dsv = 0.0f;
+        const float dout = dd[r + pad][lane];
+#pragma unroll
+        for (int k = 0; k < DW_MAX_K; ++k) {
+            if (k < K) {
+                dsv = fmaf(sw[k][lane], dd[r + 2 * pad - k][lane], dsv);
+                wacc[k] = fmaf(dout, s[r + k][lane], wacc[k]);
+            }
+        }
+        if (c_ok) {
+            const long row = (long)b * T + t0 + r;
+            const float* gr = g + row * 2 * D;
+            const float a = gr[c], sg = sigmoid_acc(gr[D + c]);
+            const float da = dsv * sg, dgate = dsv * a * sg * (1.0f - sg);
+            bf16 h, l;
+            split_bf16(da, h, l);
+            dg_hi[row * 2 * D + c] = h;
+            if (dg_lo) dg_lo[row * 2 * D + c] = l;
+            split_bf16(dgate, h, l);
+            dg_hi[row * 2 * D + D + c] = h;
+            if (dg_lo) dg_lo[row * 2 * D + D + c] = l;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < DW_MAX_K; ++k)
+        if (k < K) atomicAdd(&acc_w[k][lane], wacc[k]);
+    __syncthreads();
+    if (c_ok)
+        for (int k = warp; k < K; k += 8) atomicAdd(dw + (long)c * K + k, acc_w[k][lane]);
+}
+
+constexpr size_t DW_BWD_SMEM = (size_t)(2 * DW_ROWS + 2 * DW_MAX_K) * DW_CH * sizeof(float);
+
+inline int grid_for(long n, int block, int cap_mult = 16) {
+    long g = (n + block - 1) / block;
+    const long cap = 148L * cap_mult;
+    return (int)(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+}  // namespace
+
+extern "C" int b2t_rope_table(const float* inv_freq, float* cos_t, float* sin_t, int T, int head_dim, b2t_stream stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    B2T_CHECK_ARG(inv_freq && cos_t && sin_t && T > 0 && head_dim > 0 && head_dim % 2 == 0, "b2t_rope_table: bad arguments");
+    const int half = head_dim / 2;
+    rope_table_kernel<<<(T * half + 127) / 128, 128, 0, stream>>>(inv_freq, cos_t, sin_t, T, half);
+    B2T_CHECK_LAUNCH("b2t_rope_table");
+    return 0;
+}
+
+extern "C" int b2t_layernorm_rope_fwd(const float* x, const float* gamma, const float* beta, float eps, void* y_hi, void* y_lo,
+                                      void* r_hi, void* r_lo, float* mean, float* rstd, const float* cos_t,
+                                      const float* sin_t, int rows, int n, int T, int head_dim, b2t_stream stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    B2T_CHECK_ARG(x && gamma && beta && y_hi && r_hi && mean && rstd && cos_t && sin_t, "b2t_layernorm_rope_fwd: null argument");
+    B2T_CHECK_ARG(rows > 0 && n > 0 && n <= 1024 && T > 0 && rows % T == 0, "b2t_layernorm_rope_fwd: bad sizes rows=%d n=%d T=%d",
+                  rows, n, T);
+    B2T_CHECK_ARG(head_dim > 0 && head_dim % 2 == 0 && n % head_dim == 0, "b2t_layernorm_rope_fwd: head_dim %d must be even and divide n", head_dim);
+    B2T_CHECK_ARG((y_lo == nullptr) == (r_lo == nullptr), "b2t_layernorm_rope_fwd: y_lo / r_lo must both be set or both NULL");
+    const int grid = grid_for((long)rows * 32, 256, 8);
+    const size_t smem = 8 * (size_t)n * sizeof(float);
+    const int per = (n + 31) / 32;
+#define CALL(P)                                                                                                         \
+    ln_rope_fwd_kernel<P><<<grid, 256, smem, stream>>>(x, gamma, beta, eps, (bf16*)y_hi, (bf16*)y_lo, (bf16*)r_hi, (bf16*)r_lo, \
+                                                       mean, rstd, cos_t, sin_t, rows, n, T, head_dim)
+    if (per <= 2) { CALL(2); } else if (per <= 8) { CALL(8); } else if (per <= 24) { CALL(24); } else { CALL(32); }
+#undef CALL
+    B2T_CHECK_LAUNCH("b2t_layernorm_rope_fwd");
+    return 0;
+}
+
+extern "C" int b2t_rope_bwd_add(const float* d_rot, int64_t ld_rot, const float* d_plain, int64_t ld_plain, float* out,
+                                const float* cos_t, const float* sin_t, int64_t rows, int n, int T, int head_dim,
+                                b2t_stream stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    B2T_CHECK_ARG(d_rot && out && cos_t && sin_t && rows > 0 && n > 0 && T > 0 && head_dim % 2 == 0 && n % head_dim == 0,
+                  "b2t_rope_bwd_add: bad arguments");
+    rope_bwd_add_kernel<<<grid_for(rows * n, 256), 256, 0, stream>>>(d_rot, ld_rot, d_plain, ld_plain, out, cos_t, sin_t, rows, n,
+                                                                    T, head_dim);
+    B2T_CHECK_LAUNCH("b2t_rope_bwd_add");
+    return 0;
+}
+
+extern "C" int b2t_glu_dwconv_fwd(const float* g, const float* w, float* out, double* stats, int B, int T, int D, int K,
+                                  b2t_stream stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    B2T_CHECK_ARG(g && w && out && B > 0 && T > 0 && D > 0, "b2t_glu_dwconv_fwd: bad arguments");
+    B2T_CHECK_ARG(K > 0 && K <= DW_MAX_K && K % 2 == 1, "b2t_glu_dwconv_fwd: depthwise kernel %d must be odd and <= %d", K, DW_MAX_K);
+    dim3 grid((D + DW_CH - 1) / DW_CH, B, (T + DW_TT - 1) / DW_TT);
+    glu_dwconv_fwd_kernel<<<grid, 256, 0, stream>>>(g, w, out, stats, stats ? stats + D : nullptr, T, D, K);
+    B2T_CHECK_LAUNCH("b2t_glu_dwconv_fwd");
+    return 0;
+}
+
+extern "C" int b2t_bn_silu_fwd(const float* x, const double* stats, const float* gamma, const float* beta, float eps,
+                               float momentum, float* running_mean, float* running_var, int64_t* num_batches_tracked,
+                               float* mean_out, float* rstd_out, void* y_hi, void* y_lo, int64_t M, int D, int training,
+                               b2t_stream stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    B2T_CHECK_ARG(x && gamma && beta && running_mean && running_var && mean_out && rstd_out && y_hi && M > 0 && D > 0,
+                  "b2t_bn_silu_fwd: bad arguments");
+    B2T_CHECK_ARG(!training || stats, "b2t_bn_silu_fwd: training mode needs the batch statistics buffer");
+    dim3 grid((D + 127) / 128, (unsigned)((M + BN_RPB - 1) / BN_RPB));
+    bn_silu_fwd_kernel<<<grid, 128, 0, stream>>>(x, stats, stats ? stats + D : nullptr, gamma, beta, eps, momentum, running_mean,
+                                                 running_var, (long long*)num_batches_tracked, mean_out, rstd_out, (bf16*)y_hi,
+                                                 (bf16*)y_lo, M, D, training);
+    B2T_CHECK_LAUNCH("b2t_bn_silu_fwd");
+    return 0;
+}
+
+extern "C" int b2t_bn_silu_bwd_stats(const float* ds, const float* x, const float* mean, const float* rstd, const float* gamma,
+                                     const float* beta, float* dgamma, float* dbeta, int64_t M, int D, b2t_stream stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    B2T_CHECK_ARG(ds && x && mean && rstd && gamma && beta && dgamma && dbeta && M > 0 && D > 0, "b2t_bn_silu_bwd_stats: bad arguments");
+    dim3 grid((D + 127) / 128, (unsigned)((M + BN_RPB - 1) / BN_RPB));
+    bn_silu_bwd_stats_kernel<<<grid, 128, 0, stream>>>(ds, x, mean, rstd, gamma, beta, dgamma, dbeta, M, D);
+    B2T_CHECK_LAUNCH("b2t_bn_silu_bwd_stats");
+    return 0;
+}
+
+extern "C" int b2t_glu_dwconv_bwd(const float* ds, const float* x, const float* g, const float* w, const float* mean,
+                                  const float* rstd, const float* gamma, const float* beta, const float* dgamma,
+                                  const float* dbeta, void* dg_hi, void* dg_lo, float* dw, int B, int T, int D, int K,
+                                  int training, b2t_stream stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    B2T_CHECK_ARG(ds && x && g && w && mean && rstd && gamma && beta && dgamma && dbeta && dg_hi && dw && B > 0 && T > 0 && D > 0,
+                  "b2t_glu_dwconv_bwd: bad arguments");
+    B2T_CHECK_ARG(K > 0 && K <= DW_MAX_K && K % 2 == 1, "b2t_glu_dwconv_bwd: depthwise kernel %d must be odd and <= %d", K, DW_MAX_K);
+    static bool attr_set = false;
+    if (!attr_set) {
+        B2T_CUDA(cudaFuncSetAttribute(glu_dwconv_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DW_BWD_SMEM));
+        attr_set = true;
+    }
+    dim3 grid((D + DW_CH - 1) / DW_CH, B, (T + DW_TT - 1) / DW_TT);
+    glu_dwconv_bwd_kernel<<<grid, 256, DW_BWD_SMEM, stream>>>(ds, x, g, w, mean, rstd, gamma, beta, dgamma, dbeta, (bf16*)dg_hi,
+                                                             (bf16*)dg_lo, dw, T, D, K, (long)B * T, training);
+    B2T_CHECK_LAUNCH("b2t_glu_dwconv_bwd");
+    return 0;
+}

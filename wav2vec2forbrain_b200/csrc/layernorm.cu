@@ -72,7 +72,7 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ d
                                                      float* __restrict__ dgamma, float* __restrict__ dbeta,
                                                      float* __restrict__ dcol, int rows, int n, float out_drop_p,
                                                      unsigned long long out_seed, float br_drop_p,
-                                                     unsigned long long br_seed) {
+                                                     unsigned long long br_seed, const float* __restrict__ dres) {
     extern __shared__ float sacc[];   // [3][n]
     for (int i = threadIdx.x; i < 3 * n; i += blockDim.x) sacc[i] = 0.0f;
     __syncthreads();
@@ -113,7 +113,8 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ d
             const int c = lane + 32 * i;
             if (c < n) {
                 const long off = (long)row * n + c;
-                const float o = rstd * (g[i] - s1 - xh[i] * s2);
+                float o = rstd * (g[i] - s1 - xh[i] * s2);
+                if (dres) o += dres[off];   // + gradient arriving over the residual path around a pre-LN branch
                 if (dx) dx[off] = o;
                 if (dx_hi || dcol) {
                     float ob = o;
@@ -227,7 +228,7 @@ extern "C" int b2t_layernorm_fwd(const float* x, const float* gamma, const float
 extern "C" int b2t_layernorm_bwd(const float* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
                                  float* dx, void* dx_hi, void* dx_lo, float* dgamma, float* dbeta, float* dcol, int rows,
                                  int n, float out_drop_p, uint64_t out_seed, float br_drop_p, uint64_t br_seed,
-                                 b2t_stream stream_) {
+                                 const float* dres, b2t_stream stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     B2T_CHECK_ARG(dy && x && gamma && mean && rstd && rows > 0 && n > 0 && n <= 1024, "b2t_layernorm_bwd: bad arguments");
     const int grid = grid_for((long)rows * 32, 256, 2);
@@ -235,7 +236,7 @@ extern "C" int b2t_layernorm_bwd(const float* dy, const float* x, const float* g
 #define CALL(P)                                                                                                       \
     ln_bwd_kernel<P><<<grid, 256, smem, stream>>>(dy, x, gamma, mean, rstd, dx, (bf16*)dx_hi, (bf16*)dx_lo, dgamma, dbeta, \
                                                   dcol, rows, n, out_drop_p, (unsigned long long)out_seed, br_drop_p,  \
-                                                  (unsigned long long)br_seed)
+                                                  (unsigned long long)br_seed, dres)
     LN_DISPATCH(n, CALL);
 #undef CALL
     B2T_CHECK_LAUNCH("b2t_layernorm_bwd");

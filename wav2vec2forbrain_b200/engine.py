@@ -121,14 +121,14 @@ class Engine:
                  out_hi=hi, out_lo=lo, bias=bias, **kw)
         return out, pre, hi, lo
 
-    def _wgrad(self, dy_hi, dy_lo, x_hi, x_lo, N, K, M, out: Optional[Tensor] = None) -> Tensor:
+    def _wgrad(self, dy_hi, dy_lo, x_hi, x_lo, N, K, M, out: Optional[Tensor] = None, alpha: float = 1.0) -> Tensor:
         """dW[N,K] = dY[M,N]^T . X[M,K]  (both operands row-major, contracted over rows)."""
         kb = (M + 63) // 64
         sk = _split_k_for(N, K, kb)
         if out is None:
             out = (torch.zeros if sk > 1 else torch.empty)(N, K, dtype=torch.float32, device=dy_hi.device)
         ops.gemm(ops.mnmajor(dy_hi, dy_lo), ops.mnmajor(x_hi, x_lo), m_per_batch=N, n=K, k=M, out_f32=out,
-                 atomic=sk > 1, split_k=sk)
+                 atomic=sk > 1, split_k=sk, alpha=alpha)
         return out
 
     def _dgrad(self, dy_hi, dy_lo, w_hl, M, N, K, **kw):

@@ -207,7 +207,8 @@ def layernorm_fwd(x: Tensor, gamma: Tensor, beta: Tensor, eps: float, three: boo
 
 def layernorm_bwd(dy: Tensor, x: Tensor, gamma: Tensor, mean: Tensor, rstd: Tensor, dgamma: Tensor, dbeta: Tensor,
                   dcol: Optional[Tensor] = None, three: bool = True, want_f32: bool = True, want_split: bool = True,
-                  out_drop_p: float = 0.0, out_seed: int = 0, br_drop_p: float = 0.0, br_seed: int = 0):
+                  out_drop_p: float = 0.0, out_seed: int = 0, br_drop_p: float = 0.0, br_seed: int = 0,
+                  dres: Optional[Tensor] = None):
     """-> (dx | None, dx_hi | None, dx_lo | None); dgamma/dbeta/dcol are accumulated into."""
     rows, n = x.shape
     dx = torch.empty_like(x) if want_f32 else None
@@ -215,7 +216,7 @@ def layernorm_bwd(dy: Tensor, x: Tensor, gamma: Tensor, mean: Tensor, rstd: Tens
     lo = _bf16_like(x, want_split and three)
     check(lib().b2t_layernorm_bwd(ptr(dy), ptr(x), ptr(gamma), ptr(mean), ptr(rstd), ptr(dx), ptr(hi), ptr(lo),
                                   ptr(dgamma), ptr(dbeta), ptr(dcol), c_int(rows), c_int(n), c_float(out_drop_p),
-                                  c_uint64(out_seed), c_float(br_drop_p), c_uint64(br_seed), stream()),
+                                  c_uint64(out_seed), c_float(br_drop_p), c_uint64(br_seed), ptr(dres), stream()),
           "b2t_layernorm_bwd")
     _count()
     return dx, hi, lo
@@ -419,3 +420,97 @@ def act_bwd(dy: Tensor, pre: Tensor, mode, three: bool = True, want_f32: bool = 
           "b2t_act_bwd")
     _count()
     return out, hi, lo
+
+
+# ---------------------------------------------------------------------------------------------
+# conformer kernels (csrc/conformer.cu)
+# ---------------------------------------------------------------------------------------------
+def rope_table(inv_freq: Tensor, T: int, head_dim: int):
+    """-> (cos, sin) [T, head_dim] of Wav2Vec2ConformerRotaryPositionalEmbedding."""
+    _lib.ensure_device()
+    cos = torch.empty(T, head_dim, dtype=torch.float32, device=inv_freq.device)
+    sin = torch.empty_like(cos)
+    check(lib().b2t_rope_table(ptr(inv_freq), ptr(cos), ptr(sin), c_int(T), c_int(head_dim), stream()), "b2t_rope_table")
+    _count()
+    return cos, sin
+
+
+def layernorm_rope_fwd(x: Tensor, gamma: Tensor, beta: Tensor, eps: float, cos: Tensor, sin: Tensor, T: int, head_dim: int,
+                       three: bool = True):
+    """x [rows, n] -> (y_hi, y_lo, rot_hi, rot_lo, mean, rstd): LayerNorm output plain and rotated."""
+    _lib.ensure_device()
+    rows, n = x.shape
+    y_hi, y_lo = _bf16_like(x), _bf16_like(x, three)
+    r_hi, r_lo = _bf16_like(x), _bf16_like(x, three)
+    mean = torch.empty(rows, dtype=torch.float32, device=x.device)
+    rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
+    check(lib().b2t_layernorm_rope_fwd(ptr(x), ptr(gamma), ptr(beta), c_float(eps), ptr(y_hi), ptr(y_lo), ptr(r_hi), ptr(r_lo),
+                                       ptr(mean), ptr(rstd), ptr(cos), ptr(sin), c_int(rows), c_int(n), c_int(T),
+                                       c_int(head_dim), stream()), "b2t_layernorm_rope_fwd")
+    _count()
+    return y_hi, y_lo, r_hi, r_lo, mean, rstd
+
+
+def rope_bwd_add(d_rot: Tensor, d_plain: Optional[Tensor], cos: Tensor, sin: Tensor, T: int, head_dim: int) -> Tensor:
+    """gradient w.r.t. the un-rotated state: R^T d_rot (+ d_plain).  Inputs may be column slices (row stride != n)."""
+    rows, n = d_rot.shape
+    assert d_rot.stride(1) == 1 and (d_plain is None or d_plain.stride(1) == 1)
+    out = torch.empty(rows, n, dtype=torch.float32, device=d_rot.device)
+    check(lib().b2t_rope_bwd_add(ptr(d_rot), c_int64(d_rot.stride(0)), ptr(d_plain),
+                                 c_int64(0 if d_plain is None else d_plain.stride(0)), ptr(out), ptr(cos), ptr(sin),
+                                 c_int64(rows), c_int(n), c_int(T), c_int(head_dim), stream()), "b2t_rope_bwd_add")
+    _count()
+    return out
+
+
+def glu_dwconv_fwd(g: Tensor, w: Tensor, B: int, T: int, want_stats: bool = True):
+    """g [B*T, 2D] (value | gate), w [D, 1, K] -> (out [B*T, D], stats [2, D] float64 (sum, sum of squares) | None)."""
+    _lib.ensure_device()
+    D = g.shape[1] // 2
+    K = w.shape[-1]
+    out = torch.empty(B * T, D, dtype=torch.float32, device=g.device)
+    stats = torch.zeros(2, D, dtype=torch.float64, device=g.device) if want_stats else None
+    check(lib().b2t_glu_dwconv_fwd(ptr(g), ptr(w), ptr(out), ptr(stats), c_int(B), c_int(T), c_int(D), c_int(K), stream()),
+          "b2t_glu_dwconv_fwd")
+    _count()
+    return out, stats
+
+
+def bn_silu_fwd(x: Tensor, stats: Optional[Tensor], gamma: Tensor, beta: Tensor, eps: float, momentum: float,
+                running_mean: Tensor, running_var: Tensor, num_batches_tracked: Optional[Tensor], training: bool,
+                three: bool = True):
+    """BatchNorm1d + SiLU.  -> (y_hi, y_lo, mean [D], rstd [D]); running statistics are updated in place when training."""
+    M, D = x.shape
+    y_hi, y_lo = _bf16_like(x), _bf16_like(x, three)
+    mean = torch.empty(D, dtype=torch.float32, device=x.device)
+    rstd = torch.empty(D, dtype=torch.float32, device=x.device)
+    check(lib().b2t_bn_silu_fwd(ptr(x), ptr(stats), ptr(gamma), ptr(beta), c_float(eps), c_float(momentum), ptr(running_mean),
+                                ptr(running_var), ptr(num_batches_tracked), ptr(mean), ptr(rstd), ptr(y_hi), ptr(y_lo),
+                                c_int64(M), c_int(D), c_int(1 if training else 0), stream()), "b2t_bn_silu_fwd")
+    _count()
+    return y_hi, y_lo, mean, rstd
+
+
+def bn_silu_bwd_stats(ds: Tensor, x: Tensor, mean: Tensor, rstd: Tensor, gamma: Tensor, beta: Tensor):
+    """-> (dgamma [D], dbeta [D]) of BatchNorm behind the SiLU."""
+    M, D = x.shape
+    dgamma = torch.zeros(D, dtype=torch.float32, device=x.device)
+    dbeta = torch.zeros(D, dtype=torch.float32, device=x.device)
+    check(lib().b2t_bn_silu_bwd_stats(ptr(ds), ptr(x), ptr(mean), ptr(rstd), ptr(gamma), ptr(beta), ptr(dgamma), ptr(dbeta),
+                                      c_int64(M), c_int(D), stream()), "b2t_bn_silu_bwd_stats")
+    _count()
+    return dgamma, dbeta
+
+
+def glu_dwconv_bwd(ds: Tensor, x: Tensor, g: Tensor, w: Tensor, mean: Tensor, rstd: Tensor, gamma: Tensor, beta: Tensor,
+                   dgamma: Tensor, dbeta: Tensor, B: int, T: int, training: bool, three: bool = True):
+    """-> (dg_hi, dg_lo [B*T, 2D], dw [D, 1, K]): gradient w.r.t. the pointwise_conv1 output and the depthwise weight."""
+    D = x.shape[1]
+    K = w.shape[-1]
+    dg_hi, dg_lo = _bf16_like(g), _bf16_like(g, three)
+    dw = torch.zeros_like(w)
+    check(lib().b2t_glu_dwconv_bwd(ptr(ds), ptr(x), ptr(g), ptr(w), ptr(mean), ptr(rstd), ptr(gamma), ptr(beta), ptr(dgamma),
+                                   ptr(dbeta), ptr(dg_hi), ptr(dg_lo), ptr(dw), c_int(B), c_int(T), c_int(D), c_int(K),
+                                   c_int(1 if training else 0), stream()), "b2t_glu_dwconv_bwd")
+    _count()
+    return dg_hi, dg_lo, dw
