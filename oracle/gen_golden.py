@@ -131,6 +131,9 @@ def run_case(name, be, w2v, B, T, S, ragged, full_tensors, seed_w=42, seed_x=123
         # a deterministic sample of every gradient (first 32 + strided 32 entries)
         rec["grad_sample"] = {k: torch.cat([v.flatten()[:32], v.flatten()[::max(1, v.numel() // 32)][:32]]).clone()
                               for k, v in grads.items()}
+        # a wider strided sample: the 64-entry sample is too noisy an estimate of a tensor's rel-L2 error
+        # once that error sits within 2x of the tolerance (conformer-large, 24 layers of bf16x3 GEMMs)
+        rec["grad_sample_512"] = {k: v.flatten()[::max(1, v.numel() // 512)][:512].clone() for k, v in grads.items()}
     if w2v.kind == "conformer":
         rec["bn_running_mean_l0"] = m.state_dict()[
             "w2v_encoder.wav2vec2_conformer.encoder.layers.0.conv_module.batch_norm.running_mean"].clone()

@@ -1,0 +1,48 @@
+"""Times b2t_gemm on the GEMM shapes of the conformer-large / base steps (CUDA events, L2 flushed between
+iterations by cycling through operand copies larger than the 126 MB L2)."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from wav2vec2forbrain_b200 import ops
+
+def bench(name, m, n, k, three, a_mn=False, b_mn=False, split_k=1, bn=0, iters=20, out="f32"):
+    dev = "cuda"
+    ncopy = max(2, int(200e6 // ((m * k + n * k) * 2 * (2 if three else 1))) + 1)
+    A = [torch.randn((k, m) if a_mn else (m, k), device=dev) for _ in range(ncopy)]
+    B = [torch.randn((k, n) if b_mn else (n, k), device=dev) for _ in range(ncopy)]
+    As = [ops.split(a, three) for a in A]
+    Bs = [ops.split(b, three) for b in B]
+    del A, B
+    o = torch.zeros(m, n, device=dev)
+    hi = torch.empty(m, n, device=dev, dtype=torch.bfloat16) if out == "split" else None
+    lo = torch.empty(m, n, device=dev, dtype=torch.bfloat16) if (out == "split" and three) else None
+    def run(i):
+        a, b = As[i % ncopy], Bs[i % ncopy]
+        oa = ops.mnmajor(*a) if a_mn else ops.kmajor(*a)
+        ob = ops.mnmajor(*b) if b_mn else ops.kmajor(*b)
+        ops.gemm(oa, ob, m_per_batch=m, n=n, k=k, out_f32=o if out == "f32" or split_k > 1 else None, out_hi=hi, out_lo=lo,
+                 atomic=split_k > 1, split_k=split_k, block_n=bn)
+    for i in range(3): run(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(iters): run(i)
+    e1.record(); torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) / iters * 1e3
+    tf = 2.0 * m * n * k / us / 1e6
+    print(f"{name:34s} m={m:5d} n={n:5d} k={k:5d} terms={'3' if three else '1'} bn={bn or 'auto':>4} splitk={split_k:2d}  {us:8.1f} us  "
+          f"{tf:7.1f} TF/s alg  {tf * (3 if three else 1):7.1f} TF/s mma", flush=True)
+
+if __name__ == "__main__":
+    M = 3776
+    for three in (True, False):
+        for bn in (128, 256):
+            bench("ffn1 fwd (N=4096,K=1024)", M, 4096, 1024, three, bn=bn)
+            bench("ffn2 fwd (N=1024,K=4096)", M, 1024, 4096, three, bn=bn)
+            bench("qk proj (N=2048,K=1024)", M, 2048, 1024, three, bn=bn)
+            bench("ffn1 fwd split out", M, 4096, 1024, three, bn=bn, out="split")
+            bench("dgrad ffn2 (B mn-major)", M, 4096, 1024, three, b_mn=True, bn=bn)
+            bench("wgrad ffn1 (both mn-major)", 4096, 1024, M, three, a_mn=True, b_mn=True, bn=bn)
+            bench("wgrad 1024x1024 splitk", 1024, 1024, M, three, a_mn=True, b_mn=True, split_k=2, bn=bn)
+        bench("big square 8192^3", 8192, 8192, 8192, three, bn=128, iters=5)
+        bench("big square 8192^3", 8192, 8192, 8192, three, bn=256, iters=5)

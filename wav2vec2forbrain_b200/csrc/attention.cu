@@ -199,11 +199,24 @@ size_t attn_smem(int T, int d) { return ((size_t)2 * T * (d + 1) + ATT_WARPS * 6
 
 }  // namespace
 
+// single-tile tensor-core kernels (attention_mma.cu)
+int b2t_attn_mma_supported(int T, int d, long ld, long ld_ctx, int q_off, int k_off, int v_off);
+int b2t_attn_mma_fwd(const float* qkv, long ld, int q_off, int k_off, int v_off, const int* kv_lens, float* probs, float* ctx,
+                     void* ctx_hi, void* ctx_lo, long ld_ctx, int B, int T, int H, int d, float scale, float drop_p,
+                     unsigned long long seed, cudaStream_t stream);
+int b2t_attn_mma_bwd(const float* qkv, long ld, int q_off, int k_off, int v_off, const float* probs, const float* dctx,
+                     long ld_ctx, float* dqkv, void* dqkv_hi, void* dqkv_lo, int B, int T, int H, int d, float scale,
+                     float drop_p, unsigned long long seed, cudaStream_t stream);
+
 extern "C" int b2t_attention_fwd(const float* qkv, int64_t ld, int q_off, int k_off, int v_off, const int32_t* kv_lens,
                                  float* probs, float* ctx, void* ctx_hi, void* ctx_lo, int64_t ld_ctx, int B, int T, int H,
                                  int d, float scale, float drop_p, uint64_t seed, b2t_stream stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     B2T_CHECK_ARG(qkv && (ctx || ctx_hi) && B > 0 && T > 0 && H > 0 && d > 0 && d <= 64, "b2t_attention_fwd: bad arguments (d=%d)", d);
+    B2T_CHECK_ARG(drop_p >= 0.0f && drop_p < 1.0f, "b2t_attention_fwd: drop_p");
+    if (b2t_attn_mma_supported(T, d, ld, ld_ctx, q_off, k_off, v_off))
+        return b2t_attn_mma_fwd(qkv, ld, q_off, k_off, v_off, kv_lens, probs, ctx, ctx_hi, ctx_lo, ld_ctx, B, T, H, d, scale,
+                                drop_p, (unsigned long long)seed, stream);
     const size_t smem = attn_smem(T, d);
     B2T_CHECK_ARG(smem <= 220 * 1024, "b2t_attention_fwd: T=%d does not fit the single-tile kernel", T);
     static bool attr = false;
@@ -224,6 +237,9 @@ extern "C" int b2t_attention_bwd(const float* qkv, int64_t ld, int q_off, int k_
     cudaStream_t stream = (cudaStream_t)stream_;
     B2T_CHECK_ARG(qkv && probs && dctx && ds_ws && dqkv && B > 0 && T > 0 && H > 0 && d > 0 && d <= 64,
                   "b2t_attention_bwd: bad arguments");
+    if (b2t_attn_mma_supported(T, d, ld, ld_ctx, q_off, k_off, v_off))
+        return b2t_attn_mma_bwd(qkv, ld, q_off, k_off, v_off, probs, dctx, ld_ctx, dqkv, dqkv_hi, dqkv_lo, B, T, H, d, scale,
+                                drop_p, (unsigned long long)seed, stream);
     const size_t smem = attn_smem(T, d);
     B2T_CHECK_ARG(smem <= 220 * 1024, "b2t_attention_bwd: T=%d does not fit the single-tile kernel", T);
     static bool attr = false;

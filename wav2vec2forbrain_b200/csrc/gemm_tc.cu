@@ -171,143 +171,175 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
-// Sum the 32 registers of every lane across the 32 lanes of the warp; lane j ends with the total
-// of register j (recursive halving: 31 shuffles instead of 32 x 5).
-__device__ __forceinline__ float warp_transpose_sum(float (&v)[32], int lane) {
-#pragma unroll
-    for (int off = 16; off >= 1; off >>= 1) {
-        const bool upper = (lane & off) != 0;
-#pragma unroll
-        for (int i = 0; i < off; ++i) {
-            const float keep = upper ? v[i + off] : v[i];
-            const float send = upper ? v[i] : v[i + off];
-            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
-        }
-    }
-    return v[0];
+__device__ __forceinline__ void tmem_ld_32x8(uint32_t taddr, float* v) {
+    uint32_t* r = reinterpret_cast<uint32_t*>(v);
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
-// Fused epilogue on 32 consecutive columns of one output row held in registers.
-// off0 = element offset of (row, col0) in the output layout; nvalid = columns of this chunk
-// inside N (a multiple of 4 on the VEC path).  VEC: every pointer / ldc is 16-byte friendly.
-template <bool VEC>
-__device__ __forceinline__ void epi_chunk(const KParams& p, float (&v)[32], long long off0, int col0, int nvalid,
-                                          bool row_ok, const float* bias_ptr, int lane) {
-    float res[32], aux[32];
-    if (row_ok) {
-        if (p.residual) {
+// Column sums of an 8-column register slab over the 32 rows (lanes) of a warp: recursive halving,
+// 9 shuffles.  Returns the total of column `col_of_lane` (valid in lanes with (lane & 3) == 0).
+__device__ __forceinline__ float warp_colsum8(const float (&v)[8], int lane, int& col_of_lane) {
+    float a[4], b[2];
+    const bool u16 = (lane & 16) != 0, u8 = (lane & 8) != 0, u4 = (lane & 4) != 0;
 #pragma unroll
-            for (int g = 0; g < 8; ++g) {
-                if (g * 4 < nvalid) {
-                    if (VEC) {
-                        const float4 t = *reinterpret_cast<const float4*>(p.residual + off0 + g * 4);
-                        res[g * 4] = t.x, res[g * 4 + 1] = t.y, res[g * 4 + 2] = t.z, res[g * 4 + 3] = t.w;
-                    } else {
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) res[g * 4 + e] = g * 4 + e < nvalid ? p.residual[off0 + g * 4 + e] : 0.0f;
-                    }
-                }
-            }
-        }
-        if (p.aux_mode) {
-#pragma unroll
-            for (int g = 0; g < 8; ++g) {
-                if (g * 4 < nvalid) {
-                    if (VEC) {
-                        const float4 t = *reinterpret_cast<const float4*>(p.aux + off0 + g * 4);
-                        aux[g * 4] = t.x, aux[g * 4 + 1] = t.y, aux[g * 4 + 2] = t.z, aux[g * 4 + 3] = t.w;
-                    } else {
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) aux[g * 4 + e] = g * 4 + e < nvalid ? p.aux[off0 + g * 4 + e] : 0.0f;
-                    }
-                }
-            }
-        }
+    for (int i = 0; i < 4; ++i) {
+        const float keep = u16 ? v[i + 4] : v[i], send = u16 ? v[i] : v[i + 4];
+        a[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
     }
 #pragma unroll
-    for (int g = 0; g < 8; ++g) {
-        if (g * 4 >= nvalid || !row_ok) {   // outside the matrix: contributes nothing to column sums
+    for (int i = 0; i < 2; ++i) {
+        const float keep = u8 ? a[i + 2] : a[i], send = u8 ? a[i] : a[i + 2];
+        b[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
+    float c = (u4 ? b[1] : b[0]) + __shfl_xor_sync(0xffffffffu, u4 ? b[0] : b[1], 4);
+    c += __shfl_xor_sync(0xffffffffu, c, 1);
+    c += __shfl_xor_sync(0xffffffffu, c, 2);
+    col_of_lane = (u16 ? 4 : 0) + (u8 ? 2 : 0) + (u4 ? 1 : 0);
+    return c;
+}
+
+// Fused epilogue on 8 consecutive columns of one output row held in registers.  Every stage is its
+// own short loop with the mode branch hoisted out of it: the executed instruction footprint stays
+// small (a fully unrolled 32-column body with all modes inline thrashed the instruction cache).
+// off0 = element offset of (row, col0); nvalid = columns inside N (8, or 4 at the edge on the VEC
+// path; anything in 1..8 on the scalar path).
+template <bool VEC>
+__device__ __forceinline__ void epi_cols8(const KParams& p, float (&v)[8], long long off0, int col0, int nvalid, bool row_ok,
+                                          const float* bias_ptr, int lane) {
+    if (row_ok) {
 #pragma unroll
-            for (int e = 0; e < 4; ++e) v[g * 4 + e] = 0.0f;
-            continue;
-        }
-        float x[4];
+        for (int e = 0; e < 8; ++e) v[e] = e < nvalid ? v[e] * p.alpha : 0.0f;
+        if (bias_ptr) {
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            const int j = g * 4 + e;
-            x[e] = v[j] * p.alpha + (bias_ptr && j < nvalid ? bias_ptr[col0 + j] : 0.0f);
+            for (int e = 0; e < 8; ++e)
+                if (e < nvalid) v[e] += bias_ptr[col0 + e];
         }
         if (p.out_pre) {
             if (VEC) {
-                *reinterpret_cast<float4*>(p.out_pre + off0 + g * 4) = make_float4(x[0], x[1], x[2], x[3]);
+                *reinterpret_cast<float4*>(p.out_pre + off0) = make_float4(v[0], v[1], v[2], v[3]);
+                if (nvalid > 4) *reinterpret_cast<float4*>(p.out_pre + off0 + 4) = make_float4(v[4], v[5], v[6], v[7]);
             } else {
 #pragma unroll
-                for (int e = 0; e < 4; ++e)
-                    if (g * 4 + e < nvalid) p.out_pre[off0 + g * 4 + e] = x[e];
+                for (int e = 0; e < 8; ++e)
+                    if (e < nvalid) p.out_pre[off0 + e] = v[e];
+            }
+        }
+        if (p.act == 1) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = gelu_erf(v[e]);
+        } else if (p.act == 2) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = silu_f(v[e]);
+        } else if (p.act == 3) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = v[e] / (1.0f + fabsf(v[e]));
+        }
+        if (p.aux_mode) {
+            float a[8];
+            if (VEC) {
+                const float4 t0 = *reinterpret_cast<const float4*>(p.aux + off0);
+                const float4 t1 = nvalid > 4 ? *reinterpret_cast<const float4*>(p.aux + off0 + 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+                a[0] = t0.x, a[1] = t0.y, a[2] = t0.z, a[3] = t0.w, a[4] = t1.x, a[5] = t1.y, a[6] = t1.z, a[7] = t1.w;
+            } else {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) a[e] = e < nvalid ? p.aux[off0 + e] : 0.0f;
+            }
+            if (p.aux_mode == 1) {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) v[e] *= gelu_erf_grad(a[e]);
+            } else if (p.aux_mode == 2) {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) v[e] *= silu_grad(a[e]);
+            } else {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    const float d = 1.0f + fabsf(a[e]);
+                    v[e] *= 1.0f / (d * d);
+                }
+            }
+        }
+        if (p.drop_p > 0.0f) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e)
+                v[e] = hash_uniform(p.drop_seed, (unsigned long long)(off0 + e)) < p.drop_p ? 0.0f : v[e] * p.drop_scale;
+        }
+        if (p.out_scale != 1.0f) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] *= p.out_scale;
+        }
+        if (p.residual) {
+            if (VEC) {
+                const float4 t0 = *reinterpret_cast<const float4*>(p.residual + off0);
+                const float4 t1 = nvalid > 4 ? *reinterpret_cast<const float4*>(p.residual + off0 + 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+                v[0] += t0.x, v[1] += t0.y, v[2] += t0.z, v[3] += t0.w, v[4] += t1.x, v[5] += t1.y, v[6] += t1.z, v[7] += t1.w;
+            } else {
+#pragma unroll
+                for (int e = 0; e < 8; ++e)
+                    if (e < nvalid) v[e] += p.residual[off0 + e];
             }
         }
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            const int j = g * 4 + e;
-            float y = apply_act(x[e], p.act);
-            if (p.aux_mode) y *= apply_dact(aux[j], p.aux_mode);
-            if (p.drop_p > 0.0f)
-                y = hash_uniform(p.drop_seed, (unsigned long long)(off0 + j)) < p.drop_p ? 0.0f : y * p.drop_scale;
-            y *= p.out_scale;
-            if (p.residual) y += res[j];
-            x[e] = (VEC || j < nvalid) ? y : 0.0f;
-            v[j] = x[e];
-        }
+        for (int e = 0; e < 8; ++e) v[e] = e < nvalid ? v[e] : 0.0f;
         if (p.out_f32) {
-            float* o = p.out_f32 + off0 + g * 4;
+            float* o = p.out_f32 + off0;
             if (VEC) {
-                if (p.atomic)
-                    red_add_v4(o, x[0], x[1], x[2], x[3]);
-                else
-                    *reinterpret_cast<float4*>(o) = make_float4(x[0], x[1], x[2], x[3]);
+                if (p.atomic) {
+                    red_add_v4(o, v[0], v[1], v[2], v[3]);
+                    if (nvalid > 4) red_add_v4(o + 4, v[4], v[5], v[6], v[7]);
+                } else {
+                    *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
+                    if (nvalid > 4) *reinterpret_cast<float4*>(o + 4) = make_float4(v[4], v[5], v[6], v[7]);
+                }
             } else {
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    if (g * 4 + e < nvalid) {
+                for (int e = 0; e < 8; ++e) {
+                    if (e < nvalid) {
                         if (p.atomic)
-                            atomicAdd(o + e, x[e]);
+                            atomicAdd(o + e, v[e]);
                         else
-                            o[e] = x[e];
+                            o[e] = v[e];
                     }
                 }
             }
         }
         if (p.out_hi) {
-            bf16 h[4], l[4];
+            bf16 h[8], l[8];
 #pragma unroll
-            for (int e = 0; e < 4; ++e) split_bf16(x[e], h[e], l[e]);
+            for (int e = 0; e < 8; ++e) split_bf16(v[e], h[e], l[e]);
             if (VEC) {
-                __nv_bfloat162 a = __halves2bfloat162(h[0], h[1]), b = __halves2bfloat162(h[2], h[3]);
-                uint2 w;
-                w.x = *reinterpret_cast<uint32_t*>(&a);
-                w.y = *reinterpret_cast<uint32_t*>(&b);
-                *reinterpret_cast<uint2*>(p.out_hi + off0 + g * 4) = w;
+                auto pk = [](bf16 a, bf16 b) {
+                    __nv_bfloat162 t = __halves2bfloat162(a, b);
+                    return *reinterpret_cast<uint32_t*>(&t);
+                };
+                const uint2 h0 = make_uint2(pk(h[0], h[1]), pk(h[2], h[3])), h1 = make_uint2(pk(h[4], h[5]), pk(h[6], h[7]));
+                *reinterpret_cast<uint2*>(p.out_hi + off0) = h0;
+                if (nvalid > 4) *reinterpret_cast<uint2*>(p.out_hi + off0 + 4) = h1;
                 if (p.out_lo) {
-                    a = __halves2bfloat162(l[0], l[1]);
-                    b = __halves2bfloat162(l[2], l[3]);
-                    w.x = *reinterpret_cast<uint32_t*>(&a);
-                    w.y = *reinterpret_cast<uint32_t*>(&b);
-                    *reinterpret_cast<uint2*>(p.out_lo + off0 + g * 4) = w;
+                    const uint2 l0 = make_uint2(pk(l[0], l[1]), pk(l[2], l[3])), l1 = make_uint2(pk(l[4], l[5]), pk(l[6], l[7]));
+                    *reinterpret_cast<uint2*>(p.out_lo + off0) = l0;
+                    if (nvalid > 4) *reinterpret_cast<uint2*>(p.out_lo + off0 + 4) = l1;
                 }
             } else {
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    if (g * 4 + e < nvalid) {
-                        p.out_hi[off0 + g * 4 + e] = h[e];
-                        if (p.out_lo) p.out_lo[off0 + g * 4 + e] = l[e];
+                for (int e = 0; e < 8; ++e) {
+                    if (e < nvalid) {
+                        p.out_hi[off0 + e] = h[e];
+                        if (p.out_lo) p.out_lo[off0 + e] = l[e];
                     }
                 }
             }
         }
+    } else {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] = 0.0f;   // outside the matrix: contributes nothing to column sums
     }
     if (p.colsum) {   // warp-uniform
-        const float s = warp_transpose_sum(v, lane);
-        if (lane < nvalid) atomicAdd(p.colsum + col0 + lane, s);
+        int cl;
+        const float s = warp_colsum8(v, lane, cl);
+        if ((lane & 3) == 0 && cl < nvalid) atomicAdd(p.colsum + col0 + cl, s);
     }
 }
 
@@ -496,22 +528,25 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
                 (p.bias != nullptr && split == 0) ? p.bias + (long long)bslot * p.bias_batch_stride : nullptr;
 #pragma unroll 1
             for (int c = half; c < BN / 32; c += 2) {
-                float v[32];
-                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + c * 32);
-                tmem_ld_32x32(taddr, v);
-                if (c + 2 >= BN / 32) {
-                    // this warp's share of the accumulator is in registers: hand the TMEM stage back
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(tempty_bar(acc));
+#pragma unroll 1
+                for (int s8 = 0; s8 < 4; ++s8) {
+                    float v[8];
+                    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + c * 32 + s8 * 8);
+                    tmem_ld_32x8(taddr, v);
+                    if (c + 2 >= BN / 32 && s8 == 3) {
+                        // this warp's share of the accumulator is in registers: hand the TMEM stage back
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(tempty_bar(acc));
+                    }
+                    const int col0 = n_blk * BN + c * 32 + s8 * 8;
+                    if (col0 >= p.n) continue;   // warp-uniform
+                    const int nvalid = p.n - col0 < 8 ? p.n - col0 : 8;
+                    if (p.vec4)
+                        epi_cols8<true>(p, v, row_off + col0, col0, nvalid, row_ok, bias_ptr, lane);
+                    else
+                        epi_cols8<false>(p, v, row_off + col0, col0, nvalid, row_ok, bias_ptr, lane);
                 }
-                const int col0 = n_blk * BN + c * 32;
-                if (col0 >= p.n) continue;   // warp-uniform
-                const int nvalid = p.n - col0 < 32 ? p.n - col0 : 32;
-                if (p.vec4)
-                    epi_chunk<true>(p, v, row_off + col0, col0, nvalid, row_ok, bias_ptr, lane);
-                else
-                    epi_chunk<false>(p, v, row_off + col0, col0, nvalid, row_ok, bias_ptr, lane);
             }
         }
     }

@@ -148,6 +148,189 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ d
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// vectorised variants (n % 4 == 0): a lane owns float4 columns lane + 32 i, a warp one row; the
+// parameter-gradient column sums of the backward are a separate column-parallel kernel, so the
+// row kernel keeps no per-column accumulators (the scalar kernel needs ~250 registers for them).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint2 pack4_bf16(bf16 a, bf16 b, bf16 c, bf16 d) {
+    __nv_bfloat162 x = __halves2bfloat162(a, b), y = __halves2bfloat162(c, d);
+    uint2 w;
+    w.x = *reinterpret_cast<uint32_t*>(&x);
+    w.y = *reinterpret_cast<uint32_t*>(&y);
+    return w;
+}
+__device__ __forceinline__ void store_split4(const float (&o)[4], bf16* hi, bf16* lo, long off) {
+    bf16 h[4], l[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) split_bf16(o[e], h[e], l[e]);
+    *reinterpret_cast<uint2*>(hi + off) = pack4_bf16(h[0], h[1], h[2], h[3]);
+    if (lo) *reinterpret_cast<uint2*>(lo + off) = pack4_bf16(l[0], l[1], l[2], l[3]);
+}
+
+template <int VPL>
+__global__ void __launch_bounds__(256) ln_fwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                                                         const float* __restrict__ beta, float eps, float* __restrict__ y,
+                                                         bf16* __restrict__ y_hi, bf16* __restrict__ y_lo,
+                                                         float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows,
+                                                         int n, float drop_p, unsigned long long seed) {
+    const int lane = threadIdx.x & 31;
+    const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int nwarps = (gridDim.x * blockDim.x) >> 5;
+    const float inv_n = 1.0f / (float)n;
+    const float drop_scale = 1.0f / (1.0f - drop_p);
+    for (int row = warp_global; row < rows; row += nwarps) {
+        const float* xr = x + (long)row * n;
+        float4 v[VPL];
+        float s = 0.0f;
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            const int c = (lane + 32 * i) * 4;
+            v[i] = c < n ? *reinterpret_cast<const float4*>(xr + c) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+        }
+        const float mean = warp_sum(s) * inv_n;
+        float q = 0.0f;
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            if ((lane + 32 * i) * 4 < n) {
+                const float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
+                q += (a * a + b * b) + (c * c + d * d);
+            }
+        }
+        const float rstd = rsqrtf(warp_sum(q) * inv_n + eps);
+        if (lane == 0) {
+            if (mean_out) mean_out[row] = mean;
+            if (rstd_out) rstd_out[row] = rstd;
+        }
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            const int c = (lane + 32 * i) * 4;
+            if (c < n) {
+                const float4 ga = *reinterpret_cast<const float4*>(gamma + c), be = *reinterpret_cast<const float4*>(beta + c);
+                const long off = (long)row * n + c;
+                float o[4] = {(v[i].x - mean) * rstd * ga.x + be.x, (v[i].y - mean) * rstd * ga.y + be.y,
+                              (v[i].z - mean) * rstd * ga.z + be.z, (v[i].w - mean) * rstd * ga.w + be.w};
+                if (drop_p > 0.0f) {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                        o[e] = hash_uniform(seed, (unsigned long long)(off + e)) < drop_p ? 0.0f : o[e] * drop_scale;
+                }
+                if (y) *reinterpret_cast<float4*>(y + off) = make_float4(o[0], o[1], o[2], o[3]);
+                if (y_hi) store_split4(o, y_hi, y_lo, off);
+            }
+        }
+    }
+}
+
+template <int VPL>
+__global__ void __launch_bounds__(256) ln_bwd_vec_kernel(const float* __restrict__ dy, const float* __restrict__ x,
+                                                         const float* __restrict__ gamma, const float* __restrict__ mean_in,
+                                                         const float* __restrict__ rstd_in, float* __restrict__ dx,
+                                                         bf16* __restrict__ dx_hi, bf16* __restrict__ dx_lo, int rows, int n,
+                                                         float out_drop_p, unsigned long long out_seed, float br_drop_p,
+                                                         unsigned long long br_seed, const float* __restrict__ dres) {
+    const int lane = threadIdx.x & 31;
+    const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int nwarps = (gridDim.x * blockDim.x) >> 5;
+    const float inv_n = 1.0f / (float)n;
+    const float out_scale = 1.0f / (1.0f - out_drop_p), br_scale = 1.0f / (1.0f - br_drop_p);
+    for (int row = warp_global; row < rows; row += nwarps) {
+        const float mean = mean_in[row], rstd = rstd_in[row];
+        float xh[VPL][4], g[VPL][4];
+        float s1 = 0.0f, s2 = 0.0f;
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            const int c = (lane + 32 * i) * 4;
+            if (c < n) {
+                const long off = (long)row * n + c;
+                const float4 d4 = *reinterpret_cast<const float4*>(dy + off);
+                const float4 x4 = *reinterpret_cast<const float4*>(x + off);
+                const float4 ga = *reinterpret_cast<const float4*>(gamma + c);
+                float d[4] = {d4.x, d4.y, d4.z, d4.w};
+                const float xv[4] = {x4.x, x4.y, x4.z, x4.w};
+                const float gv[4] = {ga.x, ga.y, ga.z, ga.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    if (out_drop_p > 0.0f)
+                        d[e] = hash_uniform(out_seed, (unsigned long long)(off + e)) < out_drop_p ? 0.0f : d[e] * out_scale;
+                    xh[i][e] = (xv[e] - mean) * rstd;
+                    g[i][e] = d[e] * gv[e];
+                    s1 += g[i][e];
+                    s2 += g[i][e] * xh[i][e];
+                }
+            }
+        }
+        s1 = warp_sum(s1) * inv_n;
+        s2 = warp_sum(s2) * inv_n;
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            const int c = (lane + 32 * i) * 4;
+            if (c < n) {
+                const long off = (long)row * n + c;
+                float o[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) o[e] = rstd * (g[i][e] - s1 - xh[i][e] * s2);
+                if (dres) {
+                    const float4 r4 = *reinterpret_cast<const float4*>(dres + off);
+                    o[0] += r4.x, o[1] += r4.y, o[2] += r4.z, o[3] += r4.w;
+                }
+                if (dx) *reinterpret_cast<float4*>(dx + off) = make_float4(o[0], o[1], o[2], o[3]);
+                if (dx_hi) {
+                    if (br_drop_p > 0.0f) {
+#pragma unroll
+                        for (int e = 0; e < 4; ++e)
+                            o[e] = hash_uniform(br_seed, (unsigned long long)(off + e)) < br_drop_p ? 0.0f : o[e] * br_scale;
+                    }
+                    store_split4(o, dx_hi, dx_lo, off);
+                }
+            }
+        }
+    }
+}
+
+// column sums of the LayerNorm backward: dgamma += sum_r dy.xhat, dbeta += sum_r dy, dcol += sum_r mask.dx
+// grid (ceil(n / 32), row slabs), block (32, 8): a warp reads 128 contiguous bytes of a row.
+constexpr int LNC_ROWS = 128;
+__global__ void __launch_bounds__(256) ln_bwd_cols_kernel(const float* __restrict__ dy, const float* __restrict__ x,
+                                                          const float* __restrict__ mean_in, const float* __restrict__ rstd_in,
+                                                          const float* __restrict__ dx, float* __restrict__ dgamma,
+                                                          float* __restrict__ dbeta, float* __restrict__ dcol, int rows, int n,
+                                                          float out_drop_p, unsigned long long out_seed, float br_drop_p,
+                                                          unsigned long long br_seed) {
+    __shared__ float part[3][8][33];
+    const int c = blockIdx.x * 32 + threadIdx.x;
+    const int r0 = blockIdx.y * LNC_ROWS;
+    const int r1 = r0 + LNC_ROWS < rows ? r0 + LNC_ROWS : rows;
+    const float out_scale = 1.0f / (1.0f - out_drop_p), br_scale = 1.0f / (1.0f - br_drop_p);
+    float ag = 0.0f, ab = 0.0f, ac = 0.0f;
+    if (c < n) {
+        for (int r = r0 + threadIdx.y; r < r1; r += 8) {
+            const long off = (long)r * n + c;
+            float d = dy[off];
+            if (out_drop_p > 0.0f) d = hash_uniform(out_seed, (unsigned long long)off) < out_drop_p ? 0.0f : d * out_scale;
+            ag += d * (x[off] - mean_in[r]) * rstd_in[r];
+            ab += d;
+            if (dcol) {
+                float o = dx[off];
+                if (br_drop_p > 0.0f) o = hash_uniform(br_seed, (unsigned long long)off) < br_drop_p ? 0.0f : o * br_scale;
+                ac += o;
+            }
+        }
+    }
+    part[0][threadIdx.y][threadIdx.x] = ag;
+    part[1][threadIdx.y][threadIdx.x] = ab;
+    part[2][threadIdx.y][threadIdx.x] = ac;
+    __syncthreads();
+    if (threadIdx.y < 3 && c < n) {
+        float sum = 0.0f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) sum += part[threadIdx.y][j][threadIdx.x];
+        float* dst = threadIdx.y == 0 ? dgamma : (threadIdx.y == 1 ? dbeta : dcol);
+        if (dst) atomicAdd(dst + c, sum);
+    }
+}
+
 // y = dropout(x) (same hash mask contract as the GEMM epilogue) with optional fp32 / hi / lo outputs;
 // p == 0 degenerates to a plain split.  Also the backward (apply to the incoming gradient).
 __global__ void dropout_kernel(const float* __restrict__ x, float* __restrict__ y, bf16* __restrict__ hi,
@@ -216,6 +399,17 @@ extern "C" int b2t_layernorm_fwd(const float* x, const float* gamma, const float
     B2T_CHECK_ARG(x && gamma && beta && (y || y_hi) && rows > 0 && n > 0 && n <= 1024, "b2t_layernorm_fwd: bad arguments (n=%d)", n);
     B2T_CHECK_ARG(drop_p >= 0.0f && drop_p < 1.0f, "b2t_layernorm_fwd: drop_p");
     const int grid = grid_for((long)rows * 32, 256, 8);
+    auto al16 = [](const void* q) { return ((uintptr_t)q & 15) == 0; };
+    if (n % 4 == 0 && al16(x) && al16(gamma) && al16(beta) && al16(y) && ((uintptr_t)y_hi & 7) == 0 && ((uintptr_t)y_lo & 7) == 0) {
+        const int vpl = (n / 4 + 31) / 32;
+#define VCALL(V)                                                                                                         \
+    ln_fwd_vec_kernel<V><<<grid, 256, 0, stream>>>(x, gamma, beta, eps, y, (bf16*)y_hi, (bf16*)y_lo, mean, rstd, rows, n, \
+                                                   drop_p, (unsigned long long)seed)
+        if (vpl <= 1) { VCALL(1); } else if (vpl <= 2) { VCALL(2); } else if (vpl <= 4) { VCALL(4); } else if (vpl <= 6) { VCALL(6); } else { VCALL(8); }
+#undef VCALL
+        B2T_CHECK_LAUNCH("b2t_layernorm_fwd");
+        return 0;
+    }
 #define CALL(P)                                                                                                          \
     ln_fwd_kernel<P><<<grid, 256, 0, stream>>>(x, gamma, beta, eps, y, (bf16*)y_hi, (bf16*)y_lo, mean, rstd, rows, n, drop_p, \
                                                (unsigned long long)seed)
@@ -231,6 +425,26 @@ extern "C" int b2t_layernorm_bwd(const float* dy, const float* x, const float* g
                                  const float* dres, b2t_stream stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     B2T_CHECK_ARG(dy && x && gamma && mean && rstd && rows > 0 && n > 0 && n <= 1024, "b2t_layernorm_bwd: bad arguments");
+    auto al16 = [](const void* q) { return ((uintptr_t)q & 15) == 0; };
+    if (n % 4 == 0 && al16(dy) && al16(x) && al16(gamma) && al16(dx) && al16(dres) && ((uintptr_t)dx_hi & 7) == 0 &&
+        ((uintptr_t)dx_lo & 7) == 0 && (dx || !dcol)) {
+        const int vgrid = grid_for((long)rows * 32, 256, 8);
+        const int vpl = (n / 4 + 31) / 32;
+#define VCALL(V)                                                                                                          \
+    ln_bwd_vec_kernel<V><<<vgrid, 256, 0, stream>>>(dy, x, gamma, mean, rstd, dx, (bf16*)dx_hi, (bf16*)dx_lo, rows, n, out_drop_p, \
+                                                    (unsigned long long)out_seed, br_drop_p, (unsigned long long)br_seed, dres)
+        if (vpl <= 1) { VCALL(1); } else if (vpl <= 2) { VCALL(2); } else if (vpl <= 4) { VCALL(4); } else if (vpl <= 6) { VCALL(6); } else { VCALL(8); }
+#undef VCALL
+        B2T_CHECK_LAUNCH("b2t_layernorm_bwd");
+        if (dgamma || dbeta || dcol) {
+            dim3 cgrid((n + 31) / 32, (rows + LNC_ROWS - 1) / LNC_ROWS);
+            ln_bwd_cols_kernel<<<cgrid, dim3(32, 8), 0, stream>>>(dy, x, mean, rstd, dx, dgamma, dbeta, dcol, rows, n, out_drop_p,
+                                                                  (unsigned long long)out_seed, br_drop_p,
+                                                                  (unsigned long long)br_seed);
+            B2T_CHECK_LAUNCH("b2t_layernorm_bwd (column sums)");
+        }
+        return 0;
+    }
     const int grid = grid_for((long)rows * 32, 256, 2);
     const size_t smem = 3 * (size_t)n * sizeof(float);
 #define CALL(P)                                                                                                       \
