@@ -30,9 +30,11 @@ __device__ __forceinline__ uint32_t cluster_ctarank() {
     asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
     return r;
 }
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
 __device__ __forceinline__ void cluster_sync_all() {
-    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    cluster_arrive();
+    cluster_wait();
 }
 __device__ __forceinline__ uint32_t map_to_cta(uint32_t local_smem_addr, uint32_t rank) {
     uint32_t r;
@@ -42,6 +44,40 @@ __device__ __forceinline__ uint32_t map_to_cta(uint32_t local_smem_addr, uint32_
 __device__ __forceinline__ void st_cluster_v4(uint32_t addr, uint4 v) {
     asm volatile("st.shared::cluster.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
                  : "memory");
+}
+// remote store that signals `mbar` (an mbarrier of the DESTINATION CTA, cluster address) with its byte
+// count: the arrival of the data is the synchronisation, no cluster-wide barrier / membar per step
+__device__ __forceinline__ void st_async_v4(uint32_t addr, uint4 v, uint32_t mbar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1, %2, %3, %4}, [%5];" ::"r"(addr),
+                 "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(mbar)
+                 : "memory");
+}
+__device__ __forceinline__ void st_async_v2f(uint32_t addr, float a, float b, uint32_t mbar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f32 [%0], {%1, %2}, [%3];" ::"r"(addr), "f"(a),
+                 "f"(b), "r"(mbar)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    for (uint32_t spin = 0; !done; ++spin) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (spin > (1u << 22)) {   // a lost signal must trap, not hang the box
+            printf("b2t_gru: mbarrier timeout block %d thread %d\n", blockIdx.x, threadIdx.x);
+            __trap();
+        }
+    }
 }
 __device__ __forceinline__ void st_cluster_v2f(uint32_t addr, float a, float b) {
     asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(addr), "f"(a), "f"(b) : "memory");
@@ -147,27 +183,49 @@ __global__ void __launch_bounds__(384, 1) gru_fwd_kernel(const GruFwdArgs p) {
         hbuf[(0 * 2 + 1) * RB * HP + r * HP + k] = ll;
     }
     for (int i = tid; i < RB * U; i += blockDim.x) hown[i] = p.h0 ? p.h0[(long)dir * H + u0 + (i % U)] : 0.0f;
+    // hbar[b]: "hbuf[b] holds the complete h of the step about to start" — completed by the byte counts
+    // of the CS remote slices (st.async), one phase per use
+    __shared__ __align__(8) unsigned long long hbar[2];
+    const uint32_t hbar0 = (uint32_t)__cvta_generic_to_shared(&hbar[0]);
+    constexpr uint32_t STEP_BYTES = (uint32_t)CS * 2 * RB * U * 2;
+    if (tid == 0) {
+        mbar_init(hbar0, 1);
+        mbar_init(hbar0 + 8, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     __syncthreads();
     cluster_sync_all();
+    uint32_t hphase[2] = {0u, 0u};
 
     // gate-phase items: threads 0..255 own unit (tid % 32) for rows tid/32 and tid/32 + 8
     const int gu = tid & 31, gr = tid >> 5;
     const int gdim = p.ndir * 3 * H;
 
-    for (int s = 0; s < T; ++s) {
-        const int t = dir == 0 ? s : T - 1 - s;
-        const int cur = s & 1;
-        // prefetch the input projections of this step for the gate phase
-        float gi_v[2][3];
+    // input projections of a step, loaded one step ahead so their DRAM latency hides behind the
+    // previous step's recurrence (the gate phase never waits on global memory)
+    float gi_v[2][3];
+    auto load_gi = [&](int s_) {
+        const int t_ = dir == 0 ? s_ : T - 1 - s_;
         if (tid < 256) {
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
                 const int b = row0 + gr + 8 * j;
 #pragma unroll
                 for (int q = 0; q < 3; ++q)
-                    gi_v[j][q] = b < p.B ? p.gi[((long)b * T + t) * gdim + dir * 3 * H + q * H + u0 + gu] : 0.0f;
+                    gi_v[j][q] = (b < p.B && s_ < T) ? p.gi[((long)b * T + t_) * gdim + dir * 3 * H + q * H + u0 + gu] : 0.0f;
             }
         }
+    };
+    load_gi(0);
+
+    for (int s = 0; s < T; ++s) {
+        const int t = dir == 0 ? s : T - 1 - s;
+        const int cur = s & 1;
+        if (s > 0) {   // every slice of h_s has landed in hbuf[cur]
+            mbar_wait(hbar0 + 8 * cur, hphase[cur]);
+            hphase[cur] ^= 1u;
+        }
+        if (tid == 0 && s + 1 < T) mbar_expect_tx(hbar0 + 8 * (cur ^ 1), STEP_BYTES);
         // ---- gh = h . W_slice^T (bf16x3) ----
         {
             const bf16* hh = hbuf + (cur * 2 + 0) * RB * HP;
@@ -198,11 +256,11 @@ __global__ void __launch_bounds__(384, 1) gru_fwd_kernel(const GruFwdArgs p) {
         }
         __syncthreads();
         // ---- gates for the own 32 units (brain_feature_extractor.py nn.GRU equations, App. A.2) ----
+        float rv[2], zv[2], nv[2], ghnv[2], hpv[2], hnv[2];
         if (tid < 256) {
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
                 const int row = gr + 8 * j;
-                const int b = row0 + row;
                 const float gh_r = gh_s[row * (NCOL + 1) + gu];
                 const float gh_z = gh_s[row * (NCOL + 1) + U + gu];
                 const float gh_n = gh_s[row * (NCOL + 1) + 2 * U + gu];
@@ -216,12 +274,34 @@ __global__ void __launch_bounds__(384, 1) gru_fwd_kernel(const GruFwdArgs p) {
                 split_bf16(hn, hh, ll);
                 stage[row * U + gu] = hh;
                 stage[RB * U + row * U + gu] = ll;
+                rv[j] = r, zv[j] = z, nv[j] = n, ghnv[j] = gh_n, hpv[j] = hp, hnv[j] = hn;
+            }
+        }
+        load_gi(s + 1);
+        __syncthreads();
+        // ---- push the new h slice (bf16 hi, lo) to every CTA of the cluster (not needed after the last step) ----
+        if (s + 1 < T) {
+            const int nxt = cur ^ 1;
+            for (int idx = tid; idx < 128 * CS; idx += blockDim.x) {
+                const int dest = idx >> 7, c = idx & 127;
+                const int which = c >> 6, row = (c & 63) >> 2, ch = c & 3;
+                const uint4 v = *reinterpret_cast<const uint4*>(stage + which * RB * U + row * U + ch * 8);
+                bf16* dst = hbuf + (nxt * 2 + which) * RB * HP + row * HP + u0 + ch * 8;
+                st_async_v4(map_to_cta((uint32_t)__cvta_generic_to_shared(dst), (uint32_t)dest), v,
+                            map_to_cta(hbar0 + 8 * nxt, (uint32_t)dest));
+            }
+        }
+        // ---- outputs and saved-for-backward values (off the recurrence's critical path) ----
+        if (tid < 256) {
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const int b = row0 + gr + 8 * j;
                 if (b < p.B) {
                     const long m = (long)b * T + t;
                     const long oo = m * (p.ndir * H) + dir * H + u0 + gu;
-                    p.out[oo] = hn;
+                    p.out[oo] = hnv[j];
                     if (p.out_hi) {
-                        const float hd = hn * keep_scale(p.drop_p, p.seed, (unsigned long long)oo);
+                        const float hd = hnv[j] * keep_scale(p.drop_p, p.seed, (unsigned long long)oo);
                         bf16 dh_, dl_;
                         split_bf16(hd, dh_, dl_);
                         p.out_hi[oo] = dh_;
@@ -229,32 +309,20 @@ __global__ void __launch_bounds__(384, 1) gru_fwd_kernel(const GruFwdArgs p) {
                     }
                     if (p.save_r) {
                         const long so = ((long)dir * M + m) * H + u0 + gu;
-                        p.save_r[so] = r;
-                        p.save_z[so] = z;
-                        p.save_n[so] = n;
-                        p.save_ghn[so] = gh_n;
+                        p.save_r[so] = rv[j];
+                        p.save_z[so] = zv[j];
+                        p.save_n[so] = nv[j];
+                        p.save_ghn[so] = ghnv[j];
                         bf16 ph, pl;
-                        split_bf16(hp, ph, pl);
+                        split_bf16(hpv[j], ph, pl);
                         p.hprev_hi[so] = ph;
                         if (p.hprev_lo) p.hprev_lo[so] = pl;
                     }
                 }
             }
         }
-        __syncthreads();
-        // ---- push the new h slice (bf16 hi, lo) to every CTA of the cluster ----
-        {
-            const int nxt = cur ^ 1;
-            for (int idx = tid; idx < 128 * CS; idx += blockDim.x) {
-                const int dest = idx >> 7, c = idx & 127;
-                const int which = c >> 6, row = (c & 63) >> 2, ch = c & 3;
-                const uint4 v = *reinterpret_cast<const uint4*>(stage + which * RB * U + row * U + ch * 8);
-                bf16* dst = hbuf + (nxt * 2 + which) * RB * HP + row * HP + u0 + ch * 8;
-                st_cluster_v4(map_to_cta((uint32_t)__cvta_generic_to_shared(dst), (uint32_t)dest), v);
-            }
-        }
-        cluster_sync_all();
     }
+    cluster_sync_all();   // no CTA may exit while a peer can still write into its shared memory
 }
 
 struct GruBwdArgs {
@@ -335,72 +403,95 @@ __global__ void __launch_bounds__(BwdSmem<H>::THREADS, 1) gru_bwd_kernel(const G
     }
     for (int i = tid; i < RB * U; i += blockDim.x) dhz[i] = 0.0f;
     for (int i = tid; i < 2 * CS * RB * U; i += blockDim.x) recv[i] = 0.0f;
+    // rbar[b]: "recv[b] holds every peer's partial dh for the step about to start" (st.async byte counts)
+    __shared__ __align__(8) unsigned long long rbar[2];
+    const uint32_t rbar0 = (uint32_t)__cvta_generic_to_shared(&rbar[0]);
+    constexpr uint32_t STEP_BYTES = (uint32_t)CS * RB * U * 4;
+    if (tid == 0) {
+        mbar_init(rbar0, 1);
+        mbar_init(rbar0 + 8, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     __syncthreads();
     cluster_sync_all();
+    uint32_t rphase[2] = {0u, 0u};
 
     const int odim = p.ndir * H, gdim = p.ndir * 3 * H;
-    for (int s = 0; s < T; ++s) {
-        const int t = dir == 0 ? T - 1 - s : s;           // reverse of the forward order
-        const int tprev = dir == 0 ? t - 1 : t + 1;       // time index of the h that entered step t
-        const int cur = s & 1;
-        // ---- gate derivatives for the own units ----
-        for (int item = tid; item < RB * U; item += blockDim.x) {
+    // One (trial row, unit) item per thread and pass; its saved forward values are loaded one step
+    // ahead (DRAM latency hidden behind the previous step), its global stores are issued after the
+    // cluster barrier's arrive (the release does not have to drain them).
+    constexpr int ITEMS = (RB * U + S::THREADS - 1) / S::THREADS;
+    float f_dout[ITEMS], f_r[ITEMS], f_z[ITEMS], f_n[ITEMS], f_ghn[ITEMS], f_hp[ITEMS];
+    auto prefetch = [&](int s_) {
+        const int t_ = dir == 0 ? T - 1 - s_ : s_;
+        const int tp_ = dir == 0 ? t_ - 1 : t_ + 1;
+#pragma unroll
+        for (int it = 0; it < ITEMS; ++it) {
+            const int item = tid + it * S::THREADS;
             const int row = item / U, uu = item % U;
             const int b = row0 + row;
-            float dar = 0.f, daz = 0.f, dan = 0.f, dghn_v = 0.f, carry = 0.f;
-            if (b < p.B) {
-                float rec = dhz[item];
-#pragma unroll 4
-                for (int src = 0; src < CS; ++src) rec += recv[((cur * CS + src) * RB + row) * U + uu];
-                const long m = (long)b * T + t;
+            f_dout[it] = f_r[it] = f_z[it] = f_n[it] = f_ghn[it] = f_hp[it] = 0.0f;
+            if (item < RB * U && b < p.B && s_ < T) {
+                const long m = (long)b * T + t_;
                 const long oo = m * odim + dir * H + u0 + uu;
-                const float dh = rec + p.dout[oo] * keep_scale(p.drop_p, p.seed, (unsigned long long)oo);
                 const long so = ((long)dir * M + m) * H + u0 + uu;
-                const float r = p.save_r[so], z = p.save_z[so], n = p.save_n[so], ghn = p.save_ghn[so];
-                float hp;
-                if (tprev >= 0 && tprev < T) hp = p.out[((long)b * T + tprev) * odim + dir * H + u0 + uu];
-                else hp = p.h0 ? p.h0[(long)dir * H + u0 + uu] : 0.0f;
-                const float dn = dh * (1.0f - z);
-                const float dz = dh * (hp - n);
-                carry = dh * z;
-                dan = dn * (1.0f - n * n);
-                dar = dan * ghn * r * (1.0f - r);
-                daz = dz * z * (1.0f - z);
-                dghn_v = dan * r;
-                const long go = m * gdim + dir * 3 * H + u0 + uu;
-                p.dgi[go] = dar;
-                p.dgi[go + H] = daz;
-                p.dgi[go + 2 * H] = dan;
-                bf16 hh, ll;
-                const long ho = ((long)dir * M + m) * 3 * H + u0 + uu;
-                split_bf16(dar, hh, ll);
-                p.dgi_hi[go] = hh;
-                p.dgh_hi[ho] = hh;
-                if (p.dgi_lo) { p.dgi_lo[go] = ll; p.dgh_lo[ho] = ll; }
-                split_bf16(daz, hh, ll);
-                p.dgi_hi[go + H] = hh;
-                p.dgh_hi[ho + H] = hh;
-                if (p.dgi_lo) { p.dgi_lo[go + H] = ll; p.dgh_lo[ho + H] = ll; }
-                split_bf16(dan, hh, ll);
-                p.dgi_hi[go + 2 * H] = hh;
-                if (p.dgi_lo) p.dgi_lo[go + 2 * H] = ll;
-                split_bf16(dghn_v, hh, ll);
-                p.dgh_hi[ho + 2 * H] = hh;
-                if (p.dgh_lo) p.dgh_lo[ho + 2 * H] = ll;
-                p.dghn[so] = dghn_v;
+                f_dout[it] = p.dout[oo] * keep_scale(p.drop_p, p.seed, (unsigned long long)oo);
+                f_r[it] = p.save_r[so];
+                f_z[it] = p.save_z[so];
+                f_n[it] = p.save_n[so];
+                f_ghn[it] = p.save_ghn[so];
+                if (tp_ >= 0 && tp_ < T) f_hp[it] = p.out[((long)b * T + tp_) * odim + dir * H + u0 + uu];
+                else f_hp[it] = p.h0 ? p.h0[(long)dir * H + u0 + uu] : 0.0f;
             }
-            dhz[item] = carry;
-            bf16 hh, ll;
-            split_bf16(dar, hh, ll);
-            aop[row * AP + uu] = hh;
-            aop[RB * AP + row * AP + uu] = ll;
-            split_bf16(daz, hh, ll);
-            aop[row * AP + U + uu] = hh;
-            aop[RB * AP + row * AP + U + uu] = ll;
-            split_bf16(dghn_v, hh, ll);
-            aop[row * AP + 2 * U + uu] = hh;
-            aop[RB * AP + row * AP + 2 * U + uu] = ll;
         }
+    };
+    prefetch(0);
+    for (int s = 0; s < T; ++s) {
+        const int t = dir == 0 ? T - 1 - s : s;           // reverse of the forward order
+        const int cur = s & 1;
+        if (s > 0) {   // every peer's partial sums for this step have landed in recv[cur]
+            mbar_wait(rbar0 + 8 * cur, rphase[cur]);
+            rphase[cur] ^= 1u;
+        }
+        if (tid == 0) mbar_expect_tx(rbar0 + 8 * (cur ^ 1), STEP_BYTES);
+        // ---- gate derivatives for the own units ----
+        float o_ar[ITEMS], o_az[ITEMS], o_an[ITEMS], o_ghn[ITEMS];
+#pragma unroll
+        for (int it = 0; it < ITEMS; ++it) {
+            const int item = tid + it * S::THREADS;
+            if (item < RB * U) {
+                const int row = item / U, uu = item % U;
+                const int b = row0 + row;
+                float dar = 0.f, daz = 0.f, dan = 0.f, dghn_v = 0.f, carry = 0.f;
+                if (b < p.B) {
+                    float rec = dhz[item];
+#pragma unroll 4
+                    for (int src = 0; src < CS; ++src) rec += recv[((cur * CS + src) * RB + row) * U + uu];
+                    const float dh = rec + f_dout[it];
+                    const float r = f_r[it], z = f_z[it], n = f_n[it], ghn = f_ghn[it], hp = f_hp[it];
+                    const float dn = dh * (1.0f - z);
+                    const float dz = dh * (hp - n);
+                    carry = dh * z;
+                    dan = dn * (1.0f - n * n);
+                    dar = dan * ghn * r * (1.0f - r);
+                    daz = dz * z * (1.0f - z);
+                    dghn_v = dan * r;
+                }
+                o_ar[it] = dar, o_az[it] = daz, o_an[it] = dan, o_ghn[it] = dghn_v;
+                dhz[item] = carry;
+                bf16 hh, ll;
+                split_bf16(dar, hh, ll);
+                aop[row * AP + uu] = hh;
+                aop[RB * AP + row * AP + uu] = ll;
+                split_bf16(daz, hh, ll);
+                aop[row * AP + U + uu] = hh;
+                aop[RB * AP + row * AP + U + uu] = ll;
+                split_bf16(dghn_v, hh, ll);
+                aop[row * AP + 2 * U + uu] = hh;
+                aop[RB * AP + row * AP + 2 * U + uu] = ll;
+            }
+        }
+        prefetch(s + 1);
         __syncthreads();
         // ---- partial dh[16, units of CTA `warp`] = dgh[16, 96 own columns] . W_slice, scattered to its owner ----
         if (warp < CS) {
@@ -438,11 +529,47 @@ __global__ void __launch_bounds__(BwdSmem<H>::THREADS, 1) gru_bwd_kernel(const G
                 const uint32_t a0 = map_to_cta((uint32_t)__cvta_generic_to_shared(slot + g * U + nt * 8 + 2 * tq), (uint32_t)warp);
                 const uint32_t a1 =
                     map_to_cta((uint32_t)__cvta_generic_to_shared(slot + (g + 8) * U + nt * 8 + 2 * tq), (uint32_t)warp);
-                st_cluster_v2f(a0, acc[nt][0], acc[nt][1]);
-                st_cluster_v2f(a1, acc[nt][2], acc[nt][3]);
+                const uint32_t mb = map_to_cta(rbar0 + 8 * nxt, (uint32_t)warp);
+                st_async_v2f(a0, acc[nt][0], acc[nt][1], mb);
+                st_async_v2f(a1, acc[nt][2], acc[nt][3], mb);
             }
         }
-        cluster_sync_all();
+#pragma unroll
+        for (int it = 0; it < ITEMS; ++it) {
+            const int item = tid + it * S::THREADS;
+            const int row = item / U, uu = item % U;
+            const int b = row0 + row;
+            if (item < RB * U && b < p.B) {
+                const long m = (long)b * T + t;
+                const long so = ((long)dir * M + m) * H + u0 + uu;
+                const long go = m * gdim + dir * 3 * H + u0 + uu;
+                const long ho = ((long)dir * M + m) * 3 * H + u0 + uu;
+                const float dar = o_ar[it], daz = o_az[it], dan = o_an[it], dghn_v = o_ghn[it];
+                p.dgi[go] = dar;
+                p.dgi[go + H] = daz;
+                p.dgi[go + 2 * H] = dan;
+                bf16 hh, ll;
+                split_bf16(dar, hh, ll);
+                p.dgi_hi[go] = hh;
+                p.dgh_hi[ho] = hh;
+                if (p.dgi_lo) { p.dgi_lo[go] = ll; p.dgh_lo[ho] = ll; }
+                split_bf16(daz, hh, ll);
+                p.dgi_hi[go + H] = hh;
+                p.dgh_hi[ho + H] = hh;
+                if (p.dgi_lo) { p.dgi_lo[go + H] = ll; p.dgh_lo[ho + H] = ll; }
+                split_bf16(dan, hh, ll);
+                p.dgi_hi[go + 2 * H] = hh;
+                if (p.dgi_lo) p.dgi_lo[go + 2 * H] = ll;
+                split_bf16(dghn_v, hh, ll);
+                p.dgh_hi[ho + 2 * H] = hh;
+                if (p.dgh_lo) p.dgh_lo[ho + 2 * H] = ll;
+                p.dghn[so] = dghn_v;
+            }
+        }
+    }
+    {   // the partial sums of the last step (they only feed dh0) must land before anyone exits
+        const int cur = T & 1;
+        mbar_wait(rbar0 + 8 * cur, rphase[cur]);
     }
     // gradient w.r.t. the initial state (only consumed when hidden_start is learnable)
     if (p.dh0) {
@@ -456,6 +583,7 @@ __global__ void __launch_bounds__(BwdSmem<H>::THREADS, 1) gru_bwd_kernel(const G
             }
         }
     }
+    cluster_sync_all();   // no CTA may exit while a peer can still write into its shared memory
 }
 
 template <int H>
