@@ -35,6 +35,11 @@ def bench(name, m, n, k, three, a_mn=False, b_mn=False, split_k=1, bn=0, iters=2
 
 if __name__ == "__main__":
     M = 3776
+    if len(sys.argv) > 1 and sys.argv[1] == "prof":     # short run for ncu --set full: 4 launches per shape
+        for three in (True, False):
+            bench("ffn1 fwd (N=4096,K=1024)", M, 4096, 1024, three, bn=128, iters=1)
+            bench("ffn2 fwd (N=1024,K=4096)", M, 1024, 4096, three, bn=256, iters=1)
+        sys.exit(0)
     for three in (True, False):
         for bn in (128, 256):
             bench("ffn1 fwd (N=4096,K=1024)", M, 4096, 1024, three, bn=bn)

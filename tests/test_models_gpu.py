@@ -109,12 +109,18 @@ def test_dropout_training_is_finite_and_seeded():
 
     def loss_at(Pd, seed):
         logits, _, _, saved = eng.forward(Pd, x, day, True, seed)
-        loss, _, dl = ops.ctc_fwd_bwd(logits, tg, lens, tl)
+        loss, nll, dl = ops.ctc_fwd_bwd(logits, tg, lens, tl)
+        loss_at.nll = nll.clone()
         return loss, saved, dl
     l1, saved, dl = loss_at(P, 5)
+    n1 = loss_at.nll
     l1b, _, _ = loss_at(P, 5)
+    n1b = loss_at.nll
     l2, _, _ = loss_at(P, 6)
-    assert torch.isfinite(l1) and l1.item() == l1b.item() and l1.item() != l2.item()
+    # the forward is deterministic per trial (same seed -> bit-identical negative log-likelihoods); the batch
+    # mean is an atomicAdd over trials, so the scalar may differ by an ulp with the arrival order
+    assert torch.isfinite(l1) and torch.equal(n1, n1b) and abs(l1.item() - l1b.item()) <= 2e-6 * abs(l1.item())
+    assert abs(l1.item() - l2.item()) > 1e-5 * abs(l1.item())
     G = eng.backward(P, saved, dl)
     # directional derivative along the gradient of a few parameter tensors
     keys = ["brain_encoder.day_weights", "brain_encoder.neural_decoder.encoder.gru.weight_hh_l0",
