@@ -308,7 +308,10 @@ def gemm_roofline(model, opt, batch, step, peaks):
         real(a, b, **kw)
         e.record()
         k_eff = kw["k"] * (a.d2 if kw.get("k_spans_batches") else 1)
-        rec.append((s, e, 2.0 * kw["m_per_batch"] * kw.get("batches", 1) * kw["n"] * k_eff))
+        rec.append((s, e, 2.0 * kw["m_per_batch"] * kw.get("batches", 1) * kw["n"] * k_eff,
+                    (kw["m_per_batch"], kw.get("batches", 1), kw["n"], k_eff, "A" + ("mn" if a.mn_major else "k"),
+                     "B" + ("mn" if b.mn_major else "k"), "sk%d" % kw.get("split_k", 1), "bn%d" % kw.get("block_n", 0),
+                     "+".join(x for x in ("out_f32", "out_pre", "out_hi", "bias", "residual", "aux", "colsum", "act") if kw.get(x) is not None))))
     ops.gemm = timed_gemm
     try:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -320,8 +323,17 @@ def gemm_roofline(model, opt, batch, step, peaks):
         torch.cuda.synchronize()
     finally:
         ops.gemm = real
-    t_ms = sum(s.elapsed_time(e) for s, e, _ in rec)
-    flops = sum(f for _, _, f in rec)
+    t_ms = sum(r[0].elapsed_time(r[1]) for r in rec)
+    flops = sum(r[2] for r in rec)
+    table = os.environ.get("B2T_GEMM_TABLE")
+    if table:   # per-shape breakdown of the step's GEMM launches (debug aid, not part of the JSON line)
+        agg = {}
+        for s, e, f, key in rec:
+            c = agg.setdefault(key, [0, 0.0, 0.0])
+            c[0] += 1; c[1] += s.elapsed_time(e) * 1e3; c[2] += f
+        with open(table, "w") as fh:
+            for key, (n, us, f) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+                fh.write(f"{n:4d} x {us / n:8.1f} us = {us:9.1f} us  {f / us / 1e6:7.1f} TF/s alg  {key}\n")
     step_ms = e0.elapsed_time(e1)
     achieved = flops / (t_ms * 1e-3) / 1e12
     peak = peaks["bf16_tflops_sustained"]

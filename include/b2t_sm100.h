@@ -80,9 +80,20 @@ typedef struct {
     /* value is multiplied by out_scale after act / act'(aux) / dropout and before the residual
      * (the conformer's half-step feed-forward, modeling_wav2vec2_conformer.py:602,625); 0 reads as 1 */
     float    out_scale;
+    /* stream-K schedule.  sk_workspace: caller-owned device scratch of b2t_gemm_workspace_bytes() bytes,
+     * ZEROED ONCE at allocation (the kernel leaves its flags at zero), used by one stream at a time;
+     * NULL = whole-tile schedule.  stream_k: 0 auto (when the tile count leaves SMs idle in the last wave, or
+     * split_k > 1 was asked for: the k-blocks of all tiles are cut into one equal range per SM, partial tiles
+     * are summed through the workspace and the owner CTA runs the full fused epilogue, so no red.add and no
+     * epilogue restriction), 1 force, -1 off. */
+    void*    sk_workspace;
+    int64_t  sk_workspace_bytes;
+    int32_t  stream_k;
 } b2t_gemm_args;
 
 int b2t_gemm(const b2t_gemm_args* args, b2t_stream stream);
+/* bytes of b2t_gemm_args.sk_workspace that cover every tile shape on the current device */
+int64_t b2t_gemm_workspace_bytes(void);
 
 /* plain fp32 SIMT GEMM  C[m,n] = sum_k A(m,k) B(n,k) (+bias[n]); element strides; a debugging
  * cross-check for b2t_gemm, never used by the product path. */

@@ -33,21 +33,82 @@ def bench(name, m, n, k, three, a_mn=False, b_mn=False, split_k=1, bn=0, iters=2
     print(f"{name:34s} m={m:5d} n={n:5d} k={k:5d} terms={'3' if three else '1'} bn={bn or 'auto':>4} splitk={split_k:2d}  {us:8.1f} us  "
           f"{tf:7.1f} TF/s alg  {tf * (3 if three else 1):7.1f} TF/s mma", flush=True)
 
+def bench_epi(name, m, n, k, bn=128, b_mn=False, iters=20, **flags):
+    """ffn-shaped GEMM with a chosen set of fused epilogue stages (bf16x3)."""
+    dev = "cuda"
+    ncopy = 3
+    As = [ops.split(torch.randn(m, k, device=dev), True) for _ in range(ncopy)]
+    Bs = [ops.split(torch.randn((k, n) if b_mn else (n, k), device=dev), True) for _ in range(ncopy)]
+    kw = {}
+    if flags.get("f32"): kw["out_f32"] = torch.empty(m, n, device=dev)
+    if flags.get("pre"): kw["out_pre"] = torch.empty(m, n, device=dev)
+    if flags.get("hi"):
+        kw["out_hi"] = torch.empty(m, n, device=dev, dtype=torch.bfloat16)
+        kw["out_lo"] = torch.empty(m, n, device=dev, dtype=torch.bfloat16)
+    if flags.get("bias"): kw["bias"] = torch.randn(n, device=dev)
+    if flags.get("res"): kw["residual"] = torch.randn(m, n, device=dev)
+    if flags.get("aux"): kw["aux"] = torch.randn(m, n, device=dev); kw["aux_mode"] = flags["aux"]
+    if flags.get("colsum"): kw["colsum"] = torch.zeros(n, device=dev)
+    if flags.get("act"): kw["act"] = flags["act"]
+    if flags.get("drop"): kw["drop_p"] = 0.1; kw["drop_seed"] = 7
+    def run(i):
+        a, b = As[i % ncopy], Bs[i % ncopy]
+        ops.gemm(ops.kmajor(*a), ops.mnmajor(*b) if b_mn else ops.kmajor(*b), m_per_batch=m, n=n, k=k, block_n=bn, **kw)
+    for i in range(3): run(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(iters): run(i)
+    e1.record(); torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) / iters * 1e3
+    print(f"{name:44s} bn={bn} {us:8.1f} us  {2.0 * m * n * k / us / 1e6:7.1f} TF/s alg", flush=True)
+
+
 if __name__ == "__main__":
     M = 3776
+    if len(sys.argv) > 1 and sys.argv[1] == "epi":
+        ops.STREAM_K = False
+        for bn in (128, 256):
+            for nm, fl in [("f32", dict(f32=1)), ("hi/lo", dict(hi=1)), ("f32+hi/lo", dict(f32=1, hi=1)), ("hi/lo+aux(silu')", dict(hi=1, aux="silu")),
+                           ("hi/lo+aux(gelu')", dict(hi=1, aux="gelu")), ("hi/lo+colsum", dict(hi=1, colsum=1)),
+                           ("hi/lo+aux(silu')+colsum", dict(hi=1, aux="silu", colsum=1)),
+                           ("pre+hi/lo+bias+silu", dict(pre=1, hi=1, bias=1, act="silu")),
+                           ("pre+hi/lo+bias+gelu", dict(pre=1, hi=1, bias=1, act="gelu")),
+                           ("hi/lo+bias+silu", dict(hi=1, bias=1, act="silu")), ("pre+hi/lo", dict(pre=1, hi=1)),
+                           ("f32+bias", dict(f32=1, bias=1)), ("f32+bias+res", dict(f32=1, bias=1, res=1)),
+                           ("f32+bias+drop+res", dict(f32=1, bias=1, res=1, drop=1))]:
+                bench_epi("ffn1 " + nm, M, 4096, 1024, bn=bn, **fl)
+            bench_epi("outproj f32+bias+res", M, 1024, 1024, bn=bn, f32=1, bias=1, res=1)
+            bench_epi("outproj f32", M, 1024, 1024, bn=bn, f32=1)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "prof":     # short run for ncu --set full: 4 launches per shape
+        ops.STREAM_K = False
+        if len(sys.argv) > 2:     # component timing with B2T_GEMM_DEBUG set by the caller
+            for bn in (128, 256):
+                bench("ffn1 fwd (N=4096,K=1024)", M, 4096, 1024, True, bn=bn)
+                bench("ffn2 fwd (N=1024,K=4096)", M, 1024, 4096, True, bn=bn)
+                bench("out proj (N=1024,K=1024)", M, 1024, 1024, True, bn=bn)
+                bench("big square 8192^3", 8192, 8192, 8192, True, bn=bn, iters=3)
+            sys.exit(0)
         for three in (True, False):
             bench("ffn1 fwd (N=4096,K=1024)", M, 4096, 1024, three, bn=128, iters=1)
             bench("ffn2 fwd (N=1024,K=4096)", M, 1024, 4096, three, bn=256, iters=1)
         sys.exit(0)
-    for three in (True, False):
-        for bn in (128, 256):
-            bench("ffn1 fwd (N=4096,K=1024)", M, 4096, 1024, three, bn=bn)
-            bench("ffn2 fwd (N=1024,K=4096)", M, 1024, 4096, three, bn=bn)
-            bench("qk proj (N=2048,K=1024)", M, 2048, 1024, three, bn=bn)
-            bench("ffn1 fwd split out", M, 4096, 1024, three, bn=bn, out="split")
-            bench("dgrad ffn2 (B mn-major)", M, 4096, 1024, three, b_mn=True, bn=bn)
-            bench("wgrad ffn1 (both mn-major)", 4096, 1024, M, three, a_mn=True, b_mn=True, bn=bn)
-            bench("wgrad 1024x1024 splitk", 1024, 1024, M, three, a_mn=True, b_mn=True, split_k=2, bn=bn)
-        bench("big square 8192^3", 8192, 8192, 8192, three, bn=128, iters=5)
-        bench("big square 8192^3", 8192, 8192, 8192, three, bn=256, iters=5)
+    for sk in (False, True):
+        ops.STREAM_K = sk
+        print(f"--- stream-K {'on' if sk else 'off'}", flush=True)
+        for three in ((True, False) if not sk or len(sys.argv) > 1 else (True,)):
+            for bn in (128, 256):
+                bench("ffn1 fwd (N=4096,K=1024)", M, 4096, 1024, three, bn=bn)
+                bench("ffn2 fwd (N=1024,K=4096)", M, 1024, 4096, three, bn=bn)
+                bench("qk proj (N=2048,K=1024)", M, 2048, 1024, three, bn=bn)
+                bench("out proj (N=1024,K=1024)", M, 1024, 1024, three, bn=bn)
+                bench("ffn1 fwd split out", M, 4096, 1024, three, bn=bn, out="split")
+                bench("dgrad ffn2 (B mn-major)", M, 4096, 1024, three, b_mn=True, bn=bn)
+                bench("wgrad ffn1 (both mn-major)", 4096, 1024, M, three, a_mn=True, b_mn=True, bn=bn)
+                bench("wgrad 1024x1024 splitk", 1024, 1024, M, three, a_mn=True, b_mn=True, split_k=2, bn=bn)
+                bench("base ffn1 (M=7552,N=3072,K=768)", 7552, 3072, 768, three, bn=bn)
+                bench("base ffn2 (M=7552,N=768,K=3072)", 7552, 768, 3072, three, bn=bn)
+                bench("base qkv (M=7552,N=2304,K=768)", 7552, 2304, 768, three, bn=bn)
+            bench("big square 8192^3", 8192, 8192, 8192, three, bn=128, iters=5)
+            bench("big square 8192^3", 8192, 8192, 8192, three, bn=256, iters=5)

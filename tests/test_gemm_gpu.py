@@ -189,3 +189,42 @@ def test_simt_debug_gemm():
     a, b, bias = rnd(70, 50, seed=23), rnd(40, 50, seed=24), rnd(40, seed=25)
     out = ops.gemm_simt(a, b, bias)
     assert rel(out, a.double() @ b.double().t() + bias.double()) < 1e-5
+
+
+@pytest.mark.parametrize("bn", [64, 128, 256])
+@pytest.mark.parametrize("m,n,k", [(260, 328, 256), (1000, 768, 520), (3776, 1024, 1024), (128, 128, 4096)])
+def test_stream_k_full_epilogue(bn, m, n, k):
+    """stream-K schedule (k-block ranges per CTA, partial tiles summed through the workspace by the owner CTA)
+    with every fused epilogue stage on; twice in a row (the flags must be left clean)."""
+    ops = _ops()
+    a, b = rnd(m, k, seed=5, scale=0.3), rnd(n, k, seed=6, scale=0.3)
+    bias, res = rnd(n, seed=7), rnd(m, n, seed=8)
+    ah, al = ops.split(a)
+    bh, bl = ops.split(b)
+    z = 0.5 * (a.double() @ b.double().t()) + bias.double()
+    ref = torch.nn.functional.gelu(z) + res.double()
+    for _ in range(2):
+        out = torch.full((m, n), float("nan"), device="cuda")
+        pre = torch.empty(m, n, device="cuda")
+        hi = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
+        lo = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
+        colsum = torch.zeros(n, device="cuda")
+        ops.gemm(ops.kmajor(ah, al), ops.kmajor(bh, bl), m_per_batch=m, n=n, k=k, out_f32=out, out_pre=pre, out_hi=hi,
+                 out_lo=lo, bias=bias, residual=res, colsum=colsum, act="gelu", alpha=0.5, block_n=bn, stream_k=1)
+        assert rel(pre, z) < 2e-5
+        assert rel(out, ref) < 2e-5
+        assert rel(hi.double() + lo.double(), ref) < 3e-5
+        assert rel(colsum, ref.sum(0)) < 1e-4
+
+
+@pytest.mark.parametrize("stream_k", [-1, 1])
+def test_stream_k_wgrad_shape(stream_k):
+    """weight-gradient shape (both operands MN-major, long K, few tiles): stream-K replaces split-K + red.add."""
+    ops = _ops()
+    m, n, k = 512, 384, 3776
+    a, b = rnd(m, k, seed=9), rnd(n, k, seed=10)
+    ah, al = ops.split(a, True, transpose=True)
+    bh, bl = ops.split(b, True, transpose=True)
+    out = torch.full((m, n), float("nan"), device="cuda")
+    ops.gemm(ops.mnmajor(ah, al), ops.mnmajor(bh, bl), m_per_batch=m, n=n, k=k, out_f32=out, stream_k=stream_k)
+    assert rel(out, a.double() @ b.double().t()) < 2e-5

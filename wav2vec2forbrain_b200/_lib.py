@@ -41,6 +41,7 @@ class GemmArgs(ctypes.Structure):
         ("alpha", c_float), ("block_n", c_int32),
         ("drop_p", c_float), ("drop_seed", ctypes.c_uint64), ("bias_batch_stride", c_int64),
         ("out_scale", c_float),
+        ("sk_workspace", c_void_p), ("sk_workspace_bytes", c_int64), ("stream_k", c_int32),
     ]
 
 
@@ -54,6 +55,7 @@ def lib() -> ctypes.CDLL:
         _lib = ctypes.CDLL(LIB_PATH)
         _lib.b2t_last_error.restype = ctypes.c_char_p
         _lib.b2t_abi_version.restype = c_int
+        _lib.b2t_gemm_workspace_bytes.restype = c_int64
     return _lib
 
 

@@ -29,6 +29,7 @@ constexpr int UMMA_K = 16;
 constexpr int NUM_THREADS = 320;       // warp 0 TMA, warp 1 MMA, warps 2-9 epilogue
 constexpr int NUM_EPI_WARPS = 8;
 constexpr int SMEM_LIMIT = 227 * 1024;
+constexpr int SK_FLAG_BYTES = 1024;    // stream-K workspace: 256 int flags, then gridDim.x fp32 tile slots
 
 struct KParams {
     int m_per_batch, batches, n, num_k_blocks, k_chunks_per_slice;
@@ -48,8 +49,74 @@ struct KParams {
     float alpha;
     float drop_p, drop_scale, out_scale;
     int vec4;
+    int debug;   // B2T_GEMM_DEBUG (profiling aid): 1 skip the epilogue body, 2 skip MMA issue, 4 skip TMA loads
+    uint32_t flags;
     unsigned long long drop_seed;
     int m_tiles, n_tiles, total_items;
+    // stream-K: the tiles' k-blocks form one line of `sk_units` units cut into gridDim.x equal ranges
+    int stream_k;
+    long long sk_units;
+    float* sk_ws;      // [gridDim.x][BM * BN] fp32 partial accumulators
+    int* sk_flags;     // [gridDim.x] arrivals of partials at the tile's owner CTA (self-cleaning)
+};
+
+// One unit of work of a CTA.  mode 0: whole tile (or a legacy split-K slice, reduced with red.add);
+// stream-K: mode 1 = contributor (k-range does not start the tile: raw partial -> workspace, signal the
+// owner), mode 2 = owner (k-range starts the tile but does not finish it: waits for the n_contrib
+// following CTAs' partials, adds them, runs the fused epilogue).
+struct Item {
+    int split, batch, m_blk, n_blk, kb0, kb1, mode, n_contrib, owner;
+};
+
+struct Sched {
+    const KParams& p;
+    int item;
+    long long u, u_end;
+    __device__ __forceinline__ explicit Sched(const KParams& p_) : p(p_), item((int)blockIdx.x), u(0), u_end(0) {
+        if (p.stream_k) {
+            u = (long long)blockIdx.x * p.sk_units / gridDim.x;
+            u_end = (long long)(blockIdx.x + 1) * p.sk_units / gridDim.x;
+        }
+    }
+    __device__ __forceinline__ void decode_tile(int t, Item& it) const {
+        it.n_blk = t % p.n_tiles;
+        t /= p.n_tiles;
+        it.m_blk = t % p.m_tiles;
+        it.batch = t / p.m_tiles;
+    }
+    __device__ __forceinline__ bool next(Item& it) {
+        if (!p.stream_k) {
+            if (item >= p.total_items) return false;
+            const int per_split = p.n_tiles * p.m_tiles * p.batches;
+            it.split = item / per_split;
+            decode_tile(item - it.split * per_split, it);
+            it.kb0 = (int)(((long long)it.split * p.num_k_blocks) / p.split_k);
+            it.kb1 = (int)(((long long)(it.split + 1) * p.num_k_blocks) / p.split_k);
+            it.mode = 0, it.n_contrib = 0, it.owner = 0;
+            item += gridDim.x;
+            return true;
+        }
+        if (u >= u_end) return false;
+        const long long KB = p.num_k_blocks, G = gridDim.x;
+        const long long t = u / KB, t0 = t * KB;
+        const long long e = u_end < t0 + KB ? u_end : t0 + KB;
+        it.split = 0;
+        decode_tile((int)t, it);
+        it.kb0 = (int)(u - t0);
+        it.kb1 = (int)(e - t0);
+        it.n_contrib = 0, it.owner = 0;
+        if (it.kb0 == 0 && it.kb1 == KB) {
+            it.mode = 0;
+        } else if (it.kb0 == 0) {
+            it.mode = 2;   // CTA holding unit x is ((x + 1) * G - 1) / units
+            it.n_contrib = (int)(((t0 + KB) * G - 1) / p.sk_units) - (int)blockIdx.x;
+        } else {
+            it.mode = 1;
+            it.owner = (int)(((t0 + 1) * G - 1) / p.sk_units);
+        }
+        u = e;
+        return true;
+    }
 };
 
 // ------------------------------------------------------------------------------------------
@@ -90,6 +157,15 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map
         "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
         ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
         : "memory");
+}
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(pred));
+    return pred != 0;
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -171,11 +247,31 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
+__device__ __forceinline__ int ld_acquire_gpu(const int* p) {
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void red_release_gpu_add(int* p, int v) {
+    asm volatile("red.release.gpu.global.add.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
 __device__ __forceinline__ void tmem_ld_32x8(uint32_t taddr, float* v) {
     uint32_t* r = reinterpret_cast<uint32_t*>(v);
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
                  : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+__device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, float (&a)[8], float (&b)[8]) {
+    uint32_t* r = reinterpret_cast<uint32_t*>(a);
+    uint32_t* q = reinterpret_cast<uint32_t*>(b);
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(q[0]),
+          "=r"(q[1]), "=r"(q[2]), "=r"(q[3]), "=r"(q[4]), "=r"(q[5]), "=r"(q[6]), "=r"(q[7])
+        : "r"(taddr));
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
@@ -201,48 +297,85 @@ __device__ __forceinline__ float warp_colsum8(const float (&v)[8], int lane, int
     return c;
 }
 
+__device__ __forceinline__ void ld_f8_cg(const float* a, float (&t)[8]) {
+    const float4 t0 = __ldcg(reinterpret_cast<const float4*>(a));
+    const float4 t1 = __ldcg(reinterpret_cast<const float4*>(a + 4));
+    t[0] = t0.x, t[1] = t0.y, t[2] = t0.z, t[3] = t0.w, t[4] = t1.x, t[5] = t1.y, t[6] = t1.z, t[7] = t1.w;
+}
+
 // Fused epilogue on 8 consecutive columns of one output row held in registers.  Every stage is its
 // own short loop with the mode branch hoisted out of it: the executed instruction footprint stays
 // small (a fully unrolled 32-column body with all modes inline thrashed the instruction cache).
 // off0 = element offset of (row, col0); nvalid = columns inside N (8, or 4 at the edge on the VEC
 // path; anything in 1..8 on the scalar path).
+// epilogue stage bits (KParams::flags, held in ONE register for the whole kernel: testing p.<field> per
+// slab cost an LDCU + UISETP + branch per stage per 8 columns)
+enum : uint32_t {
+    F_ALPHA = 1u << 0, F_BIAS = 1u << 1, F_PRE = 1u << 2, F_ACT = 1u << 3, F_AUX = 1u << 4, F_DROP = 1u << 5,
+    F_SCALE = 1u << 6, F_RES = 1u << 7, F_F32 = 1u << 8, F_ATOMIC = 1u << 9, F_HI = 1u << 10, F_LO = 1u << 11,
+    F_COLSUM = 1u << 12, F_VEC = 1u << 13,
+};
+
+__device__ __forceinline__ void st_f8(float* o, const float (&v)[8], int nvalid) {
+    *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
+    if (nvalid > 4) *reinterpret_cast<float4*>(o + 4) = make_float4(v[4], v[5], v[6], v[7]);
+}
+__device__ __forceinline__ void ld_f8(const float* a, float (&t)[8], int nvalid) {
+    const float4 t0 = *reinterpret_cast<const float4*>(a);
+    const float4 t1 = nvalid > 4 ? *reinterpret_cast<const float4*>(a + 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    t[0] = t0.x, t[1] = t0.y, t[2] = t0.z, t[3] = t0.w, t[4] = t1.x, t[5] = t1.y, t[6] = t1.z, t[7] = t1.w;
+}
+
+// Fused epilogue on 8 consecutive columns of one output row held in registers.  Every stage is its
+// own short loop behind one register-bit test: the executed instruction footprint stays small (a fully
+// unrolled 32-column body with all modes inline thrashed the instruction cache).
+// off0 = element offset of (row, col0); nvalid = columns inside N (8, or 4 at the edge on the VEC
+// path; anything in 1..8 on the scalar path).
 template <bool VEC>
-__device__ __forceinline__ void epi_cols8(const KParams& p, float (&v)[8], long long off0, int col0, int nvalid, bool row_ok,
-                                          const float* bias_ptr, int lane) {
+__device__ __forceinline__ void epi_cols8(const KParams& p, const uint32_t F, float (&v)[8], long long off0, int col0,
+                                          int nvalid, bool row_ok, const float* bias_ptr, int lane) {
     if (row_ok) {
+        if (F & F_ALPHA) {
 #pragma unroll
-        for (int e = 0; e < 8; ++e) v[e] = e < nvalid ? v[e] * p.alpha : 0.0f;
-        if (bias_ptr) {
-#pragma unroll
-            for (int e = 0; e < 8; ++e)
-                if (e < nvalid) v[e] += bias_ptr[col0 + e];
+            for (int e = 0; e < 8; ++e) v[e] *= p.alpha;
         }
-        if (p.out_pre) {
+        if (bias_ptr) {
             if (VEC) {
-                *reinterpret_cast<float4*>(p.out_pre + off0) = make_float4(v[0], v[1], v[2], v[3]);
-                if (nvalid > 4) *reinterpret_cast<float4*>(p.out_pre + off0 + 4) = make_float4(v[4], v[5], v[6], v[7]);
+                float t[8];
+                ld_f8(bias_ptr + col0, t, nvalid);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) v[e] += t[e];
+            } else {
+#pragma unroll
+                for (int e = 0; e < 8; ++e)
+                    if (e < nvalid) v[e] += bias_ptr[col0 + e];
+            }
+        }
+        if (F & F_PRE) {
+            if (VEC) {
+                st_f8(p.out_pre + off0, v, nvalid);
             } else {
 #pragma unroll
                 for (int e = 0; e < 8; ++e)
                     if (e < nvalid) p.out_pre[off0 + e] = v[e];
             }
         }
-        if (p.act == 1) {
+        if (F & F_ACT) {
+            if (p.act == 1) {
 #pragma unroll
-            for (int e = 0; e < 8; ++e) v[e] = gelu_erf(v[e]);
-        } else if (p.act == 2) {
+                for (int e = 0; e < 8; ++e) v[e] = gelu_erf(v[e]);
+            } else if (p.act == 2) {
 #pragma unroll
-            for (int e = 0; e < 8; ++e) v[e] = silu_f(v[e]);
-        } else if (p.act == 3) {
+                for (int e = 0; e < 8; ++e) v[e] = silu_f(v[e]);
+            } else {
 #pragma unroll
-            for (int e = 0; e < 8; ++e) v[e] = v[e] / (1.0f + fabsf(v[e]));
+                for (int e = 0; e < 8; ++e) v[e] = v[e] / (1.0f + fabsf(v[e]));
+            }
         }
-        if (p.aux_mode) {
+        if (F & F_AUX) {
             float a[8];
             if (VEC) {
-                const float4 t0 = *reinterpret_cast<const float4*>(p.aux + off0);
-                const float4 t1 = nvalid > 4 ? *reinterpret_cast<const float4*>(p.aux + off0 + 4) : make_float4(0.f, 0.f, 0.f, 0.f);
-                a[0] = t0.x, a[1] = t0.y, a[2] = t0.z, a[3] = t0.w, a[4] = t1.x, a[5] = t1.y, a[6] = t1.z, a[7] = t1.w;
+                ld_f8(p.aux + off0, a, nvalid);
             } else {
 #pragma unroll
                 for (int e = 0; e < 8; ++e) a[e] = e < nvalid ? p.aux[off0 + e] : 0.0f;
@@ -261,43 +394,45 @@ __device__ __forceinline__ void epi_cols8(const KParams& p, float (&v)[8], long 
                 }
             }
         }
-        if (p.drop_p > 0.0f) {
+        if (F & F_DROP) {
 #pragma unroll
             for (int e = 0; e < 8; ++e)
                 v[e] = hash_uniform(p.drop_seed, (unsigned long long)(off0 + e)) < p.drop_p ? 0.0f : v[e] * p.drop_scale;
         }
-        if (p.out_scale != 1.0f) {
+        if (F & F_SCALE) {
 #pragma unroll
             for (int e = 0; e < 8; ++e) v[e] *= p.out_scale;
         }
-        if (p.residual) {
+        if (F & F_RES) {
             if (VEC) {
-                const float4 t0 = *reinterpret_cast<const float4*>(p.residual + off0);
-                const float4 t1 = nvalid > 4 ? *reinterpret_cast<const float4*>(p.residual + off0 + 4) : make_float4(0.f, 0.f, 0.f, 0.f);
-                v[0] += t0.x, v[1] += t0.y, v[2] += t0.z, v[3] += t0.w, v[4] += t1.x, v[5] += t1.y, v[6] += t1.z, v[7] += t1.w;
+                float t[8];
+                ld_f8(p.residual + off0, t, nvalid);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) v[e] += t[e];
             } else {
 #pragma unroll
                 for (int e = 0; e < 8; ++e)
                     if (e < nvalid) v[e] += p.residual[off0 + e];
             }
         }
+        if (nvalid < 8) {
 #pragma unroll
-        for (int e = 0; e < 8; ++e) v[e] = e < nvalid ? v[e] : 0.0f;
-        if (p.out_f32) {
+            for (int e = 0; e < 8; ++e) v[e] = e < nvalid ? v[e] : 0.0f;
+        }
+        if (F & F_F32) {
             float* o = p.out_f32 + off0;
             if (VEC) {
-                if (p.atomic) {
+                if (F & F_ATOMIC) {
                     red_add_v4(o, v[0], v[1], v[2], v[3]);
                     if (nvalid > 4) red_add_v4(o + 4, v[4], v[5], v[6], v[7]);
                 } else {
-                    *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
-                    if (nvalid > 4) *reinterpret_cast<float4*>(o + 4) = make_float4(v[4], v[5], v[6], v[7]);
+                    st_f8(o, v, nvalid);
                 }
             } else {
 #pragma unroll
                 for (int e = 0; e < 8; ++e) {
                     if (e < nvalid) {
-                        if (p.atomic)
+                        if (F & F_ATOMIC)
                             atomicAdd(o + e, v[e]);
                         else
                             o[e] = v[e];
@@ -305,7 +440,7 @@ __device__ __forceinline__ void epi_cols8(const KParams& p, float (&v)[8], long 
                 }
             }
         }
-        if (p.out_hi) {
+        if (F & F_HI) {
             bf16 h[8], l[8];
 #pragma unroll
             for (int e = 0; e < 8; ++e) split_bf16(v[e], h[e], l[e]);
@@ -314,20 +449,21 @@ __device__ __forceinline__ void epi_cols8(const KParams& p, float (&v)[8], long 
                     __nv_bfloat162 t = __halves2bfloat162(a, b);
                     return *reinterpret_cast<uint32_t*>(&t);
                 };
-                const uint2 h0 = make_uint2(pk(h[0], h[1]), pk(h[2], h[3])), h1 = make_uint2(pk(h[4], h[5]), pk(h[6], h[7]));
-                *reinterpret_cast<uint2*>(p.out_hi + off0) = h0;
-                if (nvalid > 4) *reinterpret_cast<uint2*>(p.out_hi + off0 + 4) = h1;
-                if (p.out_lo) {
-                    const uint2 l0 = make_uint2(pk(l[0], l[1]), pk(l[2], l[3])), l1 = make_uint2(pk(l[4], l[5]), pk(l[6], l[7]));
-                    *reinterpret_cast<uint2*>(p.out_lo + off0) = l0;
-                    if (nvalid > 4) *reinterpret_cast<uint2*>(p.out_lo + off0 + 4) = l1;
+                if (nvalid > 4) {
+                    *reinterpret_cast<uint4*>(p.out_hi + off0) = make_uint4(pk(h[0], h[1]), pk(h[2], h[3]), pk(h[4], h[5]), pk(h[6], h[7]));
+                    if (F & F_LO)
+                        *reinterpret_cast<uint4*>(p.out_lo + off0) =
+                            make_uint4(pk(l[0], l[1]), pk(l[2], l[3]), pk(l[4], l[5]), pk(l[6], l[7]));
+                } else {
+                    *reinterpret_cast<uint2*>(p.out_hi + off0) = make_uint2(pk(h[0], h[1]), pk(h[2], h[3]));
+                    if (F & F_LO) *reinterpret_cast<uint2*>(p.out_lo + off0) = make_uint2(pk(l[0], l[1]), pk(l[2], l[3]));
                 }
             } else {
 #pragma unroll
                 for (int e = 0; e < 8; ++e) {
                     if (e < nvalid) {
                         p.out_hi[off0 + e] = h[e];
-                        if (p.out_lo) p.out_lo[off0 + e] = l[e];
+                        if (F & F_LO) p.out_lo[off0 + e] = l[e];
                     }
                 }
             }
@@ -336,7 +472,7 @@ __device__ __forceinline__ void epi_cols8(const KParams& p, float (&v)[8], long 
 #pragma unroll
         for (int e = 0; e < 8; ++e) v[e] = 0.0f;   // outside the matrix: contributes nothing to column sums
     }
-    if (p.colsum) {   // warp-uniform
+    if (F & F_COLSUM) {   // warp-uniform
         int cl;
         const float s = warp_colsum8(v, lane, cl);
         if ((lane & 3) == 0 && cl < nvalid) atomicAdd(p.colsum + col0 + cl, s);
@@ -392,33 +528,28 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr_gen;
 
-    auto decode_item = [&](int item, int& split, int& batch, int& m_blk, int& n_blk) {
-        n_blk = item % p.n_tiles;
-        int t = item / p.n_tiles;
-        m_blk = t % p.m_tiles;
-        t /= p.m_tiles;
-        batch = t % p.batches;
-        split = t / p.batches;
-    };
-    auto k_range = [&](int split, int& kb0, int& kb1) {
-        kb0 = (int)(((long long)split * p.num_k_blocks) / p.split_k);
-        kb1 = (int)(((long long)(split + 1) * p.num_k_blocks) / p.split_k);
-    };
-
     if (warp == 0) {
         // ================================ TMA producer ================================
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
-                int split, batch, m_blk, n_blk, kb0, kb1;
-                decode_item(item, split, batch, m_blk, n_blk);
-                k_range(split, kb0, kb1);
+            Sched sch(p);
+            Item it;
+            while (sch.next(it)) {
+                const int batch = it.batch, m_blk = it.m_blk, n_blk = it.n_blk, kb0 = it.kb0, kb1 = it.kb1;
                 const int bbatch = p.b_batch_idx ? p.b_batch_idx[batch] : (p.b_batched ? batch : 0);
                 const int abatch = p.a_batched ? batch : 0;
                 for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(empty_bar(stage), phase ^ 1u);
                     const uint32_t fb = full_bar(stage);
+                    if (p.debug & 4) {
+                        mbar_arrive(fb);
+                        if (++stage == C::STAGES) {
+                            stage = 0;
+                            phase ^= 1u;
+                        }
+                        continue;
+                    }
                     mbar_expect_tx(fb, (uint32_t)C::STAGE_BYTES);
                     const uint32_t sA = smem_base + stage * C::STAGE_BYTES;
                     const uint32_t sB = sA + (NTERMS == 3 ? 2 : 1) * C::A_BYTES;
@@ -457,50 +588,60 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
         }
     } else if (warp == 1) {
         // ================================ MMA issuer ==================================
-        if (lane == 0) {
-            constexpr uint32_t idesc = make_idesc(BM, BN, A_MN, B_MN);
-            // K-major SW128: 8-row groups 1024 B apart (SBO), k-step = +32 B inside the swizzle row
-            // MN-major SW128: 64-element MN atoms BK*128 B apart (LBO), 8 k-rows = 1024 B (SBO),
-            //                 k-step of 16 rows = +2048 B
-            constexpr uint32_t A_LBO = A_MN ? BK * 128 : 0, B_LBO = B_MN ? BK * 128 : 0;
-            constexpr uint32_t A_KSTEP = A_MN ? UMMA_K * 128 : UMMA_K * 2, B_KSTEP = B_MN ? UMMA_K * 128 : UMMA_K * 2;
-            int stage = 0;
-            uint32_t phase = 0;
-            int local_iter = 0;
-            for (int item = blockIdx.x; item < p.total_items; item += gridDim.x, ++local_iter) {
-                int split, batch, m_blk, n_blk, kb0, kb1;
-                decode_item(item, split, batch, m_blk, n_blk);
-                k_range(split, kb0, kb1);
-                const int acc = local_iter & 1;
-                const uint32_t acc_phase = (uint32_t)(local_iter >> 1) & 1u;
-                mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+        // The WHOLE warp walks the loops so that every address / descriptor stays warp-uniform (uniform
+        // registers feed UTCHMMA directly); one elected lane issues the tcgen05 instructions.  With the loop
+        // inside `if (lane == 0)` ptxas rebuilt each descriptor in vector registers and moved it over with
+        // R2UR per MMA: ~230 instructions per k-block, slower than the 12 MMAs they issue (ncu, round 1).
+        constexpr uint32_t idesc = make_idesc(BM, BN, A_MN, B_MN);
+        // K-major SW128: 8-row groups 1024 B apart (SBO), k-step = +32 B inside the swizzle row
+        // MN-major SW128: 64-element MN atoms BK*128 B apart (LBO), 8 k-rows = 1024 B (SBO),
+        //                 k-step of 16 rows = +2048 B
+        constexpr uint32_t A_LBO = A_MN ? BK * 128 : 0, B_LBO = B_MN ? BK * 128 : 0;
+        constexpr uint32_t A_KSTEP = A_MN ? UMMA_K * 128 : UMMA_K * 2, B_KSTEP = B_MN ? UMMA_K * 128 : UMMA_K * 2;
+        constexpr uint32_t A_TERMS = (NTERMS == 3 ? 2 : 1) * C::A_BYTES;
+        // descriptors differ only in the 14-bit start-address field (bytes >> 4): plain 64-bit adds
+        const uint64_t dA0 = make_desc(smem_base, A_LBO, 1024);
+        const uint64_t dB0 = make_desc(smem_base + A_TERMS, B_LBO, 1024);
+        uint64_t dA = dA0, dB = dB0;
+        int stage = 0;
+        uint32_t phase = 0;
+        int local_iter = 0;
+        Sched sch(p);
+        Item it;
+        for (; sch.next(it); ++local_iter) {
+            const int kb0 = it.kb0, kb1 = it.kb1;
+            const int acc = local_iter & 1;
+            const uint32_t acc_phase = (uint32_t)(local_iter >> 1) & 1u;
+            mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+            tc_fence_after();
+            const uint32_t tmem_d = tmem_base + (uint32_t)(acc * BN);
+            uint32_t accumulate = 0;
+            for (int kb = kb0; kb < kb1; ++kb) {
+                mbar_wait(full_bar(stage), phase);
                 tc_fence_after();
-                const uint32_t tmem_d = tmem_base + (uint32_t)(acc * BN);
-                uint32_t accumulate = 0;
-                for (int kb = kb0; kb < kb1; ++kb) {
-                    mbar_wait(full_bar(stage), phase);
-                    tc_fence_after();
-                    const uint32_t sA = smem_base + stage * C::STAGE_BYTES;
-                    const uint32_t sB = sA + (NTERMS == 3 ? 2 : 1) * C::A_BYTES;
+                if (elect_one()) {
 #pragma unroll
-                    for (int k = 0; k < BK / UMMA_K; ++k) {
-                        const uint64_t dAh = make_desc(sA + k * A_KSTEP, A_LBO, 1024);
-                        const uint64_t dBh = make_desc(sB + k * B_KSTEP, B_LBO, 1024);
-                        tc_mma_bf16(tmem_d, dAh, dBh, idesc, accumulate);
-                        accumulate = 1;
+                    for (int k = 0; k < ((p.debug & 2) ? 0 : BK / UMMA_K); ++k) {
+                        const uint64_t dAh = dA + (uint64_t)((k * A_KSTEP) >> 4);
+                        const uint64_t dBh = dB + (uint64_t)((k * B_KSTEP) >> 4);
+                        tc_mma_bf16(tmem_d, dAh, dBh, idesc, k == 0 ? accumulate : 1u);
                         if (NTERMS == 3) {
-                            const uint64_t dAl = make_desc(sA + C::A_BYTES + k * A_KSTEP, A_LBO, 1024);
-                            const uint64_t dBl = make_desc(sB + C::B_BYTES + k * B_KSTEP, B_LBO, 1024);
-                            tc_mma_bf16(tmem_d, dAh, dBl, idesc, 1);
-                            tc_mma_bf16(tmem_d, dAl, dBh, idesc, 1);
+                            tc_mma_bf16(tmem_d, dAh, dBh + (uint64_t)(C::B_BYTES >> 4), idesc, 1);
+                            tc_mma_bf16(tmem_d, dAh + (uint64_t)(C::A_BYTES >> 4), dBh, idesc, 1);
                         }
                     }
                     tc_commit(empty_bar(stage));
                     if (kb == kb1 - 1) tc_commit(tfull_bar(acc));
-                    if (++stage == C::STAGES) {
-                        stage = 0;
-                        phase ^= 1u;
-                    }
+                }
+                __syncwarp();
+                accumulate = 1;
+                dA += (uint64_t)(C::STAGE_BYTES >> 4);
+                dB += (uint64_t)(C::STAGE_BYTES >> 4);
+                if (++stage == C::STAGES) {
+                    stage = 0;
+                    phase ^= 1u;
+                    dA = dA0;
+                    dB = dB0;
                 }
             }
         }
@@ -512,13 +653,31 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
         const int q = warp & 3;
         const int half = (warp - 2) >> 2;
         int local_iter = 0;
-        for (int item = blockIdx.x; item < p.total_items; item += gridDim.x, ++local_iter) {
-            int split, batch, m_blk, n_blk;
-            decode_item(item, split, batch, m_blk, n_blk);
+        uint32_t F = p.flags;
+        asm volatile("" : "+r"(F));   // pin the stage bits in a register (else ptxas re-reads the constant bank per test)
+        Sched sch(p);
+        Item it;
+        float* const ws_mine = p.sk_ws + (size_t)blockIdx.x * (BM * BN);
+        for (; sch.next(it); ++local_iter) {
+            const int split = it.split, batch = it.batch, m_blk = it.m_blk, n_blk = it.n_blk;
             const int acc = local_iter & 1;
             const uint32_t acc_phase = (uint32_t)(local_iter >> 1) & 1u;
             mbar_wait(tfull_bar(acc), acc_phase);
             tc_fence_after();
+            if (it.mode == 2) {
+                // stream-K owner: the partials of the following CTAs were written at the START of their ranges
+                if (lane == 0) {
+                    const int want = NUM_EPI_WARPS * it.n_contrib;
+                    const long long t0 = clock64();
+                    while (ld_acquire_gpu(p.sk_flags + blockIdx.x) < want) {
+                        if (clock64() - t0 > (1ll << 32)) {
+                            printf("b2t_gemm: stream-K owner %d timed out waiting for %d partials\n", blockIdx.x, it.n_contrib);
+                            __trap();
+                        }
+                    }
+                }
+                __syncwarp();
+            }
             const int cbatch = p.c_batch_idx ? p.c_batch_idx[batch] : batch;
             const int row = m_blk * BM + q * 32 + lane;
             const bool row_ok = row < p.m_per_batch;
@@ -529,24 +688,59 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
 #pragma unroll 1
             for (int c = half; c < BN / 32; c += 2) {
 #pragma unroll 1
-                for (int s8 = 0; s8 < 4; ++s8) {
-                    float v[8];
-                    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + c * 32 + s8 * 8);
-                    tmem_ld_32x8(taddr, v);
-                    if (c + 2 >= BN / 32 && s8 == 3) {
+                for (int s16 = 0; s16 < 2; ++s16) {
+                    float va[8], vb[8];
+                    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + c * 32 + s16 * 16);
+                    tmem_ld_32x16(taddr, va, vb);
+                    if (c + 2 >= BN / 32 && s16 == 1) {
                         // this warp's share of the accumulator is in registers: hand the TMEM stage back
                         tc_fence_before();
                         __syncwarp();
                         if (lane == 0) mbar_arrive(tempty_bar(acc));
                     }
-                    const int col0 = n_blk * BN + c * 32 + s8 * 8;
-                    if (col0 >= p.n) continue;   // warp-uniform
-                    const int nvalid = p.n - col0 < 8 ? p.n - col0 : 8;
-                    if (p.vec4)
-                        epi_cols8<true>(p, v, row_off + col0, col0, nvalid, row_ok, bias_ptr, lane);
-                    else
-                        epi_cols8<false>(p, v, row_off + col0, col0, nvalid, row_ok, bias_ptr, lane);
+                    // workspace layout [slab = c*4+s8][row in tile][8]: a warp's slab is 1 KB contiguous
+                    const int ws_off = ((c * 4 + s16 * 2) * BM + q * 32 + lane) * 8;
+                    if (it.mode == 1) {
+                        __stcg(reinterpret_cast<float4*>(ws_mine + ws_off), make_float4(va[0], va[1], va[2], va[3]));
+                        __stcg(reinterpret_cast<float4*>(ws_mine + ws_off + 4), make_float4(va[4], va[5], va[6], va[7]));
+                        __stcg(reinterpret_cast<float4*>(ws_mine + ws_off + BM * 8), make_float4(vb[0], vb[1], vb[2], vb[3]));
+                        __stcg(reinterpret_cast<float4*>(ws_mine + ws_off + BM * 8 + 4), make_float4(vb[4], vb[5], vb[6], vb[7]));
+                        continue;
+                    }
+                    const int col0 = n_blk * BN + c * 32 + s16 * 16;
+                    if (col0 >= p.n || (p.debug & 1)) continue;   // warp-uniform
+                    if (it.mode == 2) {
+                        for (int j = 1; j <= it.n_contrib; ++j) {
+                            const float* w = ws_mine + (size_t)j * (BM * BN) + ws_off;
+                            float t[8];
+                            ld_f8_cg(w, t);
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) va[e] += t[e];
+                            ld_f8_cg(w + BM * 8, t);
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) vb[e] += t[e];
+                        }
+                    }
+                    const int n_left = p.n - col0;
+                    if (F & F_VEC) {
+                        epi_cols8<true>(p, F, va, row_off + col0, col0, n_left < 8 ? n_left : 8, row_ok, bias_ptr, lane);
+                        if (n_left > 8)
+                            epi_cols8<true>(p, F, vb, row_off + col0 + 8, col0 + 8, n_left < 16 ? n_left - 8 : 8, row_ok, bias_ptr, lane);
+                    } else {
+                        epi_cols8<false>(p, F, va, row_off + col0, col0, n_left < 8 ? n_left : 8, row_ok, bias_ptr, lane);
+                        if (n_left > 8)
+                            epi_cols8<false>(p, F, vb, row_off + col0 + 8, col0 + 8, n_left < 16 ? n_left - 8 : 8, row_ok, bias_ptr, lane);
+                    }
                 }
+            }
+            if (it.mode == 1) {
+                __threadfence();
+                __syncwarp();
+                if (lane == 0) red_release_gpu_add(p.sk_flags + it.owner, 1);
+            } else if (it.mode == 2) {
+                // every epilogue warp is past its wait: clear the flag for the next launch on this stream
+                asm volatile("bar.sync 1, %0;" ::"n"(NUM_EPI_WARPS * 32) : "memory");
+                if (threadIdx.x == 64) p.sk_flags[blockIdx.x] = 0;
             }
         }
     }
@@ -633,7 +827,17 @@ int launch(const b2t_gemm_args* a, const KParams& kp, cudaStream_t stream) {
         attr_set = true;
     }
     int grid = kp.total_items < num_sms() ? kp.total_items : num_sms();
-    kern<<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(mAh, mAl, mBh, mBl, kp);
+    KParams kq = kp;
+    if (kq.stream_k) {
+        // one line of tiles x k-blocks units cut into `grid` equal ranges; every CTA is resident (grid <= #SMs, 1 CTA/SM)
+        grid = kq.sk_units < num_sms() ? (int)kq.sk_units : num_sms();
+        const size_t need = SK_FLAG_BYTES + (size_t)grid * BM * BN * sizeof(float);
+        if (need > (size_t)a->sk_workspace_bytes) {
+            kq.stream_k = 0;   // workspace too small for this tile shape: plain persistent schedule
+            grid = kp.total_items < num_sms() ? kp.total_items : num_sms();
+        }
+    }
+    kern<<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(mAh, mAl, mBh, mBl, kq);
     B2T_CHECK_LAUNCH("b2t_gemm");
     return 0;
 }
@@ -649,6 +853,10 @@ int dispatch_major(const b2t_gemm_args* a, const KParams& kp, cudaStream_t s) {
 }
 
 }  // namespace
+
+extern "C" int64_t b2t_gemm_workspace_bytes(void) {
+    return (int64_t)SK_FLAG_BYTES + (int64_t)num_sms() * BM * 256 * (int64_t)sizeof(float);
+}
 
 extern "C" int b2t_gemm(const b2t_gemm_args* a, b2t_stream stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
@@ -710,15 +918,49 @@ extern "C" int b2t_gemm(const b2t_gemm_args* a, b2t_stream stream_) {
         auto al16 = [](const void* q) { return q == nullptr || ((uintptr_t)q & 15) == 0; };
         auto al8 = [](const void* q) { return q == nullptr || ((uintptr_t)q & 7) == 0; };
         kp.vec4 = (a->n % 4 == 0) && (a->ldc % 4 == 0) && (a->c_batch_stride % 4 == 0) && al16(a->out_f32) &&
-                  al16(a->out_pre) && al16(a->residual) && al16(a->aux) && al8(a->out_hi) && al8(a->out_lo);
+                  al16(a->out_pre) && al16(a->residual) && al16(a->aux) && al16(a->bias) && (a->bias_batch_stride % 4 == 0) &&
+                  (a->out_hi == nullptr || (al16(a->out_hi) && al16(a->out_lo) && a->ldc % 8 == 0 && a->c_batch_stride % 8 == 0));
+        (void)al8;
     }
+    kp.flags = (kp.alpha != 1.0f ? F_ALPHA : 0u) | (kp.bias ? F_BIAS : 0u) | (kp.out_pre ? F_PRE : 0u) | (kp.act ? F_ACT : 0u) |
+               (kp.aux_mode ? F_AUX : 0u) | (kp.drop_p > 0.0f ? F_DROP : 0u) | (kp.out_scale != 1.0f ? F_SCALE : 0u) |
+               (kp.residual ? F_RES : 0u) | (kp.out_f32 ? F_F32 : 0u) | (kp.atomic ? F_ATOMIC : 0u) | (kp.out_hi ? F_HI : 0u) |
+               (kp.out_lo ? F_LO : 0u) | (kp.colsum ? F_COLSUM : 0u) | (kp.vec4 ? F_VEC : 0u);
 
+    {
+        static int dbg = -1;
+        if (dbg < 0) {
+            const char* e = getenv("B2T_GEMM_DEBUG");
+            dbg = e ? atoi(e) : 0;
+        }
+        kp.debug = dbg;
+    }
     int bn = a->block_n;
     if (bn == 0) bn = a->n <= 64 ? 64 : 128;
     B2T_CHECK_ARG(bn == 64 || bn == 128 || bn == 256, "b2t_gemm: block_n must be 64, 128 or 256");
     kp.m_tiles = ceil_div_i(a->m_per_batch, BM);
     kp.n_tiles = ceil_div_i(a->n, bn);
     kp.total_items = kp.m_tiles * kp.n_tiles * kp.batches * a->split_k;
+
+    // stream-K (needs a caller-owned workspace): replaces whole-tile waves (148 SMs rarely divide the tile
+    // count: M = 3776 x N = 1024 is 240 tiles = 1.62 waves) and split-K + red.add by equal k-block ranges per CTA.
+    kp.stream_k = 0;
+    if (a->sk_workspace && a->stream_k >= 0) {
+        const long long tiles = (long long)kp.m_tiles * kp.n_tiles * kp.batches;
+        const int G = num_sms();
+        const long long waves = (tiles + G - 1) / G;
+        const bool uneven = tiles * 100 < waves * G * 95;
+        const bool want = a->stream_k > 0 || ((uneven || a->split_k > 1) && tiles * kp.num_k_blocks >= 2ll * G);
+        if (want && kp.num_k_blocks >= 2) {
+            B2T_CHECK_ARG(((uintptr_t)a->sk_workspace & 15) == 0, "b2t_gemm: sk_workspace must be 16-byte aligned");
+            kp.stream_k = 1;
+            kp.split_k = 1;
+            kp.total_items = (int)tiles;
+            kp.sk_units = tiles * kp.num_k_blocks;
+            kp.sk_flags = (int*)a->sk_workspace;
+            kp.sk_ws = (float*)((char*)a->sk_workspace + SK_FLAG_BYTES);
+        }
+    }
 
     const bool three = a->a_lo != nullptr;
     if (three) {

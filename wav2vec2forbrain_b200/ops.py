@@ -103,6 +103,20 @@ def unpermute_unfold_cols(g: Tensor, C: int, KL: int) -> Tensor:
     return out
 
 
+STREAM_K = False         # stream-K schedule switch: off by default (round-1 measurements: slower than whole-tile waves at K <= 4096)
+_SK_WS = {}
+
+
+def _sk_workspace(device) -> Tensor:
+    """Per (device, stream) stream-K scratch, zeroed once (b2t_gemm leaves its flags at zero)."""
+    key = (device.index if device.index is not None else torch.cuda.current_device(), torch.cuda.current_stream().cuda_stream)
+    ws = _SK_WS.get(key)
+    if ws is None:
+        ws = torch.zeros(int(lib().b2t_gemm_workspace_bytes()), dtype=torch.uint8, device=device)
+        _SK_WS[key] = ws
+    return ws
+
+
 def gemm(a: Operand, b: Operand, *, m_per_batch: int, n: int, k: int, batches: int = 1,
          out_f32: Optional[Tensor] = None, out_pre: Optional[Tensor] = None,
          out_hi: Optional[Tensor] = None, out_lo: Optional[Tensor] = None,
@@ -111,10 +125,13 @@ def gemm(a: Operand, b: Operand, *, m_per_batch: int, n: int, k: int, batches: i
          colsum: Optional[Tensor] = None, act=None, aux_mode=None, atomic: bool = False, split_k: int = 1,
          alpha: float = 1.0, k_spans_batches: bool = False, a_batched: bool = False, b_batched: bool = False,
          b_batch_idx: Optional[Tensor] = None, c_batch_idx: Optional[Tensor] = None, block_n: int = 0,
-         drop_p: float = 0.0, drop_seed: int = 0, bias_batch_stride: int = 0, out_scale: float = 1.0) -> None:
+         drop_p: float = 0.0, drop_seed: int = 0, bias_batch_stride: int = 0, out_scale: float = 1.0,
+         stream_k: int = 0) -> None:
     """D = epilogue(alpha * A . B^T) on the tcgen05 GEMM (see b2t_gemm in include/b2t_sm100.h)."""
     _lib.ensure_device()
     g = GemmArgs()
+    ws = _sk_workspace(a.hi.device)
+    g.sk_workspace, g.sk_workspace_bytes, g.stream_k = ptr(ws), ws.numel(), (stream_k if STREAM_K else -1)
     g.a_hi, g.a_lo, g.b_hi, g.b_lo = ptr(a.hi), ptr(a.lo), ptr(b.hi), ptr(b.lo)
     g.a_d0, g.a_d1, g.a_d2, g.a_s1, g.a_s2 = a.d0, a.d1, a.d2, a.s1, a.s2
     g.b_d0, g.b_d1, g.b_d2, g.b_s1, g.b_s2 = b.d0, b.d1, b.d2, b.s1, b.s2
