@@ -21,14 +21,20 @@ _M64 = np.uint64(0xFFFFFFFFFFFFFFFF)
 
 
 def hash_uniform(seed: int, idx: torch.Tensor) -> torch.Tensor:
-    """same splitmix64 finaliser as common.cuh::hash_uniform"""
+    """same 32-bit mixer as common.cuh::hash_uniform"""
     with np.errstate(over="ignore"):
         i = idx.detach().cpu().numpy().astype(np.uint64)
-        z = np.uint64(seed & 0xFFFFFFFFFFFFFFFF) + i * np.uint64(0x9E3779B97F4A7C15)
-        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
-        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
-        z = z ^ (z >> np.uint64(31))
-        u = (z >> np.uint64(40)).astype(np.float64) / 16777216.0
+        s = seed & 0xFFFFFFFFFFFFFFFF
+        m32 = np.uint64(0xFFFFFFFF)
+        h = (((i & m32) + (i >> np.uint64(32)) * np.uint64(0x85EBCA77)) & m32) ^ np.uint64(s & 0xFFFFFFFF)
+        h = (h * np.uint64(0x9E3779B1)) & m32
+        h = h ^ np.uint64(s >> 32)
+        h = h ^ (h >> np.uint64(16))
+        h = (h * np.uint64(0x85EBCA6B)) & m32
+        h = h ^ (h >> np.uint64(13))
+        h = (h * np.uint64(0xC2B2AE35)) & m32
+        h = h ^ (h >> np.uint64(16))
+        u = (h >> np.uint64(8)).astype(np.float64) / 16777216.0
     return torch.from_numpy(u)
 
 

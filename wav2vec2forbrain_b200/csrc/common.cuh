@@ -67,19 +67,27 @@ __device__ __forceinline__ float gelu_erf_grad(float x) {
     const float pdf = 0.39894228040143267794f * __expf(-0.5f * x * x);
     return cdf + x * pdf;
 }
-__device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + __expf(-x)); }
+// MUFU.RCP (<= 1 ulp) instead of the IEEE division's called slow path: ~1e-7 relative, far inside the 1e-3 gate
+__device__ __forceinline__ float sigmoidf_(float x) { return __frcp_rn(1.0f + __expf(-x)); }
 __device__ __forceinline__ float silu_f(float x) { return x * sigmoidf_(x); }
 __device__ __forceinline__ float silu_grad(float x) {
     const float s = sigmoidf_(x);
     return s * (1.0f + x * (1.0f - s));
 }
 
-// stateless counter-based uniform in [0,1): same (seed, idx) -> same value in forward and backward
+// stateless counter-based uniform in [0,1): same (seed, idx) -> same value in forward and backward.
+// 32-bit mixing (murmur3 finaliser over the folded index, seed words xored in before two of the
+// multiplies): ~10 integer instructions; the 64-bit splitmix used first cost more than the GEMM epilogue's
+// activation math.  tests/abi_emulator.py::hash_uniform is the numpy twin.
 __device__ __forceinline__ float hash_uniform(unsigned long long seed, unsigned long long idx) {
-    unsigned long long z = seed + idx * 0x9E3779B97F4A7C15ull;
-    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
-    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
-    z = z ^ (z >> 31);
-    return (float)(z >> 40) * (1.0f / 16777216.0f);
+    uint32_t h = ((uint32_t)idx + (uint32_t)(idx >> 32) * 0x85EBCA77u) ^ (uint32_t)seed;
+    h *= 0x9E3779B1u;
+    h ^= (uint32_t)(seed >> 32);
+    h ^= h >> 16;
+    h *= 0x85EBCA6Bu;
+    h ^= h >> 13;
+    h *= 0xC2B2AE35u;
+    h ^= h >> 16;
+    return (float)(h >> 8) * (1.0f / 16777216.0f);
 }
 #endif

@@ -218,7 +218,7 @@ struct Cfg {
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = (NTERMS == 3 ? 2 : 1) * (A_BYTES + B_BYTES);
-    static constexpr int EPI_BYTES = 0;      // the epilogue works from registers
+    static constexpr int EPI_BYTES = NUM_EPI_WARPS * 32 * 32 * 4;   // one 32x32 fp32 transpose buffer per epilogue warp
     static constexpr int AUX_BYTES = 1024;   // barriers + tmem pointer
     static constexpr int STAGES_RAW = (SMEM_LIMIT - 1024 - EPI_BYTES - AUX_BYTES) / STAGE_BYTES;
     static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
@@ -247,6 +247,9 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
+__device__ __forceinline__ void prefetch_l2(const void* p) {
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
 __device__ __forceinline__ int ld_acquire_gpu(const int* p) {
     int v;
     asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -479,6 +482,170 @@ __device__ __forceinline__ void epi_cols8(const KParams& p, const uint32_t F, fl
     }
 }
 
+// ------------------------------------------------------------------------------------------
+// Coalesced epilogue.  tcgen05.ld hands every thread ONE accumulator row; written to global memory that way
+// each warp instruction touches 32 different 128-byte lines with 16 bytes each (measured: every extra
+// 62 MB output / residual / aux stream of the FFN GEMM cost 16 us = 3.9 TB/s).  Instead a warp transposes
+// its 32-row x 32-column chunk through a 4 KB XOR-swizzled smem buffer, after which 8 lanes cover 128
+// contiguous bytes of one row: every global access of the fused stages is a full line, the bias is loaded
+// once per chunk, and column sums are accumulated in registers over the chunk's rows.
+// ------------------------------------------------------------------------------------------
+constexpr int EPI_CHUNK_FLOATS = 32 * 32;
+
+template <bool VEC>
+__device__ __forceinline__ void ld4(const float* a, float (&t)[4], int nv) {
+    if (VEC) {
+        const float4 q = *reinterpret_cast<const float4*>(a);
+        t[0] = q.x, t[1] = q.y, t[2] = q.z, t[3] = q.w;
+    } else {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) t[e] = e < nv ? a[e] : 0.0f;
+    }
+}
+template <bool VEC>
+__device__ __forceinline__ void st4(float* a, const float (&t)[4], int nv) {
+    if (VEC) {
+        *reinterpret_cast<float4*>(a) = make_float4(t[0], t[1], t[2], t[3]);
+    } else {
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+            if (e < nv) a[e] = t[e];
+    }
+}
+
+// st: this warp's 4 KB staging buffer.  v: the lane's row (TMEM lane) x 32 columns.  row0: output row of
+// lane 0 inside the batch; base_off: element offset of the batch slot; col_base: first column of the chunk.
+template <bool VEC>
+__device__ __forceinline__ void epi_chunk32(const KParams& p, const uint32_t F, float* st, const float (&v)[32], int lane,
+                                            int row0, long long base_off, int col_base, const float* bias_ptr) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+        *reinterpret_cast<float4*>(st + lane * 32 + ((j ^ (lane & 7)) << 2)) =
+            make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    __syncwarp();
+    const int c4 = lane & 7, rsub = lane >> 3;
+    const int col = col_base + c4 * 4;
+    const int nv = p.n - col >= 4 ? 4 : (p.n - col > 0 ? p.n - col : 0);   // VEC: 0 or 4
+    float b4[4] = {0.f, 0.f, 0.f, 0.f};
+    if (bias_ptr && nv > 0) ld4<VEC>(bias_ptr + col, b4, nv);
+    float cs[4] = {0.f, 0.f, 0.f, 0.f};
+#define EPI_ALL(stmt)                         \
+    _Pragma("unroll") for (int i = 0; i < 4; ++i) \
+        _Pragma("unroll") for (int e = 0; e < 4; ++e) { stmt; }
+    const int last_row = p.m_per_batch - 1;
+#pragma unroll 1
+    for (int h = 0; h < 2; ++h) {
+        // Stage-major over 4 rows x 4 columns: 16 independent dependency chains per stage (the MUFU / erf
+        // latency of the activations is hidden inside the thread), rows past the matrix are computed on a
+        // clamped address and only their stores are predicated off.
+        float x[4][4], ax[4][4], rs[4][4];
+        long long off[4];
+        bool ok[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int r = (h * 4 + i) * 4 + rsub;
+            const int row = row0 + r;
+            ok[i] = row <= last_row && nv > 0;
+            off[i] = base_off + (long long)(row <= last_row ? row : last_row) * p.ldc + (nv > 0 ? col : 0);
+        }
+        if (F & F_AUX) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) ld4<VEC>(p.aux + off[i], ax[i], nv > 0 ? nv : 4);
+        }
+        if (F & F_RES) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) ld4<VEC>(p.residual + off[i], rs[i], nv > 0 ? nv : 4);
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int r = (h * 4 + i) * 4 + rsub;
+            const float4 q = *reinterpret_cast<const float4*>(st + r * 32 + ((c4 ^ (r & 7)) << 2));
+            x[i][0] = q.x, x[i][1] = q.y, x[i][2] = q.z, x[i][3] = q.w;
+        }
+        if (F & F_ALPHA) { EPI_ALL(x[i][e] *= p.alpha) }
+        EPI_ALL(x[i][e] += b4[e])
+        if (F & F_PRE) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                if (ok[i]) st4<VEC>(p.out_pre + off[i], x[i], nv);
+        }
+        if (F & F_ACT) {
+            if (p.act == 1) { EPI_ALL(x[i][e] = gelu_erf(x[i][e])) }
+            else if (p.act == 2) { EPI_ALL(x[i][e] = silu_f(x[i][e])) }
+            else { EPI_ALL(x[i][e] = x[i][e] * __frcp_rn(1.0f + fabsf(x[i][e]))) }
+        }
+        if (F & F_AUX) {
+            if (p.aux_mode == 1) { EPI_ALL(x[i][e] *= gelu_erf_grad(ax[i][e])) }
+            else if (p.aux_mode == 2) { EPI_ALL(x[i][e] *= silu_grad(ax[i][e])) }
+            else { EPI_ALL(const float d = 1.0f + fabsf(ax[i][e]); x[i][e] *= __frcp_rn(d * d)) }
+        }
+        if (F & F_DROP) {
+            EPI_ALL(x[i][e] = hash_uniform(p.drop_seed, (unsigned long long)(off[i] + e)) < p.drop_p ? 0.0f : x[i][e] * p.drop_scale)
+        }
+        if (F & F_SCALE) { EPI_ALL(x[i][e] *= p.out_scale) }
+        if (F & F_RES) { EPI_ALL(x[i][e] += rs[i][e]) }
+        EPI_ALL(x[i][e] = (ok[i] && e < nv) ? x[i][e] : 0.0f)
+        if (F & F_F32) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                if (!ok[i]) continue;
+                float* o = p.out_f32 + off[i];
+                if (F & F_ATOMIC) {
+                    if (VEC) {
+                        red_add_v4(o, x[i][0], x[i][1], x[i][2], x[i][3]);
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < 4; ++e)
+                            if (e < nv) atomicAdd(o + e, x[i][e]);
+                    }
+                } else {
+                    st4<VEC>(o, x[i], nv);
+                }
+            }
+        }
+        if (F & F_HI) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                bf16 hh[4], ll[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) split_bf16(x[i][e], hh[e], ll[e]);
+                if (!ok[i]) continue;
+                if (VEC) {
+                    auto pk = [](bf16 a, bf16 b) {
+                        __nv_bfloat162 t = __halves2bfloat162(a, b);
+                        return *reinterpret_cast<uint32_t*>(&t);
+                    };
+                    *reinterpret_cast<uint2*>(p.out_hi + off[i]) = make_uint2(pk(hh[0], hh[1]), pk(hh[2], hh[3]));
+                    if (F & F_LO) *reinterpret_cast<uint2*>(p.out_lo + off[i]) = make_uint2(pk(ll[0], ll[1]), pk(ll[2], ll[3]));
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        if (e < nv) {
+                            p.out_hi[off[i] + e] = hh[e];
+                            if (F & F_LO) p.out_lo[off[i] + e] = ll[e];
+                        }
+                    }
+                }
+            }
+        }
+        EPI_ALL(cs[e] += x[i][e])
+    }
+#undef EPI_ALL
+    if (F & F_COLSUM) {   // warp-uniform: rows of the chunk are summed over the 4 lane groups
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            cs[e] += __shfl_xor_sync(0xffffffffu, cs[e], 8);
+            cs[e] += __shfl_xor_sync(0xffffffffu, cs[e], 16);
+        }
+        if (rsub == 0) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+                if (e < nv) atomicAdd(p.colsum + col + e, cs[e]);
+        }
+    }
+    __syncwarp();   // the buffer is rewritten by the next chunk
+}
+
 template <int NTERMS, bool A_MN, bool B_MN, int BN>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ CUtensorMap tmAl,
@@ -657,11 +824,27 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
         asm volatile("" : "+r"(F));   // pin the stage bits in a register (else ptxas re-reads the constant bank per test)
         Sched sch(p);
         Item it;
+        float* const epi_buf =
+            reinterpret_cast<float*>(smem_gen + C::STAGES * C::STAGE_BYTES) + (warp - 2) * EPI_CHUNK_FLOATS;
         float* const ws_mine = p.sk_ws + (size_t)blockIdx.x * (BM * BN);
         for (; sch.next(it); ++local_iter) {
             const int split = it.split, batch = it.batch, m_blk = it.m_blk, n_blk = it.n_blk;
             const int acc = local_iter & 1;
             const uint32_t acc_phase = (uint32_t)(local_iter >> 1) & 1u;
+            if ((F & (F_AUX | F_RES)) && it.mode != 1) {
+                // the tile's MMAs are still running: pull this warp's aux / residual lines (cold in HBM inside a
+                // training step) into L2 now, one 128-byte line per lane (= row) and 32-column chunk
+                const int prow = m_blk * BM + q * 32 + lane;
+                if (prow < p.m_per_batch) {
+                    const long long poff = (long long)(p.c_batch_idx ? p.c_batch_idx[batch] : batch) * p.c_batch_stride +
+                                           (long long)prow * p.ldc + n_blk * BN;
+                    for (int c = half; c < BN / 32; c += 2) {
+                        if (n_blk * BN + c * 32 >= p.n) break;
+                        if (F & F_AUX) prefetch_l2(p.aux + poff + c * 32);
+                        if (F & F_RES) prefetch_l2(p.residual + poff + c * 32);
+                    }
+                }
+            }
             mbar_wait(tfull_bar(acc), acc_phase);
             tc_fence_after();
             if (it.mode == 2) {
@@ -679,59 +862,46 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
                 __syncwarp();
             }
             const int cbatch = p.c_batch_idx ? p.c_batch_idx[batch] : batch;
-            const int row = m_blk * BM + q * 32 + lane;
-            const bool row_ok = row < p.m_per_batch;
-            const long long row_off = (long long)cbatch * p.c_batch_stride + (long long)row * p.ldc;
+            const long long base_off = (long long)cbatch * p.c_batch_stride;
             const int bslot = p.b_batch_idx ? p.b_batch_idx[batch] : (p.b_batched ? batch : 0);
             const float* bias_ptr =
                 (p.bias != nullptr && split == 0) ? p.bias + (long long)bslot * p.bias_batch_stride : nullptr;
 #pragma unroll 1
             for (int c = half; c < BN / 32; c += 2) {
-#pragma unroll 1
-                for (int s16 = 0; s16 < 2; ++s16) {
-                    float va[8], vb[8];
-                    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + c * 32 + s16 * 16);
-                    tmem_ld_32x16(taddr, va, vb);
-                    if (c + 2 >= BN / 32 && s16 == 1) {
-                        // this warp's share of the accumulator is in registers: hand the TMEM stage back
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(tempty_bar(acc));
-                    }
-                    // workspace layout [slab = c*4+s8][row in tile][8]: a warp's slab is 1 KB contiguous
-                    const int ws_off = ((c * 4 + s16 * 2) * BM + q * 32 + lane) * 8;
-                    if (it.mode == 1) {
-                        __stcg(reinterpret_cast<float4*>(ws_mine + ws_off), make_float4(va[0], va[1], va[2], va[3]));
-                        __stcg(reinterpret_cast<float4*>(ws_mine + ws_off + 4), make_float4(va[4], va[5], va[6], va[7]));
-                        __stcg(reinterpret_cast<float4*>(ws_mine + ws_off + BM * 8), make_float4(vb[0], vb[1], vb[2], vb[3]));
-                        __stcg(reinterpret_cast<float4*>(ws_mine + ws_off + BM * 8 + 4), make_float4(vb[4], vb[5], vb[6], vb[7]));
-                        continue;
-                    }
-                    const int col0 = n_blk * BN + c * 32 + s16 * 16;
-                    if (col0 >= p.n || (p.debug & 1)) continue;   // warp-uniform
-                    if (it.mode == 2) {
-                        for (int j = 1; j <= it.n_contrib; ++j) {
-                            const float* w = ws_mine + (size_t)j * (BM * BN) + ws_off;
-                            float t[8];
-                            ld_f8_cg(w, t);
+                float v[32];
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + c * 32);
+                tmem_ld_32x32(taddr, v);
+                if (c + 2 >= BN / 32) {
+                    // this warp's share of the accumulator is in registers: hand the TMEM stage back
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(tempty_bar(acc));
+                }
+                // workspace layout [chunk c][row in tile][32]: a thread's partial row segment is one 128-byte line
+                const int ws_off = (c * BM + q * 32 + lane) * 32;
+                if (it.mode == 1) {
 #pragma unroll
-                            for (int e = 0; e < 8; ++e) va[e] += t[e];
-                            ld_f8_cg(w + BM * 8, t);
+                    for (int j = 0; j < 8; ++j)
+                        __stcg(reinterpret_cast<float4*>(ws_mine + ws_off + 4 * j),
+                               make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]));
+                    continue;
+                }
+                const int col_base = n_blk * BN + c * 32;
+                if (col_base >= p.n || (p.debug & 1)) continue;   // warp-uniform
+                if (it.mode == 2) {
+                    for (int j = 1; j <= it.n_contrib; ++j) {
+                        const float* w = ws_mine + (size_t)j * (BM * BN) + ws_off;
 #pragma unroll
-                            for (int e = 0; e < 8; ++e) vb[e] += t[e];
+                        for (int g = 0; g < 8; ++g) {
+                            const float4 t = __ldcg(reinterpret_cast<const float4*>(w + 4 * g));
+                            v[4 * g] += t.x, v[4 * g + 1] += t.y, v[4 * g + 2] += t.z, v[4 * g + 3] += t.w;
                         }
                     }
-                    const int n_left = p.n - col0;
-                    if (F & F_VEC) {
-                        epi_cols8<true>(p, F, va, row_off + col0, col0, n_left < 8 ? n_left : 8, row_ok, bias_ptr, lane);
-                        if (n_left > 8)
-                            epi_cols8<true>(p, F, vb, row_off + col0 + 8, col0 + 8, n_left < 16 ? n_left - 8 : 8, row_ok, bias_ptr, lane);
-                    } else {
-                        epi_cols8<false>(p, F, va, row_off + col0, col0, n_left < 8 ? n_left : 8, row_ok, bias_ptr, lane);
-                        if (n_left > 8)
-                            epi_cols8<false>(p, F, vb, row_off + col0 + 8, col0 + 8, n_left < 16 ? n_left - 8 : 8, row_ok, bias_ptr, lane);
-                    }
                 }
+                if (F & F_VEC)
+                    epi_chunk32<true>(p, F, epi_buf, v, lane, m_blk * BM + q * 32, base_off, col_base, bias_ptr);
+                else
+                    epi_chunk32<false>(p, F, epi_buf, v, lane, m_blk * BM + q * 32, base_off, col_base, bias_ptr);
             }
             if (it.mode == 1) {
                 __threadfence();
