@@ -68,7 +68,12 @@ __device__ __forceinline__ float gelu_erf_grad(float x) {
     return cdf + x * pdf;
 }
 // MUFU.RCP (<= 1 ulp) instead of the IEEE division's called slow path: ~1e-7 relative, far inside the 1e-3 gate
-__device__ __forceinline__ float sigmoidf_(float x) { return __frcp_rn(1.0f + __expf(-x)); }
+__device__ __forceinline__ float rcp_approx(float x) {   // one MUFU.RCP, no denormal slow-path branch
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float sigmoidf_(float x) { return rcp_approx(1.0f + __expf(-x)); }
 __device__ __forceinline__ float silu_f(float x) { return x * sigmoidf_(x); }
 __device__ __forceinline__ float silu_grad(float x) {
     const float s = sigmoidf_(x);

@@ -572,12 +572,12 @@ __device__ __forceinline__ void epi_chunk32(const KParams& p, const uint32_t F, 
         if (F & F_ACT) {
             if (p.act == 1) { EPI_ALL(x[i][e] = gelu_erf(x[i][e])) }
             else if (p.act == 2) { EPI_ALL(x[i][e] = silu_f(x[i][e])) }
-            else { EPI_ALL(x[i][e] = x[i][e] * __frcp_rn(1.0f + fabsf(x[i][e]))) }
+            else { EPI_ALL(x[i][e] = x[i][e] * rcp_approx(1.0f + fabsf(x[i][e]))) }
         }
         if (F & F_AUX) {
             if (p.aux_mode == 1) { EPI_ALL(x[i][e] *= gelu_erf_grad(ax[i][e])) }
             else if (p.aux_mode == 2) { EPI_ALL(x[i][e] *= silu_grad(ax[i][e])) }
-            else { EPI_ALL(const float d = 1.0f + fabsf(ax[i][e]); x[i][e] *= __frcp_rn(d * d)) }
+            else { EPI_ALL(const float d = 1.0f + fabsf(ax[i][e]); x[i][e] *= rcp_approx(d * d)) }
         }
         if (F & F_DROP) {
             EPI_ALL(x[i][e] = hash_uniform(p.drop_seed, (unsigned long long)(off[i] + e)) < p.drop_p ? 0.0f : x[i][e] * p.drop_scale)
