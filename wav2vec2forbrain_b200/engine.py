@@ -330,13 +330,15 @@ class Engine:
         out = torch.empty(M, D, dtype=torch.float32, device=x.device)
         pre = torch.empty(M, D, dtype=torch.float32, device=x.device) if training else None
         bias = P[q + "pos_conv_embed.conv.bias"]
-        for g in range(G):
-            a = ops.unfold_view(xg_hi[g], None if xg_lo is None else xg_lo[g], K, 1)
-            a.d1 = T   # conv output has T+1 frames, the last one is dropped (Wav2Vec2SamePadLayer)
-            wsl = slice(g * Cg, (g + 1) * Cg)
-            ops.gemm(a, ops.kmajor(wg_hi[wsl], None if wg_lo is None else wg_lo[wsl]), m_per_batch=T, batches=B, n=Cg,
-                     k=K * CP, out_f32=out[:, g * Cg:], out_pre=None if pre is None else pre[:, g * Cg:], ldc=D,
-                     c_batch_stride=T * D, a_batched=True, bias=bias[wsl], act="gelu", residual=x[:, g * Cg:], block_n=64)
+        # all groups in one launch: batch = (group, trial); the weight / bias slot is the group, the output slot
+        # (unit = Cg columns) is trial*T*G + group, so the G*B tiles fill the SMs (one group alone is B tiles)
+        gi, ci = self._posconv_batch_idx(B, T, G, x.device)
+        a = ops.unfold_view(xg_hi.view(G * B, Tpad, CP), None if xg_lo is None else xg_lo.view(G * B, Tpad, CP), K, 1)
+        a.d1 = T   # conv output has T+1 frames, the last one is dropped (Wav2Vec2SamePadLayer)
+        ops.gemm(a, ops.kmajor(wg_hi.view(G, Cg, K * CP), None if wg_lo is None else wg_lo.view(G, Cg, K * CP)),
+                 m_per_batch=T, batches=G * B, n=Cg, k=K * CP, out_f32=out, out_pre=pre, ldc=D, c_batch_stride=Cg,
+                 a_batched=True, b_batch_idx=gi, c_batch_idx=ci, bias=bias, bias_batch_stride=Cg, act="gelu", residual=x,
+                 block_n=64)
         return out, dict(xg_hi=xg_hi, xg_lo=xg_lo, pre=pre, norm=norm, Tpad=Tpad, pad=pad)
 
     @staticmethod
@@ -362,10 +364,21 @@ class Engine:
         ops.colsum(dpre, db)
         G_[q + "pos_conv_embed.conv.bias"] = db
         Tpad = st["Tpad"]
-        dxg = torch.zeros(G, B, Tpad, CP, dtype=torch.float32, device=dev)
         dwg = torch.zeros(D, K * CP, dtype=torch.float32, device=dev)
         dp_hi3 = dp_hi.view(B, T, D)
         dp_lo3 = dp_lo.view(B, T, D) if dp_lo is not None else None
+        # dgrad as a convolution of its own (no [T, K*CP] unfolded gradient, no red.add fold):
+        #   dx[b,s,i] = sum_{k',o} dpp[b, s+k', o] * Wd[i, k'*CP+o],  dpp = dpre shifted right by K-1-pad frames,
+        #   Wd[i, k'*CP+o] = W[o, (K-1-k')*CP+i]  (taps flipped, in/out channels swapped inside the group)
+        wd_hi, wd_lo = self.weights.get(q + "pos_conv_dgrad", _ver(gk, v), lambda: self._posconv_dgrad_weight(wg_hi, wg_lo, G, Cg, K, CP))
+        dpp_hi, dpp_lo = ops.posconv_pack_input(dpre, B, T, G, K - 1 - st["pad"], Tpad, three)
+        dx = torch.empty_like(dsum)
+        gi, ci = self._posconv_batch_idx(B, T, G, dev)
+        ad = ops.unfold_view(dpp_hi.view(G * B, Tpad, CP), None if dpp_lo is None else dpp_lo.view(G * B, Tpad, CP), K, 1)
+        ad.d1 = T
+        ops.gemm(ad, ops.kmajor(wd_hi.view(G, Cg, K * CP), None if wd_lo is None else wd_lo.view(G, Cg, K * CP)),
+                 m_per_batch=T, batches=G * B, n=Cg, k=K * CP, out_f32=dx, ldc=D, c_batch_stride=Cg, a_batched=True,
+                 b_batch_idx=gi, c_batch_idx=ci, residual=dsum, block_n=64)
         for g in range(G):
             wsl = slice(g * Cg, (g + 1) * Cg)
             # A: [B, T, Cg] slice of dpre (row stride D); TMA needs 16-byte aligned base and strides
@@ -380,9 +393,6 @@ class Engine:
                     tl = torch.zeros(B, T, cpad, dtype=torch.bfloat16, device=dev)
                     tl[:, :, :Cg].copy_(dp_lo3[:, :, wsl])
                 a_k = ops.Operand(th, tl, Cg, T, B, cpad, T * cpad)
-            # dgrad into the padded group-major input through the overlapping view
-            ops.gemm(a_k, ops.mnmajor(wg_hi[wsl], None if wg_lo is None else wg_lo[wsl]), m_per_batch=T, batches=B, n=K * CP,
-                     k=Cg, out_f32=dxg[g], a_batched=True, atomic=True, ldc=CP, c_batch_stride=Tpad * CP)
             # wgrad: dwg[o, k*CP+i] = sum_{b,t} dpre[b,t,o] * xg[b, t+k, i]
             uv = ops.unfold_view(st["xg_hi"][g], None if st["xg_lo"] is None else st["xg_lo"][g], K, 1, mn_major=True)
             uv.d1 = T
@@ -394,9 +404,30 @@ class Engine:
             G_[k0], G_[q + "pos_conv_embed.conv.parametrizations.weight.original1"] = dg, dv
         else:
             G_[q + "pos_conv_embed.conv.weight_g"], G_[q + "pos_conv_embed.conv.weight_v"] = dg, dv
-        dx = dsum.clone()
-        ops.posconv_unpack_dx(dxg, dx, B, T, G, st["pad"], Tpad)
         return dx
+
+    def _posconv_batch_idx(self, B: int, T: int, G: int, dev):
+        key = ("posconv_idx", B, T, G, str(dev))
+        hit = self.weights._cache.get(key)
+        if hit is None:
+            g = torch.arange(G, dtype=torch.int32).repeat_interleave(B)
+            b = torch.arange(B, dtype=torch.int32).repeat(G)
+            hit = (g.to(dev), (b * (T * G) + g).to(dev))
+            self.weights._cache[key] = hit
+        return hit
+
+    @staticmethod
+    def _posconv_dgrad_weight(wg_hi: Tensor, wg_lo: Optional[Tensor], G: int, Cg: int, K: int, CP: int):
+        """[D, K*CP] packed conv weight (row o, column k*CP+i) -> the data-gradient operand (row i, column
+        k'*CP+o with k' = K-1-k): a pure permutation of the bf16 hi/lo pairs, so it is exact."""
+        def one(w):
+            if w is None:
+                return None
+            w4 = w.view(G, Cg, K, CP)[:, :, :, :Cg].flip(2).permute(0, 3, 2, 1)    # [G, i, k', o]
+            out = torch.zeros(G, Cg, K, CP, dtype=w.dtype, device=w.device)
+            out[:, :, :, :Cg] = w4
+            return out.view(G * Cg, K * CP)
+        return one(wg_hi), one(wg_lo)
 
     def w2v_base_forward(self, P, feats: Tensor, B: int, T: int, training: bool, seed: int, skip_layers=()):
         cfg = self.w2v
