@@ -277,7 +277,7 @@ def run_ours(args):
     tps = B * world * args.steps / (ms / 1e3)
     e2e_tps = B * world * args.steps / (e2e_ms / 1e3)
     peaks = read_peaks()
-    roof = gemm_roofline(model, opt, batch, step, peaks) if not args.no_roofline else None
+    roof = gemm_roofline(model, opt, batch, step, peaks, workload) if not args.no_roofline else None
     line = {
         "metric": "train trials/sec", "value": tps, "unit": "trials/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -296,7 +296,7 @@ def run_ours(args):
     print(json.dumps(line))
 
 
-def gemm_roofline(model, opt, batch, step, peaks):
+def gemm_roofline(model, opt, batch, step, peaks, workload_key="base"):
     """CUDA-event time of every tcgen05 GEMM launch of one training step vs its algorithmic FLOPs."""
     from wav2vec2forbrain_b200 import engine, ops
     real = ops.gemm
@@ -337,8 +337,15 @@ def gemm_roofline(model, opt, batch, step, peaks):
     step_ms = e0.elapsed_time(e1)
     achieved = flops / (t_ms * 1e-3) / 1e12
     peak = peaks["bf16_tflops_sustained"]
+    traffic = None   # DRAM bytes per GEMM launch from the committed ncu capture (profiles/gemm_traffic_r01.json)
+    tpath = os.path.join(REPO, "profiles", "gemm_traffic_r01.json")
+    if os.path.exists(tpath):
+        with open(tpath) as fh:
+            tj = json.load(fh).get(workload_key)
+        if tj:
+            traffic = tj["dram_bytes_per_launch"]
     return {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05/TMA, all launches of one step)", "achieved": achieved,
-            "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
+            "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
             "peak_source": peaks["source"] + " (sustained cuBLAS bf16)", "launches": len(rec), "gemm_ms_per_step": t_ms,
             "gemm_share_of_step": t_ms / step_ms,
             "note": "algorithmic FLOPs (2MNK); the bf16x3 mode issues 3 MMAs per algorithmic MAC"}

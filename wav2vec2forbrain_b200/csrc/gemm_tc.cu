@@ -1106,7 +1106,18 @@ extern "C" int b2t_gemm(const b2t_gemm_args* a, b2t_stream stream_) {
         kp.debug = dbg;
     }
     int bn = a->block_n;
-    if (bn == 0) bn = a->n <= 64 ? 64 : 128;
+    if (bn == 0) {
+        bn = a->n <= 64 ? 64 : 128;
+        // 128 x 256 tiles move 25 % fewer operand bytes per MMA through shared memory, but halve the tile count:
+        // taken only when the wave count (148 persistent CTAs) does not get worse and the tile is long enough
+        // for the epilogue of a 128 x 256 tile to hide (measured on the step's shapes, profiles/gemm_bench_r01*)
+        if (a->a_lo != nullptr && a->n % 256 == 0 && a->split_k == 1) {
+            const long long G = num_sms();
+            const long long mt = ceil_div_i(a->m_per_batch, BM) * (long long)a->batches;
+            const long long w128 = (mt * (a->n / 128) + G - 1) / G, w256 = (mt * (a->n / 256) + G - 1) / G;
+            if (2 * w256 <= w128 && (kp.num_k_blocks >= 32 || w128 >= 4)) bn = 256;
+        }
+    }
     B2T_CHECK_ARG(bn == 64 || bn == 128 || bn == 256, "b2t_gemm: block_n must be 64, 128 or 256");
     kp.m_tiles = ceil_div_i(a->m_per_batch, BM);
     kp.n_tiles = ceil_div_i(a->n, bn);

@@ -331,6 +331,83 @@ __global__ void __launch_bounds__(256) ln_bwd_cols_kernel(const float* __restric
     }
 }
 
+// float4 variant: a thread owns 4 consecutive columns, a warp reads 512 contiguous bytes of a row, 4 rows of
+// (dy, x, dx) are requested before the first is used.  grid (ceil(n / 128), row slabs of 64), block (32, 8).
+constexpr int LNCV_ROWS = 64;
+__global__ void __launch_bounds__(256) ln_bwd_cols_vec_kernel(const float* __restrict__ dy, const float* __restrict__ x,
+                                                              const float* __restrict__ mean_in, const float* __restrict__ rstd_in,
+                                                              const float* __restrict__ dx, float* __restrict__ dgamma,
+                                                              float* __restrict__ dbeta, float* __restrict__ dcol, int rows, int n,
+                                                              float out_drop_p, unsigned long long out_seed, float br_drop_p,
+                                                              unsigned long long br_seed) {
+    __shared__ float4 part[3][8][33];
+    const int c = (blockIdx.x * 32 + threadIdx.x) * 4;
+    const int r0 = blockIdx.y * LNCV_ROWS;
+    const int r1 = r0 + LNCV_ROWS < rows ? r0 + LNCV_ROWS : rows;
+    const float out_scale = 1.0f / (1.0f - out_drop_p), br_scale = 1.0f / (1.0f - br_drop_p);
+    float ag[4] = {0.f, 0.f, 0.f, 0.f}, ab[4] = {0.f, 0.f, 0.f, 0.f}, ac[4] = {0.f, 0.f, 0.f, 0.f};
+    if (c < n) {
+        for (int rb = r0 + threadIdx.y; rb < r1; rb += 32) {
+            float4 d4[4], x4[4], o4[4];
+            float mu[4], rs[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int r = rb + 8 * i;
+                const bool ok = r < r1;
+                const long off = (long)(ok ? r : rb) * n + c;
+                d4[i] = *reinterpret_cast<const float4*>(dy + off);
+                x4[i] = *reinterpret_cast<const float4*>(x + off);
+                if (dcol) o4[i] = *reinterpret_cast<const float4*>(dx + off);
+                mu[i] = mean_in[ok ? r : rb];
+                rs[i] = ok ? rstd_in[r] : 0.0f;
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int r = rb + 8 * i;
+                if (r >= r1) continue;
+                const long off = (long)r * n + c;
+                float d[4] = {d4[i].x, d4[i].y, d4[i].z, d4[i].w};
+                const float xv[4] = {x4[i].x, x4[i].y, x4[i].z, x4[i].w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    if (out_drop_p > 0.0f)
+                        d[e] = hash_uniform(out_seed, (unsigned long long)(off + e)) < out_drop_p ? 0.0f : d[e] * out_scale;
+                    ag[e] += d[e] * (xv[e] - mu[i]) * rs[i];
+                    ab[e] += d[e];
+                }
+                if (dcol) {
+                    float o[4] = {o4[i].x, o4[i].y, o4[i].z, o4[i].w};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        if (br_drop_p > 0.0f)
+                            o[e] = hash_uniform(br_seed, (unsigned long long)(off + e)) < br_drop_p ? 0.0f : o[e] * br_scale;
+                        ac[e] += o[e];
+                    }
+                }
+            }
+        }
+    }
+    part[0][threadIdx.y][threadIdx.x] = make_float4(ag[0], ag[1], ag[2], ag[3]);
+    part[1][threadIdx.y][threadIdx.x] = make_float4(ab[0], ab[1], ab[2], ab[3]);
+    part[2][threadIdx.y][threadIdx.x] = make_float4(ac[0], ac[1], ac[2], ac[3]);
+    __syncthreads();
+    if (threadIdx.y < 3 && c < n) {
+        float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float4 t = part[threadIdx.y][j][threadIdx.x];
+            sum.x += t.x, sum.y += t.y, sum.z += t.z, sum.w += t.w;
+        }
+        float* dst = threadIdx.y == 0 ? dgamma : (threadIdx.y == 1 ? dbeta : dcol);
+        if (dst) {
+            atomicAdd(dst + c, sum.x);
+            atomicAdd(dst + c + 1, sum.y);
+            atomicAdd(dst + c + 2, sum.z);
+            atomicAdd(dst + c + 3, sum.w);
+        }
+    }
+}
+
 // y = dropout(x) (same hash mask contract as the GEMM epilogue) with optional fp32 / hi / lo outputs;
 // p == 0 degenerates to a plain split.  Also the backward (apply to the incoming gradient).
 __global__ void dropout_kernel(const float* __restrict__ x, float* __restrict__ y, bf16* __restrict__ hi,
@@ -437,6 +514,15 @@ extern "C" int b2t_layernorm_bwd(const float* dy, const float* x, const float* g
 #undef VCALL
         B2T_CHECK_LAUNCH("b2t_layernorm_bwd");
         if (dgamma || dbeta || dcol) {
+            const bool v4 = n % 4 == 0 && (((uintptr_t)dy | (uintptr_t)x | (uintptr_t)dx) & 15) == 0;
+            if (v4) {
+                dim3 vgrid((n + 127) / 128, (rows + LNCV_ROWS - 1) / LNCV_ROWS);
+                ln_bwd_cols_vec_kernel<<<vgrid, dim3(32, 8), 0, stream>>>(dy, x, mean, rstd, dx, dgamma, dbeta, dcol, rows, n,
+                                                                          out_drop_p, (unsigned long long)out_seed, br_drop_p,
+                                                                          (unsigned long long)br_seed);
+                B2T_CHECK_LAUNCH("b2t_layernorm_bwd (column sums)");
+                return 0;
+            }
             dim3 cgrid((n + 31) / 32, (rows + LNC_ROWS - 1) / LNC_ROWS);
             ln_bwd_cols_kernel<<<cgrid, dim3(32, 8), 0, stream>>>(dy, x, mean, rstd, dx, dgamma, dbeta, dcol, rows, n, out_drop_p,
                                                                   (unsigned long long)out_seed, br_drop_p,
