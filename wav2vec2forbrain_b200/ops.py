@@ -109,7 +109,7 @@ _SK_WS = {}
 
 def _sk_workspace(device) -> Tensor:
     """Per (device, stream) stream-K scratch, zeroed once (b2t_gemm leaves its flags at zero)."""
-    key = (device.index if device.index is not None else torch.cuda.current_device(), torch.cuda.current_stream().cuda_stream)
+    key = (device.index, _lib.raw_stream())
     ws = _SK_WS.get(key)
     if ws is None:
         ws = torch.zeros(int(lib().b2t_gemm_workspace_bytes()), dtype=torch.uint8, device=device)
@@ -130,8 +130,11 @@ def gemm(a: Operand, b: Operand, *, m_per_batch: int, n: int, k: int, batches: i
     """D = epilogue(alpha * A . B^T) on the tcgen05 GEMM (see b2t_gemm in include/b2t_sm100.h)."""
     _lib.ensure_device()
     g = GemmArgs()
-    ws = _sk_workspace(a.hi.device)
-    g.sk_workspace, g.sk_workspace_bytes, g.stream_k = ptr(ws), ws.numel(), (stream_k if STREAM_K else -1)
+    if STREAM_K or stream_k > 0:
+        ws = _sk_workspace(a.hi.device)
+        g.sk_workspace, g.sk_workspace_bytes, g.stream_k = ptr(ws), ws.numel(), stream_k
+    else:
+        g.stream_k = -1
     g.a_hi, g.a_lo, g.b_hi, g.b_lo = ptr(a.hi), ptr(a.lo), ptr(b.hi), ptr(b.lo)
     g.a_d0, g.a_d1, g.a_d2, g.a_s1, g.a_s2 = a.d0, a.d1, a.d2, a.s1, a.s2
     g.b_d0, g.b_d1, g.b_d2, g.b_s1, g.b_s2 = b.d0, b.d1, b.d2, b.s1, b.s2
