@@ -281,12 +281,17 @@ def run_ours(args):
     if multi:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms, e2e_ms = t.tolist()
+    peaks = read_peaks()
+    # every rank runs the roofline steps (they contain the gradient all-reduce); rank 0 reports
+    roof = gemm_roofline(model, opt, batch, step, peaks, workload) if not args.no_roofline else None
+    if multi:
+        dist.barrier()
+        torch.cuda.synchronize()
+        dist.destroy_process_group()
     if rank != 0:
         return
     tps = B * world * args.steps / (ms / 1e3)
     e2e_tps = B * world * args.steps / (e2e_ms / 1e3)
-    peaks = read_peaks()
-    roof = gemm_roofline(model, opt, batch, step, peaks, workload) if not args.no_roofline else None
     line = {
         "metric": "train trials/sec", "value": tps, "unit": "trials/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",

@@ -164,6 +164,8 @@ int b2t_attention_bwd(const float* qkv, int64_t ld, int q_off, int k_off, int v_
  * Hidden sizes 32/64/128/256/512 (a cluster of H/32 CTAs keeps W_hh on chip for the sequence).
  * ------------------------------------------------------------------------------------- */
 int b2t_gru_supported_hidden(int H);
+/* diagnostic: resident forward clusters (H/32 CTAs each) the current device can hold; < 0 = unknown */
+int b2t_gru_max_active_clusters(int H);
 int b2t_gru_fwd(const float* gi, const float* w_hh, const float* b_hh, const float* h0, float* out, void* out_hi,
                 void* out_lo, float* save_r, float* save_z, float* save_n, float* save_ghn, void* hprev_hi,
                 void* hprev_lo, int B, int T, int H, int ndir, float drop_p, uint64_t seed, b2t_stream stream);

@@ -1,0 +1,8 @@
+import sys; sys.path.insert(0,'/root/repo'); sys.path.insert(0,'/root/repo/scripts')
+import torch
+from wav2vec2forbrain_b200 import ops, _lib
+_lib.ensure_device()
+print("max active 16-CTA clusters:", _lib.lib().b2t_gru_max_active_clusters(512))
+import kernel_bench as kb
+for B in (16, 32, 48, 64, 96, 128):
+    kb.gru(B)

@@ -644,6 +644,30 @@ int launch_bwd(const GruBwdArgs& a, cudaStream_t stream) {
 
 }  // namespace
 
+/* diagnostic: how many forward clusters (H/32 CTAs each) the device can keep resident at once */
+extern "C" int b2t_gru_max_active_clusters(int H) {
+    if (H != 512) return -1;
+    constexpr int CS = 512 / U;
+    auto kern = gru_fwd_kernel<512>;
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FwdSmem<512>::TOTAL);
+    cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(CS * 16);
+    cfg.blockDim = dim3(384);
+    cfg.dynamicSmemBytes = FwdSmem<512>::TOTAL;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = CS;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    int n = -1;
+    if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess) return -2;
+    return n;
+}
+
 extern "C" int b2t_gru_supported_hidden(int H) { return (H == 32 || H == 64 || H == 128 || H == 256 || H == 512) ? 1 : 0; }
 
 extern "C" int b2t_gru_fwd(const float* gi, const float* w_hh, const float* b_hh, const float* h0, float* out, void* out_hi,
