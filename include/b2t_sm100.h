@@ -208,6 +208,45 @@ int b2t_posconv_weight_bwd(const float* dwg, const float* g, const float* v, con
 int b2t_act_bwd(const float* dy, const float* pre, float* out, void* hi, void* lo, int64_t n, int mode,
                 b2t_stream stream);
 
+/* ---------------------------------------------------------------------------------------
+ * Wav2Vec2-Conformer (RoPE) block pieces: transformers
+ * modeling_wav2vec2_conformer.py:125-156 (rotary table), :420-527 (self-attention with the rotary
+ * embedding applied to the layer-normed state BEFORE the q/k projections, v from the plain state),
+ * :360-417 (convolution module: pointwise-1 -> GLU -> depthwise k=31 -> BatchNorm1d -> SiLU ->
+ * pointwise-2; the two pointwise convolutions are b2t_gemm calls).
+ * ------------------------------------------------------------------------------------- */
+/* cos / sin tables [T, head_dim] of the rotary embedding from inv_freq [head_dim/2] */
+int b2t_rope_table(const float* inv_freq, float* cos_t, float* sin_t, int T, int head_dim, b2t_stream stream);
+/* y = LN(x)*gamma+beta written twice as bf16 hi/lo: plain (operand of the v projection) and rotated
+ * per head (operand of the fused q/k projection); saves mean / rstd.  rows = B*T, n = heads*head_dim */
+int b2t_layernorm_rope_fwd(const float* x, const float* gamma, const float* beta, float eps, void* y_hi, void* y_lo,
+                           void* r_hi, void* r_lo, float* mean, float* rstd, const float* cos_t, const float* sin_t,
+                           int rows, int n, int T, int head_dim, b2t_stream stream);
+/* out = rope^T(d_rot) + d_plain: gradient w.r.t. the layer-normed state from the q/k branch (through
+ * the transpose of the rotation) and the v branch; ld_* = row strides in elements */
+int b2t_rope_bwd_add(const float* d_rot, int64_t ld_rot, const float* d_plain, int64_t ld_plain, float* out,
+                     const float* cos_t, const float* sin_t, int64_t rows, int n, int T, int head_dim,
+                     b2t_stream stream);
+/* g [B*T, 2D] (pointwise-1 output) -> GLU -> depthwise conv over time (w [D,1,K], "same" padding) ->
+ * out [B*T, D]; stats [2, D] (double) += per-channel sum and sum of squares (BatchNorm batch statistics) */
+int b2t_glu_dwconv_fwd(const float* g, const float* w, float* out, double* stats, int B, int T, int D, int K,
+                       b2t_stream stream);
+/* BatchNorm1d (training: batch statistics from `stats`, running buffers updated with `momentum`;
+ * eval: running buffers) followed by SiLU, written as bf16 hi/lo (operand of pointwise-2) */
+int b2t_bn_silu_fwd(const float* x, const double* stats, const float* gamma, const float* beta, float eps,
+                    float momentum, float* running_mean, float* running_var, int64_t* num_batches_tracked,
+                    float* mean_out, float* rstd_out, void* y_hi, void* y_lo, int64_t M, int D, int training,
+                    b2t_stream stream);
+/* dgamma / dbeta of the BatchNorm (+=) from ds = gradient w.r.t. the SiLU output */
+int b2t_bn_silu_bwd_stats(const float* ds, const float* x, const float* mean, const float* rstd, const float* gamma,
+                          const float* beta, float* dgamma, float* dbeta, int64_t M, int D, b2t_stream stream);
+/* backward of SiLU . BatchNorm . depthwise conv . GLU in one pass: dg (bf16 hi/lo, [B*T, 2D], operand of
+ * the pointwise-1 backward GEMMs) and dw [D,1,K] (+=) */
+int b2t_glu_dwconv_bwd(const float* ds, const float* x, const float* g, const float* w, const float* mean,
+                       const float* rstd, const float* gamma, const float* beta, const float* dgamma,
+                       const float* dbeta, void* dg_hi, void* dg_lo, float* dw, int B, int T, int D, int K,
+                       int training, b2t_stream stream);
+
 #ifdef __cplusplus
 }
 #endif
