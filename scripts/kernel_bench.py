@@ -52,6 +52,8 @@ def conv(B, T=118, D=1024, K=31):
     timeit("glu_dwconv_bwd", lambda: ops.glu_dwconv_bwd(ds, dwo, g, w, mean, rstd, ga, be, dgam, dbet, B, T, True), bytes_=M * D * 24)
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "ln":
+        ln(3776, 1024); sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "gru":
         gru(32); sys.exit(0)
     gru(64); gru(32)

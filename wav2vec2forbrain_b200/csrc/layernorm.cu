@@ -224,7 +224,7 @@ __global__ void __launch_bounds__(256) ln_fwd_vec_kernel(const float* __restrict
 }
 
 template <int VPL>
-__global__ void __launch_bounds__(256) ln_bwd_vec_kernel(const float* __restrict__ dy, const float* __restrict__ x,
+__global__ void __launch_bounds__(256, 2) ln_bwd_vec_kernel(const float* __restrict__ dy, const float* __restrict__ x,
                                                          const float* __restrict__ gamma, const float* __restrict__ mean_in,
                                                          const float* __restrict__ rstd_in, float* __restrict__ dx,
                                                          bf16* __restrict__ dx_hi, bf16* __restrict__ dx_lo, int rows, int n,
@@ -247,6 +247,8 @@ __global__ void __launch_bounds__(256) ln_bwd_vec_kernel(const float* __restrict
                 const float4 d4 = *reinterpret_cast<const float4*>(dy + off);
                 const float4 x4 = *reinterpret_cast<const float4*>(x + off);
                 const float4 ga = *reinterpret_cast<const float4*>(gamma + c);
+                // the residual gradient is only needed after the two row reductions: start its trip from DRAM now
+                if (dres && (lane & 7) == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(dres + off));
                 float d[4] = {d4.x, d4.y, d4.z, d4.w};
                 const float xv[4] = {x4.x, x4.y, x4.z, x4.w};
                 const float gv[4] = {ga.x, ga.y, ga.z, ga.w};
