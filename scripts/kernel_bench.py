@@ -51,7 +51,14 @@ def conv(B, T=118, D=1024, K=31):
     timeit("bn_silu_bwd_stats", lambda: ops.bn_silu_bwd_stats(ds, dwo, mean, rstd, ga, be), bytes_=M * D * 8)
     timeit("glu_dwconv_bwd", lambda: ops.glu_dwconv_bwd(ds, dwo, g, w, mean, rstd, ga, be, dgam, dbet, B, T, True), bytes_=M * D * 24)
 
+def pre(B, T=500, C=256):
+    x = rnd(B, T, C); taps = torch.softmax(rnd(20), 0).repeat(C, 1).contiguous()
+    timeit(f"smooth_fwd B={B} (hi/lo out)", lambda: ops.smooth_fwd(x, taps, 9), bytes_=B * T * C * 8)
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "pre":
+        pre(64); pre(32); sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "ln":
         ln(3776, 1024); sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "gru":
