@@ -291,6 +291,147 @@ __global__ void __launch_bounds__(256, 2) ln_bwd_vec_kernel(const float* __restr
     }
 }
 
+// forward twin of ln_bwd_vec2_kernel (below): two warps per row, 4 rows per CTA, mean and variance combined
+// through 64 bytes of smem (two-pass variance on the register copy of the row, as in the one-warp kernel)
+template <int VPL>
+__global__ void __launch_bounds__(256) ln_fwd_vec2_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                                                          const float* __restrict__ beta, float eps, float* __restrict__ y,
+                                                          bf16* __restrict__ y_hi, bf16* __restrict__ y_lo,
+                                                          float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows,
+                                                          int n, float drop_p, unsigned long long seed) {
+    __shared__ float red[2][4][2];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int rl = warp >> 1, half = warp & 1;
+    const int row = blockIdx.x * 4 + rl;
+    const bool row_ok = row < rows;
+    const float inv_n = 1.0f / (float)n;
+    const float drop_scale = 1.0f / (1.0f - drop_p);
+    float4 v[VPL];
+    float s = 0.0f;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+        const int c = ((half * VPL + i) * 32 + lane) * 4;
+        v[i] = (row_ok && c < n) ? *reinterpret_cast<const float4*>(x + (long)row * n + c) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+    }
+    s = warp_sum(s);
+    if (lane == 0) red[0][rl][half] = s;
+    __syncthreads();
+    const float mean = (red[0][rl][0] + red[0][rl][1]) * inv_n;
+    float q = 0.0f;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+        if (((half * VPL + i) * 32 + lane) * 4 < n) {
+            const float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
+            q += (a * a + b * b) + (c * c + d * d);
+        }
+    }
+    q = warp_sum(q);
+    if (lane == 0) red[1][rl][half] = q;
+    __syncthreads();
+    const float rstd = rsqrtf((red[1][rl][0] + red[1][rl][1]) * inv_n + eps);
+    if (row_ok && half == 0 && lane == 0) {
+        if (mean_out) mean_out[row] = mean;
+        if (rstd_out) rstd_out[row] = rstd;
+    }
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+        const int c = ((half * VPL + i) * 32 + lane) * 4;
+        if (row_ok && c < n) {
+            const float4 ga = *reinterpret_cast<const float4*>(gamma + c), be = *reinterpret_cast<const float4*>(beta + c);
+            const long off = (long)row * n + c;
+            float o[4] = {(v[i].x - mean) * rstd * ga.x + be.x, (v[i].y - mean) * rstd * ga.y + be.y,
+                          (v[i].z - mean) * rstd * ga.z + be.z, (v[i].w - mean) * rstd * ga.w + be.w};
+            if (drop_p > 0.0f) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e)
+                    o[e] = hash_uniform(seed, (unsigned long long)(off + e)) < drop_p ? 0.0f : o[e] * drop_scale;
+            }
+            if (y) *reinterpret_cast<float4*>(y + off) = make_float4(o[0], o[1], o[2], o[3]);
+            if (y_hi) store_split4(o, y_hi, y_lo, off);
+        }
+    }
+}
+
+// Wide rows (n >= 512): TWO warps per row, VPL float4 per lane each, 4 rows per 256-thread CTA.  One warp per
+// row left 3776 warps of 164 registers for the whole [3776, 1024] problem (1 CTA/SM, 12 % of the warp slots,
+// 13 % of DRAM bandwidth in ncu); half the per-thread footprint doubles the rows in flight per SM.
+template <int VPL>
+__global__ void __launch_bounds__(256) ln_bwd_vec2_kernel(const float* __restrict__ dy, const float* __restrict__ x,
+                                                          const float* __restrict__ gamma, const float* __restrict__ mean_in,
+                                                          const float* __restrict__ rstd_in, float* __restrict__ dx,
+                                                          bf16* __restrict__ dx_hi, bf16* __restrict__ dx_lo, int rows, int n,
+                                                          float out_drop_p, unsigned long long out_seed, float br_drop_p,
+                                                          unsigned long long br_seed, const float* __restrict__ dres) {
+    __shared__ float red[4][2][2];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int rl = warp >> 1, half = warp & 1;
+    const int row = blockIdx.x * 4 + rl;
+    const bool row_ok = row < rows;
+    const float inv_n = 1.0f / (float)n;
+    const float out_scale = 1.0f / (1.0f - out_drop_p), br_scale = 1.0f / (1.0f - br_drop_p);
+    const float mean = row_ok ? mean_in[row] : 0.0f, rstd = row_ok ? rstd_in[row] : 0.0f;
+    float xh[VPL][4], g[VPL][4];
+    float s1 = 0.0f, s2 = 0.0f;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+        const int c = ((half * VPL + i) * 32 + lane) * 4;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) xh[i][e] = g[i][e] = 0.0f;
+        if (row_ok && c < n) {
+            const long off = (long)row * n + c;
+            const float4 d4 = *reinterpret_cast<const float4*>(dy + off);
+            const float4 x4 = *reinterpret_cast<const float4*>(x + off);
+            const float4 ga = *reinterpret_cast<const float4*>(gamma + c);
+            if (dres && (lane & 7) == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(dres + off));
+            float d[4] = {d4.x, d4.y, d4.z, d4.w};
+            const float xv[4] = {x4.x, x4.y, x4.z, x4.w};
+            const float gv[4] = {ga.x, ga.y, ga.z, ga.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                if (out_drop_p > 0.0f)
+                    d[e] = hash_uniform(out_seed, (unsigned long long)(off + e)) < out_drop_p ? 0.0f : d[e] * out_scale;
+                xh[i][e] = (xv[e] - mean) * rstd;
+                g[i][e] = d[e] * gv[e];
+                s1 += g[i][e];
+                s2 += g[i][e] * xh[i][e];
+            }
+        }
+    }
+    s1 = warp_sum(s1);
+    s2 = warp_sum(s2);
+    if (lane == 0) {
+        red[rl][half][0] = s1;
+        red[rl][half][1] = s2;
+    }
+    __syncthreads();
+    s1 = (red[rl][0][0] + red[rl][1][0]) * inv_n;
+    s2 = (red[rl][0][1] + red[rl][1][1]) * inv_n;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+        const int c = ((half * VPL + i) * 32 + lane) * 4;
+        if (row_ok && c < n) {
+            const long off = (long)row * n + c;
+            float o[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) o[e] = rstd * (g[i][e] - s1 - xh[i][e] * s2);
+            if (dres) {
+                const float4 r4 = *reinterpret_cast<const float4*>(dres + off);
+                o[0] += r4.x, o[1] += r4.y, o[2] += r4.z, o[3] += r4.w;
+            }
+            if (dx) *reinterpret_cast<float4*>(dx + off) = make_float4(o[0], o[1], o[2], o[3]);
+            if (dx_hi) {
+                if (br_drop_p > 0.0f) {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                        o[e] = hash_uniform(br_seed, (unsigned long long)(off + e)) < br_drop_p ? 0.0f : o[e] * br_scale;
+                }
+                store_split4(o, dx_hi, dx_lo, off);
+            }
+        }
+    }
+}
+
 // column sums of the LayerNorm backward: dgamma += sum_r dy.xhat, dbeta += sum_r dy, dcol += sum_r mask.dx
 // grid (ceil(n / 32), row slabs), block (32, 8): a warp reads 128 contiguous bytes of a row.
 constexpr int LNC_ROWS = 128;
@@ -484,7 +625,14 @@ extern "C" int b2t_layernorm_fwd(const float* x, const float* gamma, const float
 #define VCALL(V)                                                                                                         \
     ln_fwd_vec_kernel<V><<<grid, 256, 0, stream>>>(x, gamma, beta, eps, y, (bf16*)y_hi, (bf16*)y_lo, mean, rstd, rows, n, \
                                                    drop_p, (unsigned long long)seed)
-        if (vpl <= 1) { VCALL(1); } else if (vpl <= 2) { VCALL(2); } else if (vpl <= 4) { VCALL(4); } else if (vpl <= 6) { VCALL(6); } else { VCALL(8); }
+        if (n >= 512) {
+            const int v2 = (n / 4 + 63) / 64, g2 = (rows + 3) / 4;
+#define V2CALL(V)                                                                                                        \
+    ln_fwd_vec2_kernel<V><<<g2, 256, 0, stream>>>(x, gamma, beta, eps, y, (bf16*)y_hi, (bf16*)y_lo, mean, rstd, rows, n, \
+                                                  drop_p, (unsigned long long)seed)
+            if (v2 <= 2) { V2CALL(2); } else if (v2 <= 3) { V2CALL(3); } else { V2CALL(4); }
+#undef V2CALL
+        } else if (vpl <= 1) { VCALL(1); } else if (vpl <= 2) { VCALL(2); } else if (vpl <= 4) { VCALL(4); } else if (vpl <= 6) { VCALL(6); } else { VCALL(8); }
 #undef VCALL
         B2T_CHECK_LAUNCH("b2t_layernorm_fwd");
         return 0;
@@ -512,7 +660,14 @@ extern "C" int b2t_layernorm_bwd(const float* dy, const float* x, const float* g
 #define VCALL(V)                                                                                                          \
     ln_bwd_vec_kernel<V><<<vgrid, 256, 0, stream>>>(dy, x, gamma, mean, rstd, dx, (bf16*)dx_hi, (bf16*)dx_lo, rows, n, out_drop_p, \
                                                     (unsigned long long)out_seed, br_drop_p, (unsigned long long)br_seed, dres)
-        if (vpl <= 1) { VCALL(1); } else if (vpl <= 2) { VCALL(2); } else if (vpl <= 4) { VCALL(4); } else if (vpl <= 6) { VCALL(6); } else { VCALL(8); }
+        if (n >= 512) {
+            const int v2 = (n / 4 + 63) / 64, g2 = (rows + 3) / 4;
+#define V2CALL(V)                                                                                                         \
+    ln_bwd_vec2_kernel<V><<<g2, 256, 0, stream>>>(dy, x, gamma, mean, rstd, dx, (bf16*)dx_hi, (bf16*)dx_lo, rows, n, out_drop_p, \
+                                                  (unsigned long long)out_seed, br_drop_p, (unsigned long long)br_seed, dres)
+            if (v2 <= 2) { V2CALL(2); } else if (v2 <= 3) { V2CALL(3); } else { V2CALL(4); }
+#undef V2CALL
+        } else if (vpl <= 1) { VCALL(1); } else if (vpl <= 2) { VCALL(2); } else if (vpl <= 4) { VCALL(4); } else if (vpl <= 6) { VCALL(6); } else { VCALL(8); }
 #undef VCALL
         B2T_CHECK_LAUNCH("b2t_layernorm_bwd");
         if (dgamma || dbeta || dcol) {
