@@ -20,6 +20,12 @@ LAUNCHES = 0
 _M64 = np.uint64(0xFFFFFFFFFFFFFFFF)
 
 
+def zeros(*shape, device):
+    if len(shape) == 1 and isinstance(shape[0], (tuple, list, torch.Size)):
+        shape = tuple(shape[0])
+    return torch.zeros(shape, dtype=torch.float32, device=device)
+
+
 def hash_uniform(seed: int, idx: torch.Tensor) -> torch.Tensor:
     """same 32-bit mixer as common.cuh::hash_uniform"""
     with np.errstate(over="ignore"):

@@ -129,7 +129,7 @@ def forward(eng, P, feats: Tensor, B: int, T: int, training: bool, seed: int, sk
 
 
 def _zeros(n: int, dev) -> Tensor:
-    return torch.zeros(n, dtype=torch.float32, device=dev)
+    return _e.ops.zeros(n, device=dev)
 
 
 def _ln_bwd(eng, P, G, name: str, dy: Tensor, x: Tensor, ln, **kw):

@@ -126,7 +126,7 @@ class Engine:
         kb = (M + 63) // 64
         sk = _split_k_for(N, K, kb)
         if out is None:
-            out = (torch.zeros if sk > 1 else torch.empty)(N, K, dtype=torch.float32, device=dy_hi.device)
+            out = ops.zeros(N, K, device=dy_hi.device) if sk > 1 else torch.empty(N, K, dtype=torch.float32, device=dy_hi.device)
         ops.gemm(ops.mnmajor(dy_hi, dy_lo), ops.mnmajor(x_hi, x_lo), m_per_batch=N, n=K, k=M, out_f32=out,
                  atomic=sk > 1, split_k=sk, alpha=alpha)
         return out
@@ -241,13 +241,13 @@ class Engine:
             wname = e + f"fc.{2 * i}.weight"
             G[wname] = self._wgrad(d_hi, d_lo, st["a_hi"], st["a_lo"], sizes[i + 1], sizes[i], M)
             if d_f32 is not None:
-                db = torch.zeros(sizes[i + 1], dtype=torch.float32, device=dev)
+                db = ops.zeros(sizes[i + 1], device=dev)
                 ops.colsum(d_f32, db)
                 G[e + f"fc.{2 * i}.bias"] = db
             w_hl = self._w(P, wname)
             if i > 0:
                 # gradient w.r.t. the previous Linear's pre-activation, its column sums = that bias gradient
-                db_prev = torch.zeros(sizes[i], dtype=torch.float32, device=dev)
+                db_prev = ops.zeros(sizes[i], device=dev)
                 _, d_hi, d_lo = self._dgrad(d_hi, d_lo, w_hl, M, sizes[i + 1], sizes[i], want_f32=False, want_split=True,
                                             aux=S["fc"][i - 1]["pre"], aux_mode=be.fc_act, colsum=db_prev)
                 G[e + f"fc.{2 * (i - 1)}.bias"] = db_prev
@@ -266,9 +266,9 @@ class Engine:
                 G[e + f"gru.weight_hh_l{l}{s}"] = self._wgrad(bw["dgh_hi"][d], None if bw["dgh_lo"] is None else bw["dgh_lo"][d],
                                                               fw["hprev_hi"][d],
                                                               None if fw["hprev_lo"] is None else fw["hprev_lo"][d], 3 * H, H, M)
-            db_ih = torch.zeros(ndir * 3 * H, dtype=torch.float32, device=dev)
+            db_ih = ops.zeros(ndir * 3 * H, device=dev)
             ops.colsum(bw["dgi"], db_ih)
-            dbn = torch.zeros(ndir * H, dtype=torch.float32, device=dev)
+            dbn = ops.zeros(ndir * H, device=dev)
             ops.colsum(bw["dghn"].reshape(ndir * M, H), dbn[:H], rows=M)
             if ndir == 2:
                 ops.colsum(bw["dghn"][1], dbn[H:], rows=M)
@@ -360,11 +360,11 @@ class Engine:
         gk, v = self._posconv_params(P, q)
         wg_hi, wg_lo, norm = self.weights.get(q + "pos_conv", _ver(gk, v), lambda: ops.posconv_pack_weight(gk, v, G, three))
         dpre, dp_hi, dp_lo = ops.act_bwd(dsum, st["pre"], "gelu", three=three, want_f32=True, want_split=True)
-        db = torch.zeros(D, dtype=torch.float32, device=dev)
+        db = ops.zeros(D, device=dev)
         ops.colsum(dpre, db)
         G_[q + "pos_conv_embed.conv.bias"] = db
         Tpad = st["Tpad"]
-        dwg = torch.zeros(D, K * CP, dtype=torch.float32, device=dev)
+        dwg = ops.zeros(D, K * CP, device=dev)
         dp_hi3 = dp_hi.view(B, T, D)
         dp_lo3 = dp_lo.view(B, T, D) if dp_lo is not None else None
         # dgrad as a convolution of its own (no [T, K*CP] unfolded gradient, no red.add fold):
@@ -519,7 +519,7 @@ class Engine:
         seed = S["seed"]
 
         def zeros(n):
-            return torch.zeros(n, dtype=torch.float32, device=dev)
+            return ops.zeros(n, device=dev)
 
         ds_ws = torch.empty(B, NH, T, T, dtype=torch.float32, device=dev)
         if cfg.stable_ln:
@@ -623,7 +623,7 @@ class Engine:
         M = B * T
         d2 = dlogits.reshape(M, cfg.vocab)
         _, d_hi, d_lo = ops.dropout(d2, 0.0, 0, three=self.three, want_f32=False, want_split=True)
-        db = torch.zeros(cfg.vocab, dtype=torch.float32, device=d2.device)
+        db = ops.zeros(cfg.vocab, device=d2.device)
         ops.colsum(d2, db)
         G["w2v_encoder.lm_head.bias"] = db
         G["w2v_encoder.lm_head.weight"] = self._wgrad(d_hi, d_lo, S["hd_hi"], S["hd_lo"], cfg.vocab, cfg.hidden, M)

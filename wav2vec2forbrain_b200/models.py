@@ -26,6 +26,7 @@ import torch
 from torch import nn
 
 from . import engine as _engine
+from . import ops as _ops
 from .config import (N_DAYS, NEURAL_DIM, PRETRAINED_LATENT_SIZES, SMOOTH_TAPS, BrainEncoderConfig, W2VConfig, base_config,
                      conformer_large_config)
 
@@ -145,7 +146,8 @@ class _BrainFn(torch.autograd.Function):
     def backward(ctx, dfeats):
         G: Dict[str, Tensor] = {}
         d = dfeats.reshape(-1, dfeats.shape[-1]).contiguous()
-        ctx.rt.engine.brain_backward(ctx.P, ctx.saved, d, G)
+        with _ops.zero_arena(("brain", id(ctx.rt)), d.device):
+            ctx.rt.engine.brain_backward(ctx.P, ctx.saved, d, G)
         return (None, None, None, None, None, None) + tuple(G.get(n) for n in ctx.names)
 
 
@@ -171,14 +173,15 @@ class _EncoderFn(torch.autograd.Function):
     def backward(ctx, dlogits, dhidden):
         eng = ctx.rt.engine
         G: Dict[str, Tensor] = {}
-        dh = eng.head_backward(ctx.P, ctx.Sh, dlogits.contiguous(), G)
-        if dhidden is not None:
-            dh = dh + eng_dropout_bwd(eng, ctx.Sh, dhidden)
-        if eng.w2v.kind == "base":
-            dfeats = eng.w2v_base_backward(ctx.P, ctx.Se, dh, G)
-        else:
-            from . import conformer
-            dfeats = conformer.backward(eng, ctx.P, ctx.Se, dh, G)
+        with _ops.zero_arena(("w2v", id(ctx.rt)), dlogits.device):
+            dh = eng.head_backward(ctx.P, ctx.Sh, dlogits.contiguous(), G)
+            if dhidden is not None:
+                dh = dh + eng_dropout_bwd(eng, ctx.Sh, dhidden)
+            if eng.w2v.kind == "base":
+                dfeats = eng.w2v_base_backward(ctx.P, ctx.Se, dh, G)
+            else:
+                from . import conformer
+                dfeats = conformer.backward(eng, ctx.P, ctx.Se, dh, G)
         B, T = ctx.Sh["B"], ctx.Sh["T"]
         return (None, None, None, None, None, dfeats.view(B, T, -1)) + tuple(G.get(n) for n in ctx.names)
 

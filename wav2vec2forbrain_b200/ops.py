@@ -103,6 +103,66 @@ def unpermute_unfold_cols(g: Tensor, C: int, KL: int) -> Tensor:
     return out
 
 
+class _ZeroArena:
+    """One memset per backward pass instead of ~500 small fill launches: inside `zero_arena(key, device)` every
+    ops.zeros() is a slice of a single zero-filled fp32 buffer whose size was learned from the previous pass of
+    the same key.  A fresh buffer is allocated per pass (slices may become .grad tensors and must not be reused)."""
+
+    def __init__(self):
+        self.need = {}
+        self.buf = None
+        self.off = 0
+        self.used = 0
+        self.key = None
+
+    def begin(self, key, device):
+        self.key, self.off, self.used = key, 0, 0
+        n = self.need.get(key, 0)
+        self.buf = torch.zeros(n, dtype=torch.float32, device=device) if n else None
+
+    def end(self):
+        if self.key is not None:
+            self.need[self.key] = self.used
+        self.buf, self.key = None, None
+
+    def take(self, shape, device):
+        n = 1
+        for d in shape:
+            n *= int(d)
+        n64 = (n + 63) // 64 * 64      # 256-byte aligned slices (vector kernels want 16)
+        if self.key is None:
+            return torch.zeros(shape, dtype=torch.float32, device=device)
+        self.used += n64
+        if self.buf is not None and self.off + n64 <= self.buf.numel() and self.buf.device == torch.device(device):
+            v = self.buf[self.off:self.off + n].view(shape)
+            self.off += n64
+            return v
+        return torch.zeros(shape, dtype=torch.float32, device=device)
+
+
+_ARENA = _ZeroArena()
+
+
+class zero_arena:
+    def __init__(self, key, device):
+        self.key, self.device = key, device
+
+    def __enter__(self):
+        _ARENA.begin(self.key, self.device)
+        return self
+
+    def __exit__(self, *exc):
+        _ARENA.end()
+        return False
+
+
+def zeros(*shape, device) -> Tensor:
+    """fp32 zeros (from the active zero arena if there is one)."""
+    if len(shape) == 1 and isinstance(shape[0], (tuple, list, torch.Size)):
+        shape = tuple(shape[0])
+    return _ARENA.take(tuple(shape), device)
+
+
 STREAM_K = False         # stream-K schedule switch: off by default (round-1 measurements: slower than whole-tile waves at K <= 4096)
 _SK_WS = {}
 
@@ -514,8 +574,8 @@ def bn_silu_fwd(x: Tensor, stats: Optional[Tensor], gamma: Tensor, beta: Tensor,
 def bn_silu_bwd_stats(ds: Tensor, x: Tensor, mean: Tensor, rstd: Tensor, gamma: Tensor, beta: Tensor):
     """-> (dgamma [D], dbeta [D]) of BatchNorm behind the SiLU."""
     M, D = x.shape
-    dgamma = torch.zeros(D, dtype=torch.float32, device=x.device)
-    dbeta = torch.zeros(D, dtype=torch.float32, device=x.device)
+    dgamma = zeros(D, device=x.device)
+    dbeta = zeros(D, device=x.device)
     check(lib().b2t_bn_silu_bwd_stats(ptr(ds), ptr(x), ptr(mean), ptr(rstd), ptr(gamma), ptr(beta), ptr(dgamma), ptr(dbeta),
                                       c_int64(M), c_int(D), stream()), "b2t_bn_silu_bwd_stats")
     _count()
@@ -528,7 +588,7 @@ def glu_dwconv_bwd(ds: Tensor, x: Tensor, g: Tensor, w: Tensor, mean: Tensor, rs
     D = x.shape[1]
     K = w.shape[-1]
     dg_hi, dg_lo = _bf16_like(g), _bf16_like(g, three)
-    dw = torch.zeros_like(w)
+    dw = zeros(tuple(w.shape), device=w.device)
     check(lib().b2t_glu_dwconv_bwd(ptr(ds), ptr(x), ptr(g), ptr(w), ptr(mean), ptr(rstd), ptr(gamma), ptr(beta), ptr(dgamma),
                                    ptr(dbeta), ptr(dg_hi), ptr(dg_lo), ptr(dw), c_int(B), c_int(T), c_int(D), c_int(K),
                                    c_int(1 if training else 0), stream()), "b2t_glu_dwconv_bwd")
