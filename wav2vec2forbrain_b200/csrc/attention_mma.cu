@@ -51,12 +51,20 @@ __device__ __forceinline__ void pack_split(float x, float y, uint32_t& hi, uint3
     lo = *reinterpret_cast<uint32_t*>(&l);
 }
 
-// fp32 [T, D] slice (row stride ld) -> bf16 hi/lo [TP][D + 8] in shared memory, rows >= T zeroed
+// fp32 [T, D] slice (row stride ld) -> bf16 hi/lo [TP][D + 8] in shared memory, rows >= T zeroed.
+// Two steps so that every global load of a tile (or of several tiles) is in flight before the first
+// conversion: as one loop ptxas kept load -> split -> store order, i.e. 8 serialised L2/DRAM round trips
+// per tile and 24 per kernel prologue with a single CTA per SM to hide them.
 template <int D>
-__device__ __forceinline__ void load_split_tile(const float* __restrict__ src, long ld, int T, float scale, bf16* hi,
-                                                bf16* lo, bool vec) {
-    constexpr int PITCH = D + 8;
-    for (int i = threadIdx.x; i < TP * (D / 4); i += THREADS) {
+struct TileRegs {
+    static constexpr int ITER = TP * (D / 4) / THREADS;
+    float4 v[ITER];
+};
+template <int D>
+__device__ __forceinline__ void load_tile_regs(const float* __restrict__ src, long ld, int T, bool vec, TileRegs<D>& r) {
+#pragma unroll
+    for (int j = 0; j < TileRegs<D>::ITER; ++j) {
+        const int i = threadIdx.x + j * THREADS;
         const int t = i / (D / 4), c4 = (i - t * (D / 4)) * 4;
         float4 v = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         if (t < T) {
@@ -67,12 +75,42 @@ __device__ __forceinline__ void load_split_tile(const float* __restrict__ src, l
                 v.x = p[0], v.y = p[1], v.z = p[2], v.w = p[3];
             }
         }
+        r.v[j] = v;
+    }
+}
+template <int D>
+__device__ __forceinline__ void store_split_regs(const TileRegs<D>& r, float scale, bf16* hi, bf16* lo) {
+    constexpr int PITCH = D + 8;
+#pragma unroll
+    for (int j = 0; j < TileRegs<D>::ITER; ++j) {
+        const int i = threadIdx.x + j * THREADS;
+        const int t = i / (D / 4), c4 = (i - t * (D / 4)) * 4;
         uint2 h, l;
-        pack_split(v.x * scale, v.y * scale, h.x, l.x);
-        pack_split(v.z * scale, v.w * scale, h.y, l.y);
+        pack_split(r.v[j].x * scale, r.v[j].y * scale, h.x, l.x);
+        pack_split(r.v[j].z * scale, r.v[j].w * scale, h.y, l.y);
         *reinterpret_cast<uint2*>(hi + t * PITCH + c4) = h;
         *reinterpret_cast<uint2*>(lo + t * PITCH + c4) = l;
     }
+}
+template <int D>
+__device__ __forceinline__ void load_split_tile(const float* __restrict__ src, long ld, int T, float scale, bf16* hi,
+                                                bf16* lo, bool vec) {
+    TileRegs<D> r;
+    load_tile_regs<D>(src, ld, T, vec, r);
+    store_split_regs<D>(r, scale, hi, lo);
+}
+// three tiles at once (the kernels' prologue): all loads first
+template <int D>
+__device__ __forceinline__ void load_split_tiles3(const float* __restrict__ s0, long ld0, bool vec0, float scale0, bf16* h0, bf16* l0,
+                                                  const float* __restrict__ s1, const float* __restrict__ s2, long ld, bool vec,
+                                                  bf16* h1, bf16* l1, bf16* h2, bf16* l2, int T) {
+    TileRegs<D> r0, r1, r2;
+    load_tile_regs<D>(s0, ld0, T, vec0, r0);
+    load_tile_regs<D>(s1, ld, T, vec, r1);
+    load_tile_regs<D>(s2, ld, T, vec, r2);
+    store_split_regs<D>(r0, scale0, h0, l0);
+    store_split_regs<D>(r1, 1.0f, h1, l1);
+    store_split_regs<D>(r2, 1.0f, h2, l2);
 }
 
 // A fragment (16 rows x 16 k) of a row-major [rows][pitch] tile
@@ -122,9 +160,7 @@ attn_fwd_mma_kernel(const float* __restrict__ qkv, long ld, int q_off, int k_off
     const int b = blockIdx.x / H, h = blockIdx.x % H;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const float* base = qkv + (long)b * T * ld + h * D;
-    load_split_tile<D>(base + q_off, ld, T, scale, Qh, Ql, vec);
-    load_split_tile<D>(base + k_off, ld, T, 1.0f, Kh, Kl, vec);
-    load_split_tile<D>(base + v_off, ld, T, 1.0f, Vh, Vl, vec);
+    load_split_tiles3<D>(base + q_off, ld, vec != 0, scale, Qh, Ql, base + k_off, base + v_off, ld, vec != 0, Kh, Kl, Vh, Vl, T);
     __syncthreads();
     const int row0 = warp * 16;
     if (row0 >= T) return;
@@ -341,9 +377,8 @@ attn_bwd_mma_kernel(const float* __restrict__ qkv, long ld, int q_off, int k_off
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const float* base = qkv + (long)b * T * ld + h * D;
     const long obase = (long)b * T * ld + h * D;
-    load_split_tile<D>(dctx + (long)b * T * ld_ctx + h * D, ld_ctx, T, 1.0f, Oh, Ol, vec_ctx);
-    load_split_tile<D>(base + v_off, ld, T, 1.0f, Vh, Vl, vec);
-    load_split_tile<D>(base + k_off, ld, T, 1.0f, Kh, Kl, vec);
+    load_split_tiles3<D>(dctx + (long)b * T * ld_ctx + h * D, ld_ctx, vec_ctx != 0, 1.0f, Oh, Ol, base + v_off, base + k_off, ld,
+                         vec != 0, Vh, Vl, Kh, Kl, T);
     __syncthreads();
     const int row0 = warp * 16;
     const bool active = row0 < T;
@@ -375,32 +410,32 @@ attn_bwd_mma_kernel(const float* __restrict__ qkv, long ld, int q_off, int k_off
         const long prow0 = (((long)b * H + h) * T + r0) * T, prow1 = (((long)b * H + h) * T + r1) * T;
         float delta0 = 0.0f, delta1 = 0.0f;
         float pd[16][4];
+        // all probability loads first (64 per thread, independent), then the mask / delta arithmetic
 #pragma unroll
         for (int nt = 0; nt < 16; ++nt) {
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
                 const int col = nt * 8 + c2 + e;
-                float p0 = 0.0f, p1 = 0.0f, m0 = 1.0f, m1 = 1.0f;
-                if (col < T) {
-                    if (r0 < T) {
-                        p0 = probs[prow0 + col];
-                        if (drop_p > 0.0f)
-                            m0 = hash_uniform(seed, (unsigned long long)(prow0 + col)) < drop_p ? 0.0f : drop_scale;
-                    }
-                    if (r1 < T) {
-                        p1 = probs[prow1 + col];
-                        if (drop_p > 0.0f)
-                            m1 = hash_uniform(seed, (unsigned long long)(prow1 + col)) < drop_p ? 0.0f : drop_scale;
-                    }
+                pd[nt][e] = (col < T && r0 < T) ? probs[prow0 + col] : 0.0f;
+                pd[nt][2 + e] = (col < T && r1 < T) ? probs[prow1 + col] : 0.0f;
+            }
+        }
+#pragma unroll
+        for (int nt = 0; nt < 16; ++nt) {
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int col = nt * 8 + c2 + e;
+                const float p0 = pd[nt][e], p1 = pd[nt][2 + e];   // undropped P for now
+                float m0 = 1.0f, m1 = 1.0f;
+                if (drop_p > 0.0f && col < T) {
+                    if (r0 < T) m0 = hash_uniform(seed, (unsigned long long)(prow0 + col)) < drop_p ? 0.0f : drop_scale;
+                    if (r1 < T) m1 = hash_uniform(seed, (unsigned long long)(prow1 + col)) < drop_p ? 0.0f : drop_scale;
                 }
                 const float d0 = ds[nt][e] * m0, d1 = ds[nt][2 + e] * m1;
                 delta0 += d0 * p0;
                 delta1 += d1 * p1;
                 ds[nt][e] = d0;
                 ds[nt][2 + e] = d1;
-                pd[nt][e] = p0;          // undropped P for now
-                pd[nt][2 + e] = p1;
-                // pack the mask sign into the value? no: keep the mask by re-deriving below
             }
         }
         delta0 += __shfl_xor_sync(0xffffffffu, delta0, 1);
