@@ -151,14 +151,23 @@ __global__ void __launch_bounds__(256) glu_dwconv_fwd_kernel(const float* __rest
     const bool c_ok = c < D;
     for (int k = warp; k < K; k += 8) sw[k][lane] = c_ok ? w[(long)c * K + k] : 0.0f;
     const int nrows = DW_TT + K - 1;
-    for (int r = warp; r < nrows; r += 8) {
-        const int t = t0 - pad + r;
-        float v = 0.0f;
-        if (c_ok && t >= 0 && t < T) {
-            const float* gr = g + ((long)b * T + t) * 2 * D;
-            v = gr[c] * sigmoid_acc(gr[D + c]);
+    // rows in batches of 4 per warp with every global load issued before the first sigmoid (as one loop the
+    // 19 iterations of a warp each waited for their own two loads)
+    for (int rb = warp; rb < nrows; rb += 32) {
+        float ga[4], gb[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int r = rb + 8 * j, t = t0 - pad + r;
+            const bool ok = c_ok && r < nrows && t >= 0 && t < T;
+            const float* gr = g + ((long)b * T + (ok ? t : 0)) * 2 * D;
+            ga[j] = ok ? gr[c] : 0.0f;
+            gb[j] = ok ? gr[D + c] : 0.0f;
         }
-        s[r][lane] = v;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int r = rb + 8 * j;
+            if (r < nrows) s[r][lane] = ga[j] * sigmoid_acc(gb[j]);
+        }
     }
     __syncthreads();
     float sum = 0.0f, sq = 0.0f;
@@ -292,19 +301,33 @@ __global__ void __launch_bounds__(256) glu_dwconv_bwd_kernel(const float* __rest
     // rows r <-> frame t = t0 - (K-1-pad) + r for dd (needs [t - (K-1-pad), t + pad]) ; keep one
     // common origin t0 - pad' with pad' = K - 1 - pad... for odd K pad' == pad.
     const int nrows = DW_TT + K - 1;
-    for (int r = warp; r < nrows; r += 8) {
-        const int t = t0 - pad + r;
-        float dv = 0.0f, sv = 0.0f;
-        if (c_ok && t >= 0 && t < T) {
-            const long row = (long)b * T + t;
-            const float xh = (x[row * D + c] - mu) * rs;
-            const float dbn = ds[row * D + c] * silu_acc_grad(fmaf(xh, ga, be));
-            dv = ga * rs * (dbn - mdb - xh * mdg);
-            const float* gr = g + row * 2 * D;
-            sv = gr[c] * sigmoid_acc(gr[D + c]);
+    for (int rb = warp; rb < nrows; rb += 32) {   // 4 rows per warp and batch, all 16 loads first
+        float xv[4], dsv4[4], g0[4], g1[4];
+        bool okv[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int r = rb + 8 * j, t = t0 - pad + r;
+            okv[j] = c_ok && r < nrows && t >= 0 && t < T;
+            const long row = (long)b * T + (okv[j] ? t : 0);
+            xv[j] = okv[j] ? x[row * D + c] : 0.0f;
+            dsv4[j] = okv[j] ? ds[row * D + c] : 0.0f;
+            g0[j] = okv[j] ? g[row * 2 * D + c] : 0.0f;
+            g1[j] = okv[j] ? g[row * 2 * D + D + c] : 0.0f;
         }
-        dd[r][lane] = dv;
-        s[r][lane] = sv;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int r = rb + 8 * j;
+            if (r >= nrows) continue;
+            float dv = 0.0f, sv = 0.0f;
+            if (okv[j]) {
+                const float xh = (xv[j] - mu) * rs;
+                const float dbn = dsv4[j] * silu_acc_grad(fmaf(xh, ga, be));
+                dv = ga * rs * (dbn - mdb - xh * mdg);
+                sv = g0[j] * sigmoid_acc(g1[j]);
+            }
+            dd[r][lane] = dv;
+            s[r][lane] = sv;
+        }
     }
     __syncthreads();
     // out[t] = sum_k w[k] s[t + k - pad]  =>  d s[u] = sum_k w[k] d out[u - k + pad]
@@ -316,6 +339,8 @@ __global__ void __launch_bounds__(256) glu_dwconv_bwd_kernel(const float* __rest
         // frame t = t0 + r sits at smem row r + pad
         float dsv = 0.0f;
         const float dout = dd[r + pad][lane];
+        const long grow = ((long)b * T + t0 + r) * 2 * D;
+        const float ga_in = c_ok ? g[grow + c] : 0.0f, gb_in = c_ok ? g[grow + D + c] : 0.0f;   // in flight during the taps
 #pragma unroll
         for (int k = 0; k < DW_MAX_K; ++k) {
             if (k < K) {
@@ -325,8 +350,7 @@ __global__ void __launch_bounds__(256) glu_dwconv_bwd_kernel(const float* __rest
         }
         if (c_ok) {
             const long row = (long)b * T + t0 + r;
-            const float* gr = g + row * 2 * D;
-            const float a = gr[c], sg = sigmoid_acc(gr[D + c]);
+            const float a = ga_in, sg = sigmoid_acc(gb_in);
             const float da = dsv * sg, dgate = dsv * a * sg * (1.0f - sg);
             bf16 h, l;
             split_bf16(da, h, l);
