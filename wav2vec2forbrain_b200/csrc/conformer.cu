@@ -171,12 +171,44 @@ __global__ void __launch_bounds__(256) glu_dwconv_fwd_kernel(const float* __rest
     }
     __syncthreads();
     float sum = 0.0f, sq = 0.0f;
-    for (int r = warp; r < DW_TT && t0 + r < T; r += 8) {
-        float acc = 0.0f;
-        for (int k = 0; k < K; ++k) acc = fmaf(sw[k][lane], s[r + k][lane], acc);
-        if (c_ok) out[((long)b * T + t0 + r) * D + c] = acc;
-        sum += acc;
-        sq += acc * acc;
+    if (K == 31) {
+        // register-blocked over time (the path's kernel length): a thread keeps the 31 taps and computes 8
+        // consecutive frames from 38 window values - 69 smem loads per 8 outputs instead of 496; taps are still
+        // applied in k = 0..30 order per output (same rounding as the plain loop)
+        constexpr int KK = 31, FR = 8;
+        float wk[KK];
+#pragma unroll
+        for (int k = 0; k < KK; ++k) wk[k] = sw[k][lane];
+        for (int rg = warp * FR; rg < DW_TT && t0 + rg < T; rg += 8 * FR) {
+            float acc[FR];
+#pragma unroll
+            for (int o = 0; o < FR; ++o) acc[o] = 0.0f;
+#pragma unroll
+            for (int j = 0; j < FR + KK - 1; ++j) {
+                const float v = s[rg + j][lane];
+#pragma unroll
+                for (int o = 0; o < FR; ++o) {
+                    const int k = j - o;
+                    if (k >= 0 && k < KK) acc[o] = fmaf(wk[k], v, acc[o]);
+                }
+            }
+#pragma unroll
+            for (int o = 0; o < FR; ++o) {
+                if (t0 + rg + o < T) {
+                    if (c_ok) out[((long)b * T + t0 + rg + o) * D + c] = acc[o];
+                    sum += acc[o];
+                    sq += acc[o] * acc[o];
+                }
+            }
+        }
+    } else {
+        for (int r = warp; r < DW_TT && t0 + r < T; r += 8) {
+            float acc = 0.0f;
+            for (int k = 0; k < K; ++k) acc = fmaf(sw[k][lane], s[r + k][lane], acc);
+            if (c_ok) out[((long)b * T + t0 + r) * D + c] = acc;
+            sum += acc;
+            sq += acc * acc;
+        }
     }
     if (ssum) {
         red[0][warp][lane] = sum;
@@ -335,30 +367,75 @@ __global__ void __launch_bounds__(256) glu_dwconv_bwd_kernel(const float* __rest
     float wacc[DW_MAX_K];
 #pragma unroll
     for (int k = 0; k < DW_MAX_K; ++k) wacc[k] = 0.0f;
-    for (int r = warp; r < DW_TT && t0 + r < T; r += 8) {
-        // frame t = t0 + r sits at smem row r + pad
-        float dsv = 0.0f;
-        const float dout = dd[r + pad][lane];
-        const long grow = ((long)b * T + t0 + r) * 2 * D;
-        const float ga_in = c_ok ? g[grow + c] : 0.0f, gb_in = c_ok ? g[grow + D + c] : 0.0f;   // in flight during the taps
+    auto emit = [&](int r, float dsv, float ga_in, float gb_in) {
+        const long row = (long)b * T + t0 + r;
+        const float a = ga_in, sg = sigmoid_acc(gb_in);
+        const float da = dsv * sg, dgate = dsv * a * sg * (1.0f - sg);
+        bf16 h, l;
+        split_bf16(da, h, l);
+        dg_hi[row * 2 * D + c] = h;
+        if (dg_lo) dg_lo[row * 2 * D + c] = l;
+        split_bf16(dgate, h, l);
+        dg_hi[row * 2 * D + D + c] = h;
+        if (dg_lo) dg_lo[row * 2 * D + D + c] = l;
+    };
+    if (K == 31) {
+        // register-blocked over 8 consecutive frames (see the forward kernel): the taps and the 31 weight-gradient
+        // accumulators stay in registers, each window value of dd / s is read once per 8 outputs
+        constexpr int KK = 31, FR = 8, PD = 15;
+        float wk[KK];
 #pragma unroll
-        for (int k = 0; k < DW_MAX_K; ++k) {
-            if (k < K) {
-                dsv = fmaf(sw[k][lane], dd[r + 2 * pad - k][lane], dsv);
-                wacc[k] = fmaf(dout, s[r + k][lane], wacc[k]);
+        for (int k = 0; k < KK; ++k) wk[k] = sw[k][lane];
+        for (int rg = warp * FR; rg < DW_TT && t0 + rg < T; rg += 8 * FR) {
+            float gin0[FR], gin1[FR], dsv[FR], dout[FR];
+#pragma unroll
+            for (int o = 0; o < FR; ++o) {
+                const bool ok = c_ok && t0 + rg + o < T;
+                const long grow = ((long)b * T + (ok ? t0 + rg + o : 0)) * 2 * D;
+                gin0[o] = ok ? g[grow + c] : 0.0f;            // in flight during the tap loops
+                gin1[o] = ok ? g[grow + D + c] : 0.0f;
+                dsv[o] = 0.0f;
+                dout[o] = t0 + rg + o < T ? dd[rg + o + PD][lane] : 0.0f;
+            }
+#pragma unroll
+            for (int j = FR + KK - 2; j >= 0; --j) {   // descending j = ascending tap index per output
+                const float v = dd[rg + j][lane];
+#pragma unroll
+                for (int o = 0; o < FR; ++o) {
+                    const int k = o + 2 * PD - j;
+                    if (k >= 0 && k < KK) dsv[o] = fmaf(wk[k], v, dsv[o]);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < FR + KK - 1; ++j) {
+                const float v = s[rg + j][lane];
+#pragma unroll
+                for (int o = 0; o < FR; ++o) {
+                    const int k = j - o;
+                    if (k >= 0 && k < KK) wacc[k] = fmaf(dout[o], v, wacc[k]);
+                }
+            }
+            if (c_ok) {
+#pragma unroll
+                for (int o = 0; o < FR; ++o)
+                    if (t0 + rg + o < T) emit(rg + o, dsv[o], gin0[o], gin1[o]);
             }
         }
-        if (c_ok) {
-            const long row = (long)b * T + t0 + r;
-            const float a = ga_in, sg = sigmoid_acc(gb_in);
-            const float da = dsv * sg, dgate = dsv * a * sg * (1.0f - sg);
-            bf16 h, l;
-            split_bf16(da, h, l);
-            dg_hi[row * 2 * D + c] = h;
-            if (dg_lo) dg_lo[row * 2 * D + c] = l;
-            split_bf16(dgate, h, l);
-            dg_hi[row * 2 * D + D + c] = h;
-            if (dg_lo) dg_lo[row * 2 * D + D + c] = l;
+    } else {
+        for (int r = warp; r < DW_TT && t0 + r < T; r += 8) {
+            // frame t = t0 + r sits at smem row r + pad
+            float dsv = 0.0f;
+            const float dout = dd[r + pad][lane];
+            const long grow = ((long)b * T + t0 + r) * 2 * D;
+            const float ga_in = c_ok ? g[grow + c] : 0.0f, gb_in = c_ok ? g[grow + D + c] : 0.0f;   // in flight during the taps
+#pragma unroll
+            for (int k = 0; k < DW_MAX_K; ++k) {
+                if (k < K) {
+                    dsv = fmaf(sw[k][lane], dd[r + 2 * pad - k][lane], dsv);
+                    wacc[k] = fmaf(dout, s[r + k][lane], wacc[k]);
+                }
+            }
+            if (c_ok) emit(r, dsv, ga_in, gb_in);
         }
     }
 #pragma unroll
