@@ -263,13 +263,20 @@ __global__ void __launch_bounds__(128) bn_silu_fwd_kernel(const float* __restric
     const float ga = gamma[c] * rstd, be = beta[c] - mean * gamma[c] * rstd;
     const long r0 = (long)blockIdx.y * BN_RPB;
     const long r1 = r0 + BN_RPB < M ? r0 + BN_RPB : M;
-    for (long r = r0; r < r1; ++r) {
-        const long off = r * D + c;
-        const float y = silu_acc(fmaf(x[off], ga, be));
-        bf16 h, l;
-        split_bf16(y, h, l);
-        y_hi[off] = h;
-        if (y_lo) y_lo[off] = l;
+    for (long rb = r0; rb < r1; rb += 8) {   // 8 rows per batch, loads first
+        float xv[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) xv[j] = rb + j < r1 ? x[(rb + j) * D + c] : 0.0f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            if (rb + j >= r1) break;
+            const long off = (rb + j) * D + c;
+            const float y = silu_acc(fmaf(xv[j], ga, be));
+            bf16 h, l;
+            split_bf16(y, h, l);
+            y_hi[off] = h;
+            if (y_lo) y_lo[off] = l;
+        }
     }
 }
 
@@ -285,12 +292,22 @@ __global__ void __launch_bounds__(128) bn_silu_bwd_stats_kernel(const float* __r
     const long r0 = (long)blockIdx.y * BN_RPB;
     const long r1 = r0 + BN_RPB < M ? r0 + BN_RPB : M;
     float sb = 0.0f, sg = 0.0f;
-    for (long r = r0; r < r1; ++r) {
-        const long off = r * D + c;
-        const float xh = (x[off] - mu) * rs;
-        const float dbn = ds[off] * silu_acc_grad(fmaf(xh, ga, be));
-        sb += dbn;
-        sg += dbn * xh;
+    for (long rb = r0; rb < r1; rb += 8) {   // 8 rows per batch, all 16 loads first
+        float xv[8], dv[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const bool ok = rb + j < r1;
+            xv[j] = ok ? x[(rb + j) * D + c] : 0.0f;
+            dv[j] = ok ? ds[(rb + j) * D + c] : 0.0f;
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            if (rb + j >= r1) break;
+            const float xh = (xv[j] - mu) * rs;
+            const float dbn = dv[j] * silu_acc_grad(fmaf(xh, ga, be));
+            sb += dbn;
+            sg += dbn * xh;
+        }
     }
     atomicAdd(dbeta + c, sb);
     atomicAdd(dgamma + c, sg);
