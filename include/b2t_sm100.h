@@ -92,6 +92,8 @@ typedef struct {
 } b2t_gemm_args;
 
 int b2t_gemm(const b2t_gemm_args* args, b2t_stream stream);
+/* cap the persistent grid at `sms` CTAs (0 = all SMs): leaves SMs to a concurrent collective (also env B2T_GEMM_SMS) */
+int b2t_gemm_set_sm_limit(int sms);
 /* bytes of b2t_gemm_args.sk_workspace that cover every tile shape on the current device */
 int64_t b2t_gemm_workspace_bytes(void);
 

@@ -174,6 +174,7 @@ def backward(eng, P, S: dict, dh: Tensor, G: Dict[str, Tensor]) -> Tensor:
     dh, _, _ = _ln_bwd(eng, P, G, Q + "layer_norm", dh, S["enc_ln"]["x"], S["enc_ln"]["ln"], want_split=False)
     ds_ws = torch.empty(B, NH, T, T, dtype=torch.float32, device=dev)
     for i in reversed(range(cfg.layers)):
+        eng.emit_grads(G)   # gradients of the layers above are complete: start their all-reduce (data parallel)
         st = S["layers"][i]
         if st is None:
             continue

@@ -964,14 +964,21 @@ int make_map(CUtensorMap* map, const void* ptr, int64_t d0, int64_t d1, int64_t 
     return 0;
 }
 
+// SMs the persistent grid may use.  B2T_GEMM_SMS / b2t_gemm_set_sm_limit leave SMs free for a concurrent
+// collective: a persistent grid of one CTA per SM whose tiles are statically strided runs a second wave for
+// the CTAs that could not get an SM while NCCL kernels hold some (measured at 2 GPUs: the step grows by about
+// the all-reduce time).
+int g_sm_limit = 0;
 int num_sms() {
     static int n = 0;
     if (!n) {
         int dev = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        const char* e = getenv("B2T_GEMM_SMS");
+        if (e && atoi(e) > 0 && g_sm_limit == 0) g_sm_limit = atoi(e);
     }
-    return n;
+    return (g_sm_limit > 0 && g_sm_limit < n) ? g_sm_limit : n;
 }
 
 template <int NTERMS, bool A_MN, bool B_MN, int BN>
@@ -1024,8 +1031,13 @@ int dispatch_major(const b2t_gemm_args* a, const KParams& kp, cudaStream_t s) {
 
 }  // namespace
 
+extern "C" int b2t_gemm_set_sm_limit(int sms) {
+    g_sm_limit = sms > 0 ? sms : 0;
+    return 0;
+}
+
 extern "C" int64_t b2t_gemm_workspace_bytes(void) {
-    return (int64_t)SK_FLAG_BYTES + (int64_t)num_sms() * BM * 256 * (int64_t)sizeof(float);
+    return (int64_t)SK_FLAG_BYTES + (int64_t)256 * BM * 256 * (int64_t)sizeof(float);
 }
 
 extern "C" int b2t_gemm(const b2t_gemm_args* a, b2t_stream stream_) {

@@ -46,6 +46,14 @@ def shard_indices(n: int, rank: int, world: int) -> List[int]:
     return list(range(rank, n, world))
 
 
+class _null:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        return False
+
+
 class GradientBuckets:
     """Bucketed asynchronous all-reduce(mean) of parameter gradients.
 
@@ -62,6 +70,14 @@ class GradientBuckets:
         self.params = [p for p in params if p.requires_grad]
         self.overlap = overlap and torch.cuda.is_available()
         self.stream = torch.cuda.Stream() if self.overlap else None
+        self.bucket_bytes = bucket_bytes
+        # early path (sink / sync_early): gradients handed over by the engine while the backward schedule of the
+        # same autograd node is still being issued; keyed by parameter name
+        self.param_of_name: Dict[str, nn.Parameter] = {}
+        self._early: List[torch.Tensor] = []
+        self._early_bytes = 0
+        self._early_work = []
+        self._early_done = set()
         self.buckets: List[List[nn.Parameter]] = []
         cur, size = [], 0
         for p in reversed(self.params):
@@ -88,6 +104,59 @@ class GradientBuckets:
         self._launched = [False] * len(self.buckets)
         self._work = []
         self._active = False
+        self._early_done = set()
+
+    # ---- early path ---------------------------------------------------------------------------------
+    def sink(self, named) -> None:
+        """named: [(parameter name, finished gradient tensor)].  The three autograd nodes of the model return all
+        their gradients at once, so post-accumulate hooks alone cannot overlap anything with the node's own
+        backward; the engine calls this after every encoder layer instead.  Full buckets start their all-reduce on
+        the side stream right away (behind everything issued so far on the compute stream)."""
+        for name, g in named:
+            p = self.param_of_name.get(name)
+            if p is None or not p.requires_grad:
+                continue
+            self._active = True
+            self._early.append(g)
+            self._early_done.add(id(p))
+            self._early_bytes += g.numel() * g.element_size()
+        if self._early_bytes >= self.bucket_bytes:
+            self._flush_early()
+
+    def _flush_early(self) -> None:
+        grads, self._early, self._early_bytes = self._early, [], 0
+        if not grads:
+            return
+        if self.overlap:
+            self.stream.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(self.stream):
+                flat = torch.cat([g.reshape(-1) for g in grads])
+                flat.div_(self.world)
+                work = dist.all_reduce(flat, group=self.group, async_op=True)
+        else:
+            flat = torch.cat([g.reshape(-1) for g in grads])
+            flat.div_(self.world)
+            dist.all_reduce(flat, group=self.group)
+            work = None
+        self._early_work.append((work, flat, grads))
+
+    def sync_early(self) -> None:
+        """End of an autograd node: reduce what is left and write every averaged value back into the tensors
+        the node is about to return, ordered before anything autograd does with them."""
+        self._flush_early()
+        for work, flat, grads in self._early_work:
+            ctx = torch.cuda.stream(self.stream) if self.overlap else _null()
+            with ctx:
+                if work is not None:
+                    work.wait()
+                off = 0
+                for g in grads:
+                    n = g.numel()
+                    g.copy_(flat[off:off + n].view_as(g))
+                    off += n
+        if self.overlap and self._early_work:
+            torch.cuda.current_stream().wait_stream(self.stream)
+        self._early_work = []
 
     def _on_grad(self, p: nn.Parameter) -> None:
         self._active = True
@@ -98,7 +167,7 @@ class GradientBuckets:
 
     def _launch(self, bi: int) -> None:
         self._launched[bi] = True
-        grads = [p.grad for p in self.buckets[bi] if p.grad is not None]
+        grads = [p.grad for p in self.buckets[bi] if p.grad is not None and id(p) not in self._early_done]
         if not grads:
             return
         if self.overlap:
@@ -152,7 +221,8 @@ class DataParallel:
     initial weights/buffers from rank 0, installs the bucket hooks, and waits for the all-reduce in an
     optimizer step pre-hook (call `finish()` yourself before clip_grad_norm_)."""
 
-    def __init__(self, model: nn.Module, bucket_bytes: int = 48 << 20, process_group=None, overlap: bool = True):
+    def __init__(self, model: nn.Module, bucket_bytes: int = 48 << 20, process_group=None, overlap: bool = True,
+                 early_reduce: Optional[bool] = None):
         self.model = model
         self.group = process_group
         for t in list(model.parameters()) + list(model.buffers()):
@@ -161,6 +231,16 @@ class DataParallel:
         if rt is not None:
             rt.rank = dist.get_rank(process_group)   # per-rank dropout masks; LayerDrop generator stays shared
         self.buckets = GradientBuckets(list(model.parameters()), bucket_bytes, process_group, overlap)
+        # early_reduce: start each bucket's all-reduce from inside the encoder's backward schedule (engine.emit_grads)
+        # instead of after the whole autograd node.  Off by default: measured on 2 B200 (conformer-large, B = 32 per
+        # GPU) the early path is SLOWER (963 vs 991 trials/s) - NCCL's CTAs take SMs from the persistent one-CTA-per-SM
+        # GEMM grid, whose statically strided tiles then need a second wave.  B2T_DP_EARLY=1 turns it on.
+        if early_reduce is None:
+            early_reduce = os.environ.get("B2T_DP_EARLY", "0") == "1"
+        if early_reduce and rt is not None and hasattr(rt, "engine"):
+            self.buckets.param_of_name = dict(model.named_parameters())
+            rt.engine.grad_sink = self.buckets.sink
+            rt.engine.grad_sync = self.buckets.sync_early
 
     def attach_optimizer(self, optimizer: torch.optim.Optimizer) -> None:
         optimizer.register_step_pre_hook(lambda opt, args, kwargs: self.finish())

@@ -71,6 +71,37 @@ class Engine:
             raise NotImplementedError(f"encoder_fc_activation_function={be.fc_act}")
 
     # ------------------------------------------------------------------------------------------
+    # gradient sink: data parallel training hands finished gradients to the all-reduce while the backward
+    # schedule of the same autograd node is still being issued (dist.GradientBuckets.sink); None = single GPU
+    # ------------------------------------------------------------------------------------------
+    grad_sink = None
+    grad_sync = None
+
+    def begin_grads(self) -> None:
+        self._emitted = set()
+
+    def emit_grads(self, G: Dict[str, Tensor]) -> None:
+        """Everything in G that was not handed over yet is final (a layer only writes its own keys)."""
+        if self.grad_sink is None:
+            return
+        done = getattr(self, "_emitted", None)
+        if done is None:
+            done = self._emitted = set()
+        new = [(k, v) for k, v in G.items() if k not in done and v is not None]
+        if new:
+            done.update(k for k, _ in new)
+            self.grad_sink(new)
+
+    def sync_grads(self, G: Dict[str, Tensor]) -> None:
+        """End of an autograd node: the rest is handed over and every early all-reduce is written back before
+        autograd sees the tensors."""
+        if self.grad_sink is None:
+            return
+        self.emit_grads(G)
+        self.grad_sync()
+        self._emitted = set()
+
+    # ------------------------------------------------------------------------------------------
     # helpers
     # ------------------------------------------------------------------------------------------
     def _w(self, P, name: str):
@@ -528,6 +559,7 @@ class Engine:
             dh, _, _ = ops.layernorm_bwd(dh, hin, P[q + "layer_norm.weight"], mf, rf, G[q + "layer_norm.weight"],
                                          G[q + "layer_norm.bias"], three=three, want_split=False)
         for i in reversed(range(cfg.layers)):
+            self.emit_grads(G)   # gradients of the layers above are complete: start their all-reduce (data parallel)
             st = S["layers"][i]
             if st is None:
                 continue

@@ -148,6 +148,7 @@ class _BrainFn(torch.autograd.Function):
         d = dfeats.reshape(-1, dfeats.shape[-1]).contiguous()
         with _ops.zero_arena(("brain", id(ctx.rt)), d.device):
             ctx.rt.engine.brain_backward(ctx.P, ctx.saved, d, G)
+            ctx.rt.engine.sync_grads(G)
         return (None, None, None, None, None, None) + tuple(G.get(n) for n in ctx.names)
 
 
@@ -182,6 +183,7 @@ class _EncoderFn(torch.autograd.Function):
             else:
                 from . import conformer
                 dfeats = conformer.backward(eng, ctx.P, ctx.Se, dh, G)
+            eng.sync_grads(G)
         B, T = ctx.Sh["B"], ctx.Sh["T"]
         return (None, None, None, None, None, dfeats.view(B, T, -1)) + tuple(G.get(n) for n in ctx.names)
 
