@@ -7,7 +7,3 @@ timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; tail -1
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_reference.log 2>&1; tail -1 gpurun_out/bench_reference.log | cut -c1-300
 timeout 600 python bench.py > gpurun_out/bench_base.log 2>&1; tail -1 gpurun_out/bench_base.log | cut -c1-300
 timeout 600 python bench.py --workload conformer > gpurun_out/bench_conformer.log 2>&1; tail -1 gpurun_out/bench_conformer.log | cut -c1-300
-python scripts/gemm_bench.py prof > gpurun_out/gemm_prof_plain.log 2>&1 &&
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:gemm_tc_kernel -c 8 -f -o gpurun_out/gemm_final \
-    python scripts/gemm_bench.py prof > gpurun_out/gemm_final_ncu.log 2>&1
-cat gpurun_out/gemm_prof_plain.log | cut -c1-150
