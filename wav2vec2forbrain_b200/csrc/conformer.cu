@@ -127,7 +127,8 @@ __global__ void rope_bwd_add_kernel(const float* __restrict__ d_rot, long ld_rot
     }
 }
 
-__device__ __forceinline__ float sigmoid_acc(float x) { return 1.0f / (1.0f + expf(-x)); }
+// ex2.approx + rcp.approx (~1e-7 relative): the IEEE division's slow-path branch serialised the unrolled row batches
+__device__ __forceinline__ float sigmoid_acc(float x) { return rcp_approx(1.0f + __expf(-x)); }
 __device__ __forceinline__ float silu_acc(float x) { return x * sigmoid_acc(x); }
 __device__ __forceinline__ float silu_acc_grad(float x) {
     const float s = sigmoid_acc(x);
