@@ -61,6 +61,8 @@ if __name__ == "__main__":
         pre(64); pre(32); sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "ln":
         ln(3776, 1024); sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "conv":
+        conv(32); sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "gru":
         gru(32); sys.exit(0)
     gru(64); gru(32)

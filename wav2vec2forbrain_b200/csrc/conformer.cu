@@ -128,7 +128,13 @@ __global__ void rope_bwd_add_kernel(const float* __restrict__ d_rot, long ld_rot
 }
 
 // ex2.approx + rcp.approx (~1e-7 relative): the IEEE division's slow-path branch serialised the unrolled row batches
-__device__ __forceinline__ float sigmoid_acc(float x) { return rcp_approx(1.0f + __expf(-x)); }
+// ex2.approx.ftz: no denormal-range fix-up code around the MUFU (a flushed result gives sigmoid = 1, inf gives 0)
+__device__ __forceinline__ float ex2_ftz(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float sigmoid_acc(float x) { return rcp_approx(1.0f + ex2_ftz(-1.4426950408889634f * x)); }
 __device__ __forceinline__ float silu_acc(float x) { return x * sigmoid_acc(x); }
 __device__ __forceinline__ float silu_acc_grad(float x) {
     const float s = sigmoid_acc(x);
@@ -330,12 +336,19 @@ __global__ void __launch_bounds__(256) glu_dwconv_bwd_kernel(const float* __rest
     float (*s)[DW_CH] = reinterpret_cast<float (*)[DW_CH]>(dyn + DW_ROWS * DW_CH);      // glu, with halo
     float (*sw)[DW_CH] = reinterpret_cast<float (*)[DW_CH]>(dyn + 2 * DW_ROWS * DW_CH);
     float (*acc_w)[DW_CH] = reinterpret_cast<float (*)[DW_CH]>(dyn + (2 * DW_ROWS + DW_MAX_K) * DW_CH);
+    // GLU value and gate sigmoid of the tile's own frames, kept for the GLU backward at the end (no second read of g)
+    float (*sa)[DW_CH] = reinterpret_cast<float (*)[DW_CH]>(dyn + (2 * DW_ROWS + 2 * DW_MAX_K) * DW_CH);
+    float (*ssg)[DW_CH] = reinterpret_cast<float (*)[DW_CH]>(dyn + (2 * DW_ROWS + 2 * DW_MAX_K + DW_TT) * DW_CH);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int c = blockIdx.x * DW_CH + lane;
     const int b = blockIdx.y;
     const int t0 = blockIdx.z * DW_TT;
     const int pad = (K - 1) / 2;
     const bool c_ok = c < D;
+    // per-CTA base pointers, 32-bit offsets inside one trial (T * 2D < 2^31)
+    const float* __restrict__ xb = x + (long)b * T * D + c;
+    const float* __restrict__ dsb = ds + (long)b * T * D + c;
+    const float* __restrict__ gb = g + (long)b * T * 2 * D + c;
     for (int k = warp; k < K; k += 8) {
         sw[k][lane] = c_ok ? w[(long)c * K + k] : 0.0f;
         acc_w[k][lane] = 0.0f;
@@ -358,25 +371,28 @@ __global__ void __launch_bounds__(256) glu_dwconv_bwd_kernel(const float* __rest
         for (int j = 0; j < 4; ++j) {
             const int r = rb + 8 * j, t = t0 - pad + r;
             okv[j] = c_ok && r < nrows && t >= 0 && t < T;
-            const long row = (long)b * T + (okv[j] ? t : 0);
-            xv[j] = okv[j] ? x[row * D + c] : 0.0f;
-            dsv4[j] = okv[j] ? ds[row * D + c] : 0.0f;
-            g0[j] = okv[j] ? g[row * 2 * D + c] : 0.0f;
-            g1[j] = okv[j] ? g[row * 2 * D + D + c] : 0.0f;
+            const int to = okv[j] ? t : 0;
+            xv[j] = okv[j] ? xb[to * D] : 0.0f;
+            dsv4[j] = okv[j] ? dsb[to * D] : 0.0f;
+            g0[j] = okv[j] ? gb[to * 2 * D] : 0.0f;
+            g1[j] = okv[j] ? gb[to * 2 * D + D] : 0.0f;
         }
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
+        for (int j = 0; j < 4; ++j) {   // branch-free: masked frames carry zeros through the math
             const int r = rb + 8 * j;
-            if (r >= nrows) continue;
-            float dv = 0.0f, sv = 0.0f;
-            if (okv[j]) {
-                const float xh = (xv[j] - mu) * rs;
-                const float dbn = dsv4[j] * silu_acc_grad(fmaf(xh, ga, be));
-                dv = ga * rs * (dbn - mdb - xh * mdg);
-                sv = g0[j] * sigmoid_acc(g1[j]);
+            const float xh = (xv[j] - mu) * rs;
+            const float dbn = dsv4[j] * silu_acc_grad(fmaf(xh, ga, be));
+            const float dv = okv[j] ? ga * rs * (dbn - mdb - xh * mdg) : 0.0f;
+            const float sg = sigmoid_acc(g1[j]);
+            if (r < nrows) {   // warp-uniform
+                dd[r][lane] = dv;
+                s[r][lane] = g0[j] * sg;
+                const int rc = r - pad;
+                if (rc >= 0 && rc < DW_TT) {
+                    sa[rc][lane] = g0[j];
+                    ssg[rc][lane] = sg;
+                }
             }
-            dd[r][lane] = dv;
-            s[r][lane] = sv;
         }
     }
     __syncthreads();
@@ -385,17 +401,19 @@ __global__ void __launch_bounds__(256) glu_dwconv_bwd_kernel(const float* __rest
     float wacc[DW_MAX_K];
 #pragma unroll
     for (int k = 0; k < DW_MAX_K; ++k) wacc[k] = 0.0f;
-    auto emit = [&](int r, float dsv, float ga_in, float gb_in) {
-        const long row = (long)b * T + t0 + r;
-        const float a = ga_in, sg = sigmoid_acc(gb_in);
+    bf16* __restrict__ dgh = dg_hi + ((long)b * T + t0) * 2 * D + c;
+    bf16* __restrict__ dgl = dg_lo ? dg_lo + ((long)b * T + t0) * 2 * D + c : nullptr;
+    auto emit = [&](int r, float dsv) {
+        const float a = sa[r][lane], sg = ssg[r][lane];
         const float da = dsv * sg, dgate = dsv * a * sg * (1.0f - sg);
+        const int off = r * 2 * D;
         bf16 h, l;
         split_bf16(da, h, l);
-        dg_hi[row * 2 * D + c] = h;
-        if (dg_lo) dg_lo[row * 2 * D + c] = l;
+        dgh[off] = h;
+        if (dgl) dgl[off] = l;
         split_bf16(dgate, h, l);
-        dg_hi[row * 2 * D + D + c] = h;
-        if (dg_lo) dg_lo[row * 2 * D + D + c] = l;
+        dgh[off + D] = h;
+        if (dgl) dgl[off + D] = l;
     };
     if (K == 31) {
         // register-blocked over 8 consecutive frames (see the forward kernel): the taps and the 31 weight-gradient
@@ -405,13 +423,9 @@ __global__ void __launch_bounds__(256) glu_dwconv_bwd_kernel(const float* __rest
 #pragma unroll
         for (int k = 0; k < KK; ++k) wk[k] = sw[k][lane];
         for (int rg = warp * FR; rg < DW_TT && t0 + rg < T; rg += 8 * FR) {
-            float gin0[FR], gin1[FR], dsv[FR], dout[FR];
+            float dsv[FR], dout[FR];
 #pragma unroll
             for (int o = 0; o < FR; ++o) {
-                const bool ok = c_ok && t0 + rg + o < T;
-                const long grow = ((long)b * T + (ok ? t0 + rg + o : 0)) * 2 * D;
-                gin0[o] = ok ? g[grow + c] : 0.0f;            // in flight during the tap loops
-                gin1[o] = ok ? g[grow + D + c] : 0.0f;
                 dsv[o] = 0.0f;
                 dout[o] = t0 + rg + o < T ? dd[rg + o + PD][lane] : 0.0f;
             }
@@ -436,7 +450,7 @@ __global__ void __launch_bounds__(256) glu_dwconv_bwd_kernel(const float* __rest
             if (c_ok) {
 #pragma unroll
                 for (int o = 0; o < FR; ++o)
-                    if (t0 + rg + o < T) emit(rg + o, dsv[o], gin0[o], gin1[o]);
+                    if (t0 + rg + o < T) emit(rg + o, dsv[o]);
             }
         }
     } else {
@@ -444,8 +458,6 @@ __global__ void __launch_bounds__(256) glu_dwconv_bwd_kernel(const float* __rest
             // frame t = t0 + r sits at smem row r + pad
             float dsv = 0.0f;
             const float dout = dd[r + pad][lane];
-            const long grow = ((long)b * T + t0 + r) * 2 * D;
-            const float ga_in = c_ok ? g[grow + c] : 0.0f, gb_in = c_ok ? g[grow + D + c] : 0.0f;   // in flight during the taps
 #pragma unroll
             for (int k = 0; k < DW_MAX_K; ++k) {
                 if (k < K) {
@@ -453,7 +465,7 @@ __global__ void __launch_bounds__(256) glu_dwconv_bwd_kernel(const float* __rest
                     wacc[k] = fmaf(dout, s[r + k][lane], wacc[k]);
                 }
             }
-            if (c_ok) emit(r, dsv, ga_in, gb_in);
+            if (c_ok) emit(r, dsv);
         }
     }
 #pragma unroll
@@ -464,7 +476,7 @@ __global__ void __launch_bounds__(256) glu_dwconv_bwd_kernel(const float* __rest
         for (int k = warp; k < K; k += 8) atomicAdd(dw + (long)c * K + k, acc_w[k][lane]);
 }
 
-constexpr size_t DW_BWD_SMEM = (size_t)(2 * DW_ROWS + 2 * DW_MAX_K) * DW_CH * sizeof(float);
+constexpr size_t DW_BWD_SMEM = (size_t)(2 * DW_ROWS + 2 * DW_MAX_K + 2 * DW_TT) * DW_CH * sizeof(float);
 
 inline int grid_for(long n, int block, int cap_mult = 16) {
     long g = (n + block - 1) / block;
