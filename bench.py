@@ -18,6 +18,7 @@ box) on the host cores, on a bounded sample (8 trials per step) of the same work
 from __future__ import annotations
 
 import argparse
+import datetime
 import json
 import os
 import subprocess
@@ -164,18 +165,101 @@ def to_device_batch(models, hb, device):
     return b
 
 
+class NvmlSampler:
+    """In-process NVML (what nvidia-smi reads) from a thread, two queries every 250 ms while the timed region runs.
+    Preferred over the nvidia-smi process below: on some boxes each poll of the 9-field nvidia-smi query stalls kernel
+    launches for 25-50 ms (conformer step 58.7 -> 66-77 ms with 6-7 polls inside the timed region; the end-to-end loop,
+    timed without a sampler, was unaffected)."""
+
+    def __init__(self, dev_index: int, period: float = 0.25):
+        import threading
+        import pynvml
+        self.nv = pynvml
+        pynvml.nvmlInit()
+        try:
+            self.h = pynvml.nvmlDeviceGetHandleByUUID("GPU-" + str(torch.cuda.get_device_properties(dev_index).uuid))
+        except Exception:
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(dev_index)
+        self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        self._sample()            # first call of each query outside the timed region
+        self.rows = []
+        self.on = False
+        self.period = period
+        self.ev = threading.Event()
+        self.t = threading.Thread(target=self._run, daemon=True)
+        self.t.start()
+
+    def _sample(self):
+        return (float(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)),
+                int(self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)))
+
+    def _run(self):
+        while not self.ev.wait(self.period):
+            if self.on:
+                try:
+                    self.rows.append(self._sample())
+                except Exception:
+                    pass
+
+    def wait_ready(self):
+        pass
+
+    def mark(self):
+        self.on = True
+
+    def stop(self):
+        self.on = False
+        self.ev.set()
+        self.t.join(timeout=2)
+        out = {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "source": "nvml"}
+        rows = self.rows
+        if rows:
+            sm = sorted(r[0] for r in rows)
+            out["sm_mhz"] = sm[len(sm) // 2]
+            bits = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
+            for nm, bit in bits.items():
+                if any(r[1] & bit for r in rows):
+                    out["reasons"].append(nm)
+        out["samples"] = len(rows)
+        return out
+
+
+def make_sampler(dev_index: int):
+    if os.environ.get("B2T_BENCH_NO_SAMPLER") == "1":
+        return None
+    try:
+        return NvmlSampler(dev_index)
+    except Exception:
+        return ClockSampler(dev_index, period_ms=1000)
+
+
 class ClockSampler:
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+    """One nvidia-smi process polling every 200 ms.  It is started (and its driver initialisation waited for) BEFORE
+    the warm-up steps: attaching to the driver takes 0.1-0.4 s on some boxes and stalls kernel launches while it does,
+    which used to land inside the first timed steps.  mark() is called when the timed region starts; only the samples
+    after it are reported."""
+    Q = ("timestamp,index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index: int):
+    def __init__(self, gpu_index: int, period_ms: int = 200):
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         self.p = None
+        self.t_mark = None
         try:
-            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", str(period_ms),
                                        "-i", str(gpu_index)], stdout=self.f, stderr=subprocess.DEVNULL)
         except Exception:
             self.p = None
+
+    def wait_ready(self, timeout: float = 10.0):
+        t0 = time.time()
+        while self.p is not None and time.time() - t0 < timeout:
+            if os.path.getsize(self.f.name) > 0 or self.p.poll() is not None:
+                return
+            time.sleep(0.02)
+
+    def mark(self):
+        self.t_mark = datetime.datetime.now()
 
     def stop(self):
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
@@ -191,9 +275,19 @@ class ClockSampler:
         with open(self.f.name) as fh:
             for line in fh:
                 parts = [x.strip() for x in line.split(",")]
-                if len(parts) >= 9:
+                if len(parts) >= 10:
                     rows.append(parts)
         os.unlink(self.f.name)
+        if self.t_mark is not None:
+            timed = []
+            for r in rows:
+                try:
+                    if datetime.datetime.strptime(r[0], "%Y/%m/%d %H:%M:%S.%f") >= self.t_mark:
+                        timed.append(r)
+                except ValueError:
+                    timed.append(r)
+            rows = timed or rows[-1:]
+        rows = [r[1:] for r in rows]
         if not rows:
             return out
         sm = sorted(float(r[1]) for r in rows if r[1].replace(".", "").isdigit())
@@ -243,11 +337,15 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = make_sampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.wait_ready()
     for _ in range(max(args.warmup, 3)):
         step(batch)
     # ---- device-resident timing ----
     barrier()
-    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.mark()
     l0 = ops.LAUNCHES
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()

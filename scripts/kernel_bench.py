@@ -8,6 +8,7 @@ def timeit(name, fn, iters=10, bytes_=None):
     for _ in range(3): fn()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda._sleep(4_000_000)   # ~2 ms of GPU backlog so that the host's launch overhead is not what is timed
     e0.record()
     for _ in range(iters): fn()
     e1.record(); torch.cuda.synchronize()

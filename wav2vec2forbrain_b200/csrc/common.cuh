@@ -61,6 +61,22 @@ __device__ __forceinline__ void split_bf16(float x, bf16& hi, bf16& lo) {
     lo = __float2bfloat16_rn(x - __bfloat162float(hi));
 }
 
+// four consecutive values as one 8-byte store per operand half
+__device__ __forceinline__ uint2 pack4_bf16(bf16 a, bf16 b, bf16 c, bf16 d) {
+    __nv_bfloat162 x = __halves2bfloat162(a, b), y = __halves2bfloat162(c, d);
+    uint2 w;
+    w.x = *reinterpret_cast<uint32_t*>(&x);
+    w.y = *reinterpret_cast<uint32_t*>(&y);
+    return w;
+}
+__device__ __forceinline__ void store_split4(const float (&o)[4], bf16* hi, bf16* lo, long off) {
+    bf16 h[4], l[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) split_bf16(o[e], h[e], l[e]);
+    *reinterpret_cast<uint2*>(hi + off) = pack4_bf16(h[0], h[1], h[2], h[3]);
+    if (lo) *reinterpret_cast<uint2*>(lo + off) = pack4_bf16(l[0], l[1], l[2], l[3]);
+}
+
 __device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
 __device__ __forceinline__ float gelu_erf_grad(float x) {
     const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));

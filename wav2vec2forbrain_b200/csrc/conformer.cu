@@ -320,6 +320,108 @@ __global__ void __launch_bounds__(128) bn_silu_bwd_stats_kernel(const float* __r
     atomicAdd(dgamma + c, sg);
 }
 
+// float4 forms of the two kernels above (D % 4 == 0): lane = 4 channels, warp = 8 rows in one batch of 16-byte loads,
+// CTA = 128 channels x 32 rows; 8-byte bf16 stores; the backward sums its 4 warps in smem before the atomics.
+__global__ void __launch_bounds__(128) bn_silu_fwd_vec_kernel(const float* __restrict__ x, const double* __restrict__ ssum,
+                                                              const double* __restrict__ ssq, const float* __restrict__ gamma,
+                                                              const float* __restrict__ beta, float eps, float momentum,
+                                                              float* __restrict__ running_mean, float* __restrict__ running_var,
+                                                              long long* __restrict__ nbt, float* __restrict__ mean_out,
+                                                              float* __restrict__ rstd_out, bf16* __restrict__ y_hi,
+                                                              bf16* __restrict__ y_lo, long M, int D, int training) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int c = blockIdx.x * 128 + lane * 4;
+    if (c >= D) return;
+    const long r0 = (long)blockIdx.y * BN_RPB + warp * 8;
+    float4 xv[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+        xv[j] = r0 + j < M ? *reinterpret_cast<const float4*>(x + (r0 + j) * D + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+    const bool writer = blockIdx.y == 0 && warp == 0;
+    float ga[4], be[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        float mean, rstd;
+        if (training) {
+            const double m = ssum[c + q] / (double)M;
+            double var = ssq[c + q] / (double)M - m * m;
+            var = var < 0.0 ? 0.0 : var;
+            mean = (float)m;
+            rstd = (float)(1.0 / sqrt(var + (double)eps));
+            if (writer) {
+                const double unb = M > 1 ? var * (double)M / (double)(M - 1) : var;
+                running_mean[c + q] = (1.0f - momentum) * running_mean[c + q] + momentum * mean;
+                running_var[c + q] = (1.0f - momentum) * running_var[c + q] + momentum * (float)unb;
+                if (c + q == 0 && nbt) *nbt += 1;
+            }
+        } else {
+            mean = running_mean[c + q];
+            rstd = 1.0f / sqrtf(running_var[c + q] + eps);
+        }
+        if (writer) {
+            mean_out[c + q] = mean;
+            rstd_out[c + q] = rstd;
+        }
+        ga[q] = gamma[c + q] * rstd;
+        be[q] = beta[c + q] - mean * gamma[c + q] * rstd;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        if (r0 + j >= M) break;
+        const float o[4] = {silu_acc(fmaf(xv[j].x, ga[0], be[0])), silu_acc(fmaf(xv[j].y, ga[1], be[1])),
+                            silu_acc(fmaf(xv[j].z, ga[2], be[2])), silu_acc(fmaf(xv[j].w, ga[3], be[3]))};
+        store_split4(o, y_hi, y_lo, (r0 + j) * D + c);
+    }
+}
+
+__global__ void __launch_bounds__(128) bn_silu_bwd_stats_vec_kernel(const float* __restrict__ ds, const float* __restrict__ x,
+                                                                    const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                                    const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                                    float* __restrict__ dgamma, float* __restrict__ dbeta, long M,
+                                                                    int D) {
+    __shared__ float red[2][4][128];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int c = blockIdx.x * 128 + lane * 4;
+    const bool c_ok = c < D;
+    const long r0 = (long)blockIdx.y * BN_RPB + warp * 8;
+    float4 xv[8], dv[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const bool ok = c_ok && r0 + j < M;
+        xv[j] = ok ? *reinterpret_cast<const float4*>(x + (r0 + j) * D + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+        dv[j] = ok ? *reinterpret_cast<const float4*>(ds + (r0 + j) * D + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    float mu[4], rs[4], ga[4], be[4], sb[4] = {0.f, 0.f, 0.f, 0.f}, sg[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        mu[q] = c_ok ? mean[c + q] : 0.f, rs[q] = c_ok ? rstd[c + q] : 0.f;
+        ga[q] = c_ok ? gamma[c + q] : 0.f, be[q] = c_ok ? beta[c + q] : 0.f;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {   // masked rows carry ds = 0
+        const float xs[4] = {xv[j].x, xv[j].y, xv[j].z, xv[j].w}, dd4[4] = {dv[j].x, dv[j].y, dv[j].z, dv[j].w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const float xh = (xs[q] - mu[q]) * rs[q];
+            const float dbn = dd4[q] * silu_acc_grad(fmaf(xh, ga[q], be[q]));
+            sb[q] += dbn;
+            sg[q] = fmaf(dbn, xh, sg[q]);
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        red[0][warp][lane * 4 + q] = sb[q];
+        red[1][warp][lane * 4 + q] = sg[q];
+    }
+    __syncthreads();
+    const int cc = blockIdx.x * 128 + threadIdx.x;
+    if (cc < D) {
+        const int t = threadIdx.x;
+        atomicAdd(dbeta + cc, (red[0][0][t] + red[0][1][t]) + (red[0][2][t] + red[0][3][t]));
+        atomicAdd(dgamma + cc, (red[1][0][t] + red[1][1][t]) + (red[1][2][t] + red[1][3][t]));
+    }
+}
+
 // backward, pass 2 (fused): BatchNorm+SiLU backward -> depthwise-conv backward (input and weight
 // gradients) -> GLU backward, written as the bf16 hi/lo operand dg [B*T, 2D] of the
 // pointwise_conv1 wgrad / dgrad GEMMs.  Same tiling as the forward kernel.
@@ -548,9 +650,15 @@ extern "C" int b2t_bn_silu_fwd(const float* x, const double* stats, const float*
                   "b2t_bn_silu_fwd: bad arguments");
     B2T_CHECK_ARG(!training || stats, "b2t_bn_silu_fwd: training mode needs the batch statistics buffer");
     dim3 grid((D + 127) / 128, (unsigned)((M + BN_RPB - 1) / BN_RPB));
-    bn_silu_fwd_kernel<<<grid, 128, 0, stream>>>(x, stats, stats ? stats + D : nullptr, gamma, beta, eps, momentum, running_mean,
-                                                 running_var, (long long*)num_batches_tracked, mean_out, rstd_out, (bf16*)y_hi,
-                                                 (bf16*)y_lo, M, D, training);
+    const bool vec = D % 4 == 0 && ((uintptr_t)x % 16 == 0) && ((uintptr_t)y_hi % 8 == 0) && (!y_lo || (uintptr_t)y_lo % 8 == 0);
+    if (vec)
+        bn_silu_fwd_vec_kernel<<<grid, 128, 0, stream>>>(x, stats, stats ? stats + D : nullptr, gamma, beta, eps, momentum,
+                                                         running_mean, running_var, (long long*)num_batches_tracked, mean_out,
+                                                         rstd_out, (bf16*)y_hi, (bf16*)y_lo, M, D, training);
+    else
+        bn_silu_fwd_kernel<<<grid, 128, 0, stream>>>(x, stats, stats ? stats + D : nullptr, gamma, beta, eps, momentum, running_mean,
+                                                     running_var, (long long*)num_batches_tracked, mean_out, rstd_out, (bf16*)y_hi,
+                                                     (bf16*)y_lo, M, D, training);
     B2T_CHECK_LAUNCH("b2t_bn_silu_fwd");
     return 0;
 }
@@ -560,7 +668,10 @@ extern "C" int b2t_bn_silu_bwd_stats(const float* ds, const float* x, const floa
     cudaStream_t stream = (cudaStream_t)stream_;
     B2T_CHECK_ARG(ds && x && mean && rstd && gamma && beta && dgamma && dbeta && M > 0 && D > 0, "b2t_bn_silu_bwd_stats: bad arguments");
     dim3 grid((D + 127) / 128, (unsigned)((M + BN_RPB - 1) / BN_RPB));
-    bn_silu_bwd_stats_kernel<<<grid, 128, 0, stream>>>(ds, x, mean, rstd, gamma, beta, dgamma, dbeta, M, D);
+    if (D % 4 == 0 && (uintptr_t)x % 16 == 0 && (uintptr_t)ds % 16 == 0)
+        bn_silu_bwd_stats_vec_kernel<<<grid, 128, 0, stream>>>(ds, x, mean, rstd, gamma, beta, dgamma, dbeta, M, D);
+    else
+        bn_silu_bwd_stats_kernel<<<grid, 128, 0, stream>>>(ds, x, mean, rstd, gamma, beta, dgamma, dbeta, M, D);
     B2T_CHECK_LAUNCH("b2t_bn_silu_bwd_stats");
     return 0;
 }

@@ -153,21 +153,6 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ d
 // parameter-gradient column sums of the backward are a separate column-parallel kernel, so the
 // row kernel keeps no per-column accumulators (the scalar kernel needs ~250 registers for them).
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint2 pack4_bf16(bf16 a, bf16 b, bf16 c, bf16 d) {
-    __nv_bfloat162 x = __halves2bfloat162(a, b), y = __halves2bfloat162(c, d);
-    uint2 w;
-    w.x = *reinterpret_cast<uint32_t*>(&x);
-    w.y = *reinterpret_cast<uint32_t*>(&y);
-    return w;
-}
-__device__ __forceinline__ void store_split4(const float (&o)[4], bf16* hi, bf16* lo, long off) {
-    bf16 h[4], l[4];
-#pragma unroll
-    for (int e = 0; e < 4; ++e) split_bf16(o[e], h[e], l[e]);
-    *reinterpret_cast<uint2*>(hi + off) = pack4_bf16(h[0], h[1], h[2], h[3]);
-    if (lo) *reinterpret_cast<uint2*>(lo + off) = pack4_bf16(l[0], l[1], l[2], l[3]);
-}
-
 template <int VPL>
 __global__ void __launch_bounds__(256) ln_fwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
                                                          const float* __restrict__ beta, float eps, float* __restrict__ y,
