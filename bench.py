@@ -7,13 +7,21 @@ One "step" = the reference's per-batch training step (src/train/train_loop.py:44
 optimizer.zero_grad -> model.forward(batch) -> loss.backward() -> [grad all-reduce] -> Adam.step,
 on one synthetic batch of the shape BASELINE.json names (256-ch features, T=500, 40-char targets).
 
-N=1 workload = BASELINE.json configs[1]: b2p2t_gru+w2v full fine-tuning, GRU 3x512 bidirectional +
-FC[256] + wav2vec2-base architecture (random init), batch 64.  N>1: same per-GPU batch (weak
-scaling), NCCL gradient all-reduce overlapped with backward.
+Default workload (no --workload flag) = the north-star configuration: b2p2t_gru+w2v_conformer, GRU 3x512
+bidirectional + FC[256] + wav2vec2-conformer-rope-large architecture (random init), batch 32 per GPU —
+BASELINE.json configs[3] at N=1 (the largest single-GPU config) and configs[4] at N>1 (weak scaling, NCCL
+gradient all-reduce overlapped with backward).  `--workload base|frozen` select configs[1] / configs[2]; their
+lines are kept under profiles/.
 
 `--impl reference` times the reference's own CPU implementation of the same step (the oracle port,
 oracle/b2t_oracle.py — the reference is pure PyTorch and /root/reference does not exist on the GPU
-box) on the host cores, on a bounded sample (8 trials per step) of the same workload.
+box) on the host cores, on a bounded sample (8 trials per step, printed as sample_trials_per_step) of the
+same workload.
+
+Besides the contract keys the N=1 line carries `inference` (eval + no_grad forward + greedy decode, trials/s)
+and `gpu_eager_baseline` (baseline/eager_gpu.py: the reference's step executed by PyTorch-eager library kernels
+on the same GPU, fp32 and bf16-autocast — the same-box bar of SURVEY.md §2.1; not the product, not the
+`--impl reference` arm); N>1 lines carry `comm` (exposed gradient all-reduce milliseconds per step).
 """
 from __future__ import annotations
 
@@ -32,9 +40,12 @@ REPO = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, REPO)
 
 T_FRAMES, S_TARGET, N_CH = 500, 40, 256
+PER_GPU_BATCH = {"base": 64, "frozen": 128, "conformer": 32}      # BASELINE.json configs[1], [2], [3]/[4]
+REFERENCE_SAMPLE_BATCH = 8                                        # trials per step of the CPU reference arm
 
 # algorithmic forward GFLOP per trial at T=500; training = 3x forward
 GF_TRAIN = {"base": 91.18, "frozen": 69.50, "conformer": 440.66}
+GF_INFER = {"base": 30.39, "frozen": 30.39, "conformer": 146.89}
 
 
 def read_peaks():
@@ -75,7 +86,7 @@ def oracle_step_fn(workload: str, B: int):
     groups = [{"params": brain, "lr": 1e-4}]
     if workload != "frozen":
         groups.append({"params": w2vp, "lr": 1e-5})
-    opt = torch.optim.Adam(groups, weight_decay=1e-4)
+    opt = torch.optim.Adam(groups, weight_decay=1e-4, eps=1e-8)   # base_args.py:113,121; experiment eps
     batch = make_host_batch(B)
 
     def step():
@@ -103,18 +114,23 @@ def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    B = 8
+    B = REFERENCE_SAMPLE_BATCH
     steps = max(1, min(args.steps, 20))
     warmup = max(1, min(args.warmup, 3))
     tps, ms = time_oracle(args.workload, steps, warmup, B)
     cores = os.cpu_count() or 1
+    # `config` names the workload of our arm (the contract: same config / metric / unit); what one step of THIS arm
+    # really ran is a bounded sample of that workload's per-GPU batch, stated in `sample_trials_per_step`,
+    # `ms_per_step` (of that sample) and cpu_baseline.sample (CPU trials/s is batch-independent to a few %)
+    cfg = workload_config(args.workload, args.gpus, PER_GPU_BATCH[args.workload])
     line = {
         "impl": "reference", "metric": "train trials/sec", "value": tps, "unit": "trials/s", "n_gpus": args.gpus,
         "steps": steps, "warmup": warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args.workload, args.gpus, 64 if args.workload != "conformer" else 32),
+        "config": cfg, "sample_trials_per_step": B,
         "cpu_baseline": {"value": tps, "unit": "trials/s", "cores": cores, "kind": "port",
-                         "sample": f"{steps} steps of {B} trials (T=500) of the same workload, torch CPU fp32, all host threads"},
+                         "sample": f"{steps} steps of {B} trials (T=500) of the same workload after {warmup} warm-up, "
+                                   "torch CPU fp32, all host threads"},
         "e2e": {"value": tps, "unit": "trials/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
@@ -124,7 +140,8 @@ def workload_config(workload: str, n_gpus: int, per_gpu_batch: int):
     names = {
         "base": "b2p2t_gru+w2v full fine-tuning, wav2vec2-base arch (BASELINE.json configs[1])",
         "frozen": "b2p2t_gru+w2v frozen_w2v (BASELINE.json configs[2])",
-        "conformer": "b2p2t_gru+w2v_conformer, wav2vec2-conformer-rope-large arch (BASELINE.json configs[3]/[4])",
+        "conformer": "b2p2t_gru+w2v_conformer, wav2vec2-conformer-rope-large arch, batch 32/GPU (BASELINE.json "
+                     + ("configs[3])" if n_gpus == 1 else "configs[4], data parallel)"),
     }
     return {"workload": names[workload], "per_gpu_batch": per_gpu_batch, "global_batch": per_gpu_batch * n_gpus,
             "T": T_FRAMES, "channels": N_CH, "target_len": S_TARGET, "gru": "3x512 bidirectional", "fc": [256],
@@ -134,7 +151,7 @@ def workload_config(workload: str, n_gpus: int, per_gpu_batch: int):
 # ---------------------------------------------------------------------------------------------
 # our arm
 # ---------------------------------------------------------------------------------------------
-def build_model(workload: str, precision: str):
+def build_model(workload: str, precision: str, optimizer: str = "fused"):
     from wav2vec2forbrain_b200 import models
     a = models.BrainEncoderArgs(encoder_gru_hidden_size=512, encoder_num_gru_layers=3, encoder_fc_hidden_sizes=(256,),
                                 gaussian_smooth_width=1.5, encoder_dropout=0.45)
@@ -153,7 +170,15 @@ def build_model(workload: str, precision: str):
     groups = [{"params": brain_p, "lr": 1e-4}]
     if workload != "frozen":
         groups.append({"params": list(model.w2v_encoder.parameters()), "lr": 1e-5})   # b2t_gru_w2v_experiment.py:111-145
-    opt = torch.optim.Adam(groups, weight_decay=1e-4, fused=True)
+    else:
+        # unfreeze_strategy == "brain_encoder": nobody reads the w2v weight gradients -> dgrad only
+        model.runtime.skip_w2v_wgrad = True
+    # weight_decay / eps as create_optimizer passes them (b2t_gru_w2v_experiment.py:138-145, base_args.py:113,121)
+    if optimizer == "torch":
+        opt = torch.optim.Adam(groups, weight_decay=1e-4, eps=1e-8, fused=True)
+    else:
+        from wav2vec2forbrain_b200 import optim as boptim
+        opt = boptim.FusedAdam(groups, weight_decay=1e-4, eps=1e-8)
     return model, opt
 
 
@@ -315,8 +340,8 @@ def run_ours(args):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     workload, precision = args.workload, args.precision
-    B = args.batch or (32 if workload == "conformer" else (128 if workload == "frozen" else 64))
-    model, opt = build_model(workload, precision)
+    B = args.batch or PER_GPU_BATCH[workload]
+    model, opt = build_model(workload, precision, args.optimizer)
     dp = None
     if multi:
         dp = bdist.DataParallel(model)
@@ -380,8 +405,49 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms, e2e_ms = t.tolist()
     peaks = read_peaks()
+    # ---- exposed gradient all-reduce per step (N > 1): the same timed loop with the collective switched off ----
+    comm = None
+    if multi:
+        dp.buckets.enabled = False
+        for _ in range(2):
+            step(batch)
+        barrier()
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c0.record()
+        for _ in range(args.steps):
+            step(batch)
+        c1.record()
+        barrier()
+        dp.buckets.enabled = True
+        tt = torch.tensor([c0.elapsed_time(c1)], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        nocomm_ms = tt.item() / args.steps
+        for p in model.parameters():        # the un-reduced steps let the replicas drift: re-broadcast rank 0's weights
+            dist.broadcast(p.data, src=0)
+        comm = {"exposed_ms_per_step": ms / args.steps - nocomm_ms, "ms_per_step_without_allreduce": nocomm_ms,
+                "allreduce_bytes_per_step": dp.buckets.bytes_per_step, "buckets": len(dp.buckets.buckets),
+                "how": "same timed loop with the gradient all-reduce disabled, max over ranks"}
     # every rank runs the roofline steps (they contain the gradient all-reduce); rank 0 reports
     roof = gemm_roofline(model, opt, batch, step, peaks, workload) if not args.no_roofline else None
+    # ---- inference: eval() + no_grad forward + greedy CTC decode on the device (train_loop.py:89-109, evaluator.py:108-120)
+    infer = None
+    if not args.no_inference and rank == 0:
+        model.eval()
+        with torch.no_grad():
+            for _ in range(3):
+                ops.greedy_decode(model.forward(batch).logits)
+            i0, i1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            i0.record()
+            for _ in range(args.steps):
+                ops.greedy_decode(model.forward(batch).logits)
+            i1.record()
+            torch.cuda.synchronize()
+        model.train()
+        ims = i0.elapsed_time(i1) / args.steps
+        infer = {"value": B / (ims / 1e3), "unit": "trials/s", "ms_per_batch": ims, "per_gpu_batch": B, "n_gpus": 1,
+                 "what": "eval() + no_grad forward + greedy CTC decode kernel, device-resident batch, CUDA events",
+                 "roofline_frac": B / (ims / 1e3) * GF_INFER[workload] / (peaks["bf16_tflops_sustained"] * 1e3)}
     if multi:
         dist.barrier()
         torch.cuda.synchronize()
@@ -401,10 +467,34 @@ def run_ours(args):
     }
     if roof is not None:
         line["roofline"] = roof
+    if infer is not None:
+        line["inference"] = infer
+    if comm is not None:
+        line["comm"] = comm
+    line["optimizer"] = ("wav2vec2forbrain_b200.optim.FusedAdam (multi-tensor CUDA kernel)" if args.optimizer == "fused"
+                         else "torch.optim.Adam(fused=True)")
+    if world == 1 and not args.no_eager:
+        # the same-box bar: the reference's step by PyTorch-eager library kernels on this GPU
+        del model, opt
+        torch.cuda.empty_cache()
+        from baseline import eager_gpu
+        dbatch = {k: v.to(dev) for k, v in hb.items()}
+        eager = {"what": "reference training step executed by PyTorch-eager library kernels (cuDNN GRU, cuBLAS, ATen, "
+                         "transformers encoder classes; baseline/eager_gpu.py) on the same GPU, same workload and batch; "
+                         "NOT the product and NOT the --impl reference arm", "per_gpu_batch": B}
+        for key, ac in (("fp32", False), ("bf16_autocast", True)):
+            try:
+                eager[key] = eager_gpu.time_eager(workload, dbatch, dev, ac)
+                eager[key]["ours_over_eager"] = tps / eager[key]["value"]
+            except Exception as ex:       # never lose the product's line to the baseline
+                eager[key] = {"error": f"{type(ex).__name__}: {ex}"[:300]}
+        eager["fp32"]["note"] = "torch defaults, as the reference runs: fp32 matmul (TF32 off), cuDNN may use TF32"
+        line["gpu_eager_baseline"] = eager
     if world == 1 and not args.no_cpu_baseline:
-        v, _ = time_oracle(workload, steps=2, warmup=1, B=8)
+        v, _ = time_oracle(workload, steps=3, warmup=1, B=REFERENCE_SAMPLE_BATCH)
         line["cpu_baseline"] = {"value": v, "unit": "trials/s", "cores": os.cpu_count() or 1, "kind": "port",
-                                "sample": "2 steps of 8 trials (T=500) of the same workload, torch CPU fp32, all host threads"}
+                                "sample": f"3 steps of {REFERENCE_SAMPLE_BATCH} trials (T=500) of the same workload after 1 "
+                                          "warm-up, torch CPU fp32, all host threads"}
     print(json.dumps(line))
 
 
@@ -474,9 +564,13 @@ def main():
     ap.add_argument("--batch", type=int, default=0)
     ap.add_argument("--no-roofline", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-eager", action="store_true", help="skip the PyTorch-eager same-box baseline")
+    ap.add_argument("--no-inference", action="store_true")
+    ap.add_argument("--optimizer", default="fused", choices=["fused", "torch"],
+                    help="fused = this repo's multi-tensor Adam kernel; torch = torch.optim.Adam(fused=True)")
     args = ap.parse_args()
     if args.workload is None:
-        args.workload = "base"
+        args.workload = "conformer"     # north-star config: configs[3] at N=1, configs[4] at N>1
     if args.impl == "reference":
         run_reference_arm(args)
     else:

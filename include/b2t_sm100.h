@@ -249,6 +249,72 @@ int b2t_glu_dwconv_bwd(const float* ds, const float* x, const float* g, const fl
                        const float* dbeta, void* dg_hi, void* dg_lo, float* dw, int B, int T, int D, int K,
                        int training, b2t_stream stream);
 
+/* ---------------------------------------------------------------------------------------
+ * multi-tensor Adam + global-norm gradient clipping.
+ * Replaces torch.optim.Adam(params, lr, weight_decay, eps) — L2 weight-decay form, two parameter
+ * groups (src/experiments/experiment.py:25-28, src/experiments/b2t_gru_w2v_experiment.py:109-145) —
+ * and torch.nn.utils.clip_grad_norm_ (src/train/train_loop.py:72-78).
+ * `tensors` (device): one entry per parameter that has a gradient; `chunks` (device): pairs
+ * (tensor index, chunk index), one CTA per B2T_MT_CHUNK elements.  Every call is one launch over
+ * all tensors; nothing synchronises with the host (the norm and the clip coefficient stay on the
+ * device).
+ * ------------------------------------------------------------------------------------- */
+#define B2T_MT_CHUNK 65536
+#define B2T_ADAM_MAX_GROUPS 32
+typedef struct {
+    float* p; float* g; float* m; float* v;   /* parameter, gradient, exp_avg, exp_avg_sq (fp32) */
+    int64_t n;                                /* elements */
+    int32_t group;                            /* index into the groups array */
+    int32_t pad_;
+} b2t_mt_tensor;
+typedef struct {
+    float lr, beta1, beta2, eps, weight_decay;
+    float bias_c1;        /* 1 - beta1^step */
+    float bias_c2_sqrt;   /* sqrt(1 - beta2^step) */
+    int32_t pad_;
+} b2t_adam_group;
+/* p, m, v updated in place exactly as torch.optim.Adam's single-tensor path orders the operations;
+ * grad_scale (device scalar, may be NULL) multiplies every gradient first */
+int b2t_adam_multi(const b2t_mt_tensor* tensors, const int32_t* chunks, int n_chunks, const b2t_adam_group* groups,
+                   int n_groups, const float* grad_scale, b2t_stream stream);
+/* *sumsq (device double, caller zeroes it) += sum of squares of every gradient in the table */
+int b2t_grad_sumsq_multi(const b2t_mt_tensor* tensors, const int32_t* chunks, int n_chunks, double* sumsq,
+                         b2t_stream stream);
+/* gradients *= min(1, max_norm / (sqrt(*sumsq) + 1e-6)); *total_norm_out = sqrt(*sumsq) */
+int b2t_grad_clip_multi(const b2t_mt_tensor* tensors, const int32_t* chunks, int n_chunks, const double* sumsq,
+                        float max_norm, float* total_norm_out, b2t_stream stream);
+
+/* ---------------------------------------------------------------------------------------
+ * WER / CER counts of the greedy CTC decode on the device, replacing the
+ * per-batch host path of src/train/evaluator.py:108-120 (argmax -> .cpu() -> tokenizer.batch_decode)
+ * and :163-229 (torcheval WordErrorRate, edit_distance.SequenceMatcher character distance).
+ * pred_ids [B, ld_pred]: per-frame argmax ids (b2t_greedy_decode's `argmax`); targets [B,S] padded
+ * with pad_id.  vocab_chars [V][8]: byte 0 = length (<= 7), bytes 1.. = the token's characters;
+ * delim_id is decoded as ' '.  Decode rules are the tokenizer's: group repeats (predictions only),
+ * drop pad, join, strip, then " ' " -> "'" when cleanup != 0; eos_id >= 0 additionally cuts the
+ * prediction after the first eos string.  counts[4] (int64, +=): character distance, target
+ * characters, word distance, target words; per_trial [B,4] (optional) the same per trial.
+ * ------------------------------------------------------------------------------------- */
+int b2t_ctc_error_counts(const int32_t* pred_ids, int T, int64_t ld_pred, const int64_t* targets, int S,
+                         const uint8_t* vocab_chars, int V, int pad_id, int delim_id, int eos_id, int cleanup,
+                         int64_t* counts, int32_t* per_trial, int B, b2t_stream stream);
+
+/* ---------------------------------------------------------------------------------------
+ * input pipeline over device-resident trials.  frames [sum_T, C] fp32 holds
+ * every trial back to back, trial i = rows trial_offsets[i] .. trial_offsets[i+1].
+ * b2t_block_zscore: block-wise feature normalisation (src/datasets/preprocessing.py:60-72,100-113):
+ *   y = (x - mean_block) / (std_block + eps) per channel, statistics over all frames of the trials
+ *   with the same trial_block id (< 0: trial left unnormalised); ws = 3*n_blocks*C doubles.
+ * b2t_collate: the collate function of src/datasets/brain2text.py:178-211 for the trials idx[0..B):
+ *   out [B, t_max, C] zero padded, targets [B, s_out] from labels [N, s_all] (pad 0), input_lens,
+ *   target_lens, day_idxs (all int64).
+ * ------------------------------------------------------------------------------------- */
+int b2t_block_zscore(const float* x, float* y, const int64_t* trial_offsets, const int32_t* trial_block, int n_trials,
+                     int n_blocks, int C, double* ws, double eps, b2t_stream stream);
+int b2t_collate(const float* frames, const int64_t* trial_offsets, const int32_t* idx, int B, int C, int t_max, float* out,
+                const int64_t* labels, int s_all, const int64_t* label_lens, const int64_t* days, int64_t* out_targets,
+                int s_out, int64_t* out_input_lens, int64_t* out_target_lens, int64_t* out_days, b2t_stream stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -128,6 +128,11 @@ def forward(eng, P, feats: Tensor, B: int, T: int, training: bool, seed: int, sk
     return h, S
 
 
+def _v3(w):
+    """[out, in] weight gradient seen as the Conv1d weight [out, in, 1] (None in frozen-w2v mode)."""
+    return None if w is None else w.view(w.shape[0], w.shape[1], 1)
+
+
 def _zeros(n: int, dev) -> Tensor:
     return _e.ops.zeros(n, device=dev)
 
@@ -190,7 +195,7 @@ def backward(eng, P, S: dict, dh: Tensor, G: Dict[str, Tensor]) -> Tensor:
         cm = L + "conv_module."
         cs = st["conv"]
         w2 = _w2d(eng, P, cm + "pointwise_conv2.weight")
-        G[cm + "pointwise_conv2.weight"] = eng._wgrad(g_hi, g_lo, cs["s_hi"], cs["s_lo"], D, D, M).view(D, D, 1)
+        G[cm + "pointwise_conv2.weight"] = _v3(eng._wgrad(g_hi, g_lo, cs["s_hi"], cs["s_lo"], D, D, M))
         dsil, _, _ = eng._dgrad(g_hi, g_lo, w2, M, D, D)
         gam, bet = P[cm + "batch_norm.weight"], P[cm + "batch_norm.bias"]
         bn_mean, bn_rstd = cs["bn"]
@@ -199,7 +204,7 @@ def backward(eng, P, S: dict, dh: Tensor, G: Dict[str, Tensor]) -> Tensor:
         dg_hi, dg_lo, ddw = ops.glu_dwconv_bwd(dsil, cs["dwo"], cs["g"], P[cm + "depthwise_conv.weight"], bn_mean, bn_rstd, gam,
                                                bet, dgam, dbet, B, T, training, three=three)
         G[cm + "depthwise_conv.weight"] = ddw
-        G[cm + "pointwise_conv1.weight"] = eng._wgrad(dg_hi, dg_lo, cs["n_hi"], cs["n_lo"], 2 * D, D, M).view(2 * D, D, 1)
+        G[cm + "pointwise_conv1.weight"] = _v3(eng._wgrad(dg_hi, dg_lo, cs["n_hi"], cs["n_lo"], 2 * D, D, M))
         dn, _, _ = eng._dgrad(dg_hi, dg_lo, _w2d(eng, P, cm + "pointwise_conv1.weight"), M, 2 * D, D)
         dbo = _zeros(D, dev)
         d2, g_hi, g_lo = _ln_bwd(eng, P, G, cm + "layer_norm", dn, cs["x"], cs["ln"], dres=d3, dcol=dbo, br_drop_p=p_att,
@@ -219,7 +224,8 @@ def backward(eng, P, S: dict, dh: Tensor, G: Dict[str, Tensor]) -> Tensor:
         qk_hi, qk_lo = dq_hi[:, :2 * D], (None if dq_lo is None else dq_lo[:, :2 * D])
         v_hi, v_lo = dq_hi[:, 2 * D:], (None if dq_lo is None else dq_lo[:, 2 * D:])
         dwqk = eng._wgrad(qk_hi, qk_lo, at["r_hi"], at["r_lo"], 2 * D, D, M)
-        G[sa + "linear_q.weight"], G[sa + "linear_k.weight"] = dwqk[:D], dwqk[D:]
+        if dwqk is not None:
+            G[sa + "linear_q.weight"], G[sa + "linear_k.weight"] = dwqk[:D], dwqk[D:]
         G[sa + "linear_v.weight"] = eng._wgrad(v_hi, v_lo, at["y_hi"], at["y_lo"], D, D, M)
         wqk = eng._w_cat(P, sa + "qk", [sa + "linear_q.weight", sa + "linear_k.weight"])
         du_rot, _, _ = eng._dgrad(qk_hi, qk_lo, wqk, M, 2 * D, D)

@@ -152,8 +152,15 @@ class Engine:
                  out_hi=hi, out_lo=lo, bias=bias, **kw)
         return out, pre, hi, lo
 
-    def _wgrad(self, dy_hi, dy_lo, x_hi, x_lo, N, K, M, out: Optional[Tensor] = None, alpha: float = 1.0) -> Tensor:
+    # frozen-w2v mode (unfreeze_strategy == "brain_encoder", b2t_gru_w2v_experiment.py:129-133): the optimizer never
+    # reads the w2v weight gradients, so the encoder backward is data-gradient only; set by
+    # models._EncoderFn.backward around the encoder's schedule, never during the brain encoder's
+    _skip_wgrad = False
+
+    def _wgrad(self, dy_hi, dy_lo, x_hi, x_lo, N, K, M, out: Optional[Tensor] = None, alpha: float = 1.0) -> Optional[Tensor]:
         """dW[N,K] = dY[M,N]^T . X[M,K]  (both operands row-major, contracted over rows)."""
+        if self._skip_wgrad:
+            return None
         kb = (M + 63) // 64
         sk = _split_k_for(N, K, kb)
         if out is None:
@@ -410,6 +417,8 @@ class Engine:
         ops.gemm(ad, ops.kmajor(wd_hi.view(G, Cg, K * CP), None if wd_lo is None else wd_lo.view(G, Cg, K * CP)),
                  m_per_batch=T, batches=G * B, n=Cg, k=K * CP, out_f32=dx, ldc=D, c_batch_stride=Cg, a_batched=True,
                  b_batch_idx=gi, c_batch_idx=ci, residual=dsum, block_n=64)
+        if self._skip_wgrad:
+            return dx
         for g in range(G):
             wsl = slice(g * Cg, (g + 1) * Cg)
             # A: [B, T, Cg] slice of dpre (row stride D); TMA needs 16-byte aligned base and strides
@@ -614,7 +623,7 @@ class Engine:
             ops.colsum(dqkv, dbq)
             dwq = self._wgrad(dq_hi, dq_lo, st["in_hi"], st["in_lo"], 3 * D, D, M)
             for j, nm in enumerate(("q_proj", "k_proj", "v_proj")):
-                G[Lq + f"attention.{nm}.weight"] = dwq[j * D:(j + 1) * D]
+                G[Lq + f"attention.{nm}.weight"] = None if dwq is None else dwq[j * D:(j + 1) * D]
                 G[Lq + f"attention.{nm}.bias"] = dbq[j * D:(j + 1) * D]
             wqkv = self._w_cat(P, Lq + "qkv", [Lq + "attention.q_proj.weight", Lq + "attention.k_proj.weight",
                                                Lq + "attention.v_proj.weight"])

@@ -75,32 +75,55 @@ class _LazyMetrics(dict):
     """`metrics` dict of ModelOutput whose float values are materialised (device->host sync) only
     when somebody reads them.  The reference calls ctc_loss.item() inside forward
     (w2v_custom_feat_extractor.py:94), a stream sync per step that readers who never look at the
-    metrics should not pay for; readers (evaluator.track_batch) see plain floats."""
+    metrics should not pay for; readers (evaluator.track_batch, history.MetricEntry) see plain floats.
+
+    Every read path materialises: __iter__ is overridden on purpose, which also takes CPython off its
+    dict-subclass fast paths (dict(m), {**m}, m.copy(), json.dump), so none of them can see a tensor."""
 
     def set_lazy(self, key, tensor):
         dict.__setitem__(self, key, tensor)
 
-    def _mat(self, key):
-        v = dict.__getitem__(self, key)
-        if isinstance(v, Tensor):
-            v = v.item()
-            dict.__setitem__(self, key, v)
-        return v
+    def _mat_all(self):
+        for k in list(dict.keys(self)):
+            v = dict.__getitem__(self, k)
+            if isinstance(v, Tensor):
+                dict.__setitem__(self, k, v.item())
 
     def __getitem__(self, key):
-        return self._mat(key)
+        self._mat_all()
+        return dict.__getitem__(self, key)
 
     def get(self, key, default=None):
-        return self._mat(key) if key in self else default
+        self._mat_all()
+        return dict.get(self, key, default)
+
+    def __iter__(self):
+        self._mat_all()
+        return dict.__iter__(self)
+
+    def keys(self):
+        self._mat_all()
+        return dict.keys(self)
 
     def items(self):
-        return [(k, self._mat(k)) for k in list(self.keys())]
+        self._mat_all()
+        return dict.items(self)
 
     def values(self):
-        return [self._mat(k) for k in list(self.keys())]
+        self._mat_all()
+        return dict.values(self)
+
+    def copy(self):
+        self._mat_all()
+        return dict(dict.items(self))
+
+    def __reduce__(self):
+        self._mat_all()
+        return (dict, (dict(dict.items(self)),))
 
     def __repr__(self):
-        return repr(dict(self.items()))
+        self._mat_all()
+        return dict.__repr__(self)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -115,6 +138,9 @@ class _Runtime:
         # LayerDrop decisions come from a host generator seeded identically on every rank
         self.layerdrop_gen = torch.Generator().manual_seed(seed)
         self.augment = (0.0, 0.0)   # (whiteNoiseSD, constantOffsetSD); (0, 0) = the reference's observable behaviour
+        # frozen-w2v training (unfreeze_strategy == "brain_encoder"): skip the w2v weight gradients nobody reads
+        # (set by compat's _create_model swap and by bench.py --workload frozen)
+        self.skip_w2v_wgrad = False
 
     def next_seed(self) -> int:
         self.step += 1
@@ -174,15 +200,22 @@ class _EncoderFn(torch.autograd.Function):
     def backward(ctx, dlogits, dhidden):
         eng = ctx.rt.engine
         G: Dict[str, Tensor] = {}
+        skip = ctx.rt.skip_w2v_wgrad
         with _ops.zero_arena(("w2v", id(ctx.rt)), dlogits.device):
-            dh = eng.head_backward(ctx.P, ctx.Sh, dlogits.contiguous(), G)
-            if dhidden is not None:
-                dh = dh + eng_dropout_bwd(eng, ctx.Sh, dhidden)
-            if eng.w2v.kind == "base":
-                dfeats = eng.w2v_base_backward(ctx.P, ctx.Se, dh, G)
-            else:
-                from . import conformer
-                dfeats = conformer.backward(eng, ctx.P, ctx.Se, dh, G)
+            eng._skip_wgrad = skip
+            try:
+                dh = eng.head_backward(ctx.P, ctx.Sh, dlogits.contiguous(), G)
+                if dhidden is not None:
+                    dh = dh + eng_dropout_bwd(eng, ctx.Sh, dhidden)
+                if eng.w2v.kind == "base":
+                    dfeats = eng.w2v_base_backward(ctx.P, ctx.Se, dh, G)
+                else:
+                    from . import conformer
+                    dfeats = conformer.backward(eng, ctx.P, ctx.Se, dh, G)
+            finally:
+                eng._skip_wgrad = False
+            if skip:
+                G = {}      # data gradient only: no w2v parameter receives a .grad
             eng.sync_grads(G)
         B, T = ctx.Sh["B"], ctx.Sh["T"]
         return (None, None, None, None, None, dfeats.view(B, T, -1)) + tuple(G.get(n) for n in ctx.names)
