@@ -268,9 +268,13 @@ typedef struct {
     int32_t pad_;
 } b2t_mt_tensor;
 typedef struct {
-    float lr, beta1, beta2, eps, weight_decay;
-    float bias_c1;        /* 1 - beta1^step */
-    float bias_c2_sqrt;   /* sqrt(1 - beta2^step) */
+    /* every derived scalar is computed by the host in double and rounded once, as torch does with its Python
+     * floats (1 - 0.999f in fp32 would be 4.7e-5 off 0.001) */
+    float beta2, eps, weight_decay;
+    float one_minus_beta1;   /* 1 - beta1 */
+    float one_minus_beta2;   /* 1 - beta2 */
+    float step_size;         /* lr / (1 - beta1^step) */
+    float bias_c2_sqrt;      /* sqrt(1 - beta2^step) */
     int32_t pad_;
 } b2t_adam_group;
 /* p, m, v updated in place exactly as torch.optim.Adam's single-tensor path orders the operations;

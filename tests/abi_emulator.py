@@ -88,9 +88,13 @@ def permute_unfold_cols(w, C, KL, three=True):
     return _split_t(wp, three)
 
 
-def unpermute_unfold_cols(g, C, KL):
+def unpermute_unfold_cols(g, C, KL, out=None):
     rows = g.shape[0]
-    return g.reshape(rows, KL, C).permute(0, 2, 1).reshape(rows, C * KL).contiguous()
+    r = g.reshape(rows, KL, C).permute(0, 2, 1).reshape(rows, C * KL).contiguous()
+    if out is not None:
+        out.copy_(r)
+        return out
+    return r
 
 
 def _act(x, mode):
@@ -105,9 +109,10 @@ def _act(x, mode):
 
 
 def _dact(a, mode):
-    a = a.detach().clone().requires_grad_(True)
-    _act(a, mode).sum().backward()
-    return a.grad
+    with torch.enable_grad():      # the engine's backward runs inside autograd.Function.backward (grad mode off)
+        a = a.detach().clone().requires_grad_(True)
+        g, = torch.autograd.grad(_act(a, mode).sum(), a)
+    return g
 
 
 def gemm(a, b, *, m_per_batch, n, k, batches=1, out_f32=None, out_pre=None, out_hi=None, out_lo=None, ldc=None,
@@ -352,14 +357,15 @@ def gru_bwd(dout, fw, w_hh, h0, dh0, B, T, H, ndir, three=True, drop_p=0.0, seed
 
 
 def ctc_fwd_bwd(logits, targets, input_lens, target_lens, want_grad=True):
-    x = logits.detach().double().requires_grad_(True)
-    lp = F.log_softmax(x, -1).transpose(0, 1)
-    loss = F.ctc_loss(lp, targets, input_lens.long(), target_lens, blank=0, reduction="mean", zero_infinity=True)
-    nll = F.ctc_loss(lp, targets, input_lens.long(), target_lens, blank=0, reduction="none", zero_infinity=True)
-    grad = None
-    if want_grad:
-        loss.backward()
-        grad = x.grad.float()
+    with torch.enable_grad():     # also called from inside autograd.Function.forward (models._CTCFn)
+        x = logits.detach().double().requires_grad_(True)
+        lp = F.log_softmax(x, -1).transpose(0, 1)
+        loss = F.ctc_loss(lp, targets, input_lens.long(), target_lens, blank=0, reduction="mean", zero_infinity=True)
+        nll = F.ctc_loss(lp, targets, input_lens.long(), target_lens, blank=0, reduction="none", zero_infinity=True)
+        grad = None
+        if want_grad:
+            grad, = torch.autograd.grad(loss, x)
+            grad = grad.float()
     return loss.detach().float(), nll.detach().float(), grad
 
 
@@ -408,13 +414,17 @@ def posconv_unpack_dx(dxg, dx, B, T, G, pad_left, Tp):
         d4[:, :, g] += dxg[g, :, pad_left:pad_left + T, :Cg]
 
 
-def posconv_weight_bwd(dwg, g, v, norm):
+def posconv_weight_bwd(dwg, g, v, norm, dg_out=None, dv_out=None):
     D, Cg, K = v.shape
     dwn = dwg.double().reshape(D, K, POSCONV_CP)[:, :, :Cg].permute(0, 2, 1)   # [D, Cg, K]
     vd, nd, gd = v.double(), norm.double().view(1, 1, K), g.double().reshape(1, 1, K)
     s = (dwn * vd).sum((0, 1), keepdim=True)
     dg = (s / nd).reshape(g.shape).float()
     dv = (dwn * gd / nd - vd * gd * s / nd ** 3).float()
+    if dg_out is not None:
+        dg = dg_out.copy_(dg)
+    if dv_out is not None:
+        dv = dv_out.copy_(dv)
     return dg, dv
 
 
@@ -513,15 +523,20 @@ def bn_silu_fwd(x, stats, gamma, beta, eps, momentum, running_mean, running_var,
     return hi, lo, mean.float(), rstd.float()
 
 
-def bn_silu_bwd_stats(ds, x, mean, rstd, gamma, beta):
+def bn_silu_bwd_stats(ds, x, mean, rstd, gamma, beta, dgamma_out=None, dbeta_out=None):
     global LAUNCHES
     LAUNCHES += 1
     xh = (x.double() - mean.double()) * rstd.double()
     dbn = ds.double() * _dact(xh * gamma.double() + beta.double(), "silu")
-    return (dbn * xh).sum(0).float(), dbn.sum(0).float()
+    dg, db = (dbn * xh).sum(0).float(), dbn.sum(0).float()
+    if dgamma_out is not None:
+        dg = dgamma_out.add_(dg)
+    if dbeta_out is not None:
+        db = dbeta_out.add_(db)
+    return dg, db
 
 
-def glu_dwconv_bwd(ds, x, g, w, mean, rstd, gamma, beta, dgamma, dbeta, B, T, training, three=True):
+def glu_dwconv_bwd(ds, x, g, w, mean, rstd, gamma, beta, dgamma, dbeta, B, T, training, three=True, dw_out=None):
     global LAUNCHES
     LAUNCHES += 1
     M, D = x.shape
@@ -532,10 +547,14 @@ def glu_dwconv_bwd(ds, x, g, w, mean, rstd, gamma, beta, dgamma, dbeta, B, T, tr
         dx = gamma.double() * rstd.double() * (dbn - dbeta.double() / M - xh * dgamma.double() / M)
     else:
         dx = gamma.double() * rstd.double() * dbn
-    gl = g.detach().double().requires_grad_(True)
-    wl = w.detach().double().view(D, 1, K).requires_grad_(True)
-    s = (gl[:, :D] * torch.sigmoid(gl[:, D:])).view(B, T, D).transpose(1, 2)
-    out = F.conv1d(s, wl, None, padding=(K - 1) // 2, groups=D).transpose(1, 2).reshape(M, D)
-    out.backward(dx)
-    hi, lo = _split_t(gl.grad.float(), three)
-    return hi, lo, wl.grad.float().view_as(w)
+    with torch.enable_grad():
+        gl = g.detach().double().requires_grad_(True)
+        wl = w.detach().double().view(D, 1, K).requires_grad_(True)
+        s = (gl[:, :D] * torch.sigmoid(gl[:, D:])).view(B, T, D).transpose(1, 2)
+        out = F.conv1d(s, wl, None, padding=(K - 1) // 2, groups=D).transpose(1, 2).reshape(M, D)
+        ggl, gwl = torch.autograd.grad(out, (gl, wl), dx.detach())
+    hi, lo = _split_t(ggl.float(), three)
+    dw = gwl.float().view_as(w)
+    if dw_out is not None:
+        dw = dw_out.add_(dw)
+    return hi, lo, dw

@@ -49,9 +49,11 @@ def _worker(rank, world, port, outdir):
     for step, use in enumerate([True, False]):
         opt.zero_grad()
         loss = m(data[step][bdist.shard_indices(8, rank, world)], use)
-        loss.backward()
-        dp.finish()
+        loss.backward()                    # the end-of-backward callback finishes the reduction (no finish() call:
+        #                                    clip_grad_norm_ of the unmodified Trainer, train_loop.py:72-75, sees averages)
+        tn = torch.nn.utils.clip_grad_norm_(m.parameters(), 1e9)
         dp.finish()                        # idempotent within a step
+        assert abs(tn.item() - torch.nn.utils.clip_grad_norm_(m.parameters(), 1e9).item()) < 1e-6
         res.append({k: (None if p.grad is None else p.grad.clone()) for k, p in m.named_parameters()})
         opt.step()
     torch.save((rank, res, {k: v.detach().clone() for k, v in m.named_parameters()}), os.path.join(outdir, f"r{rank}.pt"))
@@ -89,68 +91,86 @@ def test_bucketed_allreduce_matches_global_batch_gradient(tmp_path):
         assert torch.allclose(outs[0][2][k], p.detach(), atol=1e-6) and torch.allclose(outs[1][2][k], p.detach(), atol=1e-6)
 
 
-class _NodeFn(torch.autograd.Function):
-    """One autograd node that returns the gradients of several parameters at once and hands them to the sink while
-    its backward is still running (the shape of the engine's encoder node)."""
-
-    @staticmethod
-    def forward(ctx, buckets, x, wa, wb):
-        ctx.buckets = buckets
-        ctx.save_for_backward(x, wa, wb)
-        return ((x @ wa.t()) @ wb.t()).pow(2).mean()
-
-    @staticmethod
-    def backward(ctx, dl):
-        x, wa, wb = ctx.saved_tensors
-        with torch.enable_grad():
-            wa_, wb_ = wa.detach().requires_grad_(), wb.detach().requires_grad_()
-            l = ((x @ wa_.t()) @ wb_.t()).pow(2).mean()
-            gb, = torch.autograd.grad(l, wb_, retain_graph=True)
-            gb = gb * dl
-            ctx.buckets.sink([("wb", gb)])             # "layer above" finished first
-            ga, = torch.autograd.grad(l, wa_)
-            ga = ga * dl
-            ctx.buckets.sink([("wa", ga)])
-        ctx.buckets.sync_early()
-        return None, None, ga, gb
-
-
-def _worker_sink(rank, world, port, outdir):
+def _worker_model(rank, world, port, outdir):
+    """The product model classes on the ABI emulator (CPU), flat gradient arena + in-place bucket all-reduce over gloo."""
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
-    from wav2vec2forbrain_b200 import dist as bdist
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from tests import abi_emulator
+    from tests.golden_util import load_case
+    from wav2vec2forbrain_b200 import dist as bdist, engine, models
+    from wav2vec2forbrain_b200.config import W2VConfig
+    engine.ops = abi_emulator
+    models._EMULATED = True
     bdist.init_process_group("gloo")
-    torch.manual_seed(5)
-    wa, wb = nn.Parameter(torch.randn(5, 6)), nn.Parameter(torch.randn(2, 5))
-    other = nn.Parameter(torch.randn(3))           # reduced by the ordinary hook path in the same step
-    gb = bdist.GradientBuckets([wa, wb, other], bucket_bytes=16, process_group=None, overlap=False)
-    gb.param_of_name = {"wa": wa, "wb": wb}
-    g = torch.Generator().manual_seed(100)
-    data = torch.randn(8, 6, generator=g)
-    x = data[bdist.shard_indices(8, rank, world)]
-    loss = _NodeFn.apply(gb, x, wa, wb) + (other * (rank + 1)).sum()
-    loss.backward()
-    gb.finish()
-    torch.save((wa.grad.clone(), wb.grad.clone(), other.grad.clone()), os.path.join(outdir, f"s{rank}.pt"))
+    rec, _, _, sd, batch = load_case("tiny_base")
+    be, w = rec["be"], rec["w2v"]
+    ck = "golden/tiny_base_dp"
+    models.register_architecture(ck, lambda **kw: W2VConfig(**dict(dict(
+        kind="base", hidden=w["hidden"], layers=w["layers"], heads=w["heads"], ffn=w["ffn"], vocab=w["vocab"],
+        pos_conv_k=w["pos_conv_k"], pos_conv_groups=w["pos_conv_groups"], hidden_dropout=0.0, attention_dropout=0.0,
+        activation_dropout=0.0, final_dropout=0.0, layerdrop=0.5), **kw)), be["out_size"])
+    args = models.BrainEncoderArgs(encoder_gru_hidden_size=be["gru_hidden"], encoder_num_gru_layers=be["gru_layers"],
+                                   encoder_fc_hidden_sizes=tuple(be["fc_hidden"]), gaussian_smooth_width=be["smooth_sigma"])
+    brain = models.B2P2TModel(args, models.B2TBrainFeatureExtractor(args, ck, 256 * 32), wav2vec_checkpoint=ck)
+    m = models.W2VBrainEncoderModel(args, brain, ck, None, True)
+    m.load_state_dict(sd, strict=True)
+    with torch.no_grad():
+        for p in m.parameters():
+            p.add_(0.01 * rank)                      # DataParallel must broadcast rank 0's weights
+    dp = bdist.DataParallel(m, bucket_bytes=4096, overlap=False)
+    assert isinstance(dp.buckets, bdist.ArenaBuckets) and len(dp.buckets.buckets) > 4
+    m.train()
+    B = batch["input"].shape[0]
+    sel = [b for b in range(B) if b % world == rank] if B >= world else [0]
+    # every rank gets a shard of the same size (B = 3 in the golden: trials 0 / 1)
+    sel = [rank % B]
+    mb = models.B2tSampleBatch(batch["input"][sel], batch["target"][sel])
+    mb.day_idxs, mb.input_lens, mb.target_lens = batch["day_idxs"][sel], batch["input_lens"][sel], batch["target_lens"][sel]
+    res = []
+    for step in range(3):
+        m.zero_grad(set_to_none=True)
+        # local gradients of this shard, no collective
+        dp.buckets.enabled = False
+        st = m.runtime.layerdrop_gen.get_state()
+        seed_step = m.runtime.step
+        m.forward(mb).loss.backward()
+        local = {k: p.grad.clone() for k, p in m.named_parameters() if p.grad is not None}
+        # the same step again (same LayerDrop draw, same seeds) with the in-place all-reduce
+        m.zero_grad(set_to_none=True)
+        dp.buckets.enabled = True
+        m.runtime.layerdrop_gen.set_state(st)
+        m.runtime.step = seed_step
+        m.forward(mb).loss.backward()
+        tn = torch.nn.utils.clip_grad_norm_(m.parameters(), 1e9)       # no finish() call before it
+        red = {k: p.grad.clone() for k, p in m.named_parameters() if p.grad is not None}
+        assert all(m.runtime.grad_arena().owns(k, p.grad) for k, p in m.named_parameters() if p.grad is not None)
+        res.append((local, red, tn.item()))
+    torch.save((rank, res, m.runtime.engine.arena_copies), os.path.join(outdir, f"m{rank}.pt"))
     dist.barrier()
     dist.destroy_process_group()
 
 
-def test_early_sink_reduces_inside_the_node_and_hooks_skip_those_parameters(tmp_path):
+def test_product_model_arena_buckets_average_in_place(tmp_path):
     world, port = 2, _free_port()
     ctx = mp.get_context("spawn")
-    procs = [ctx.Process(target=_worker_sink, args=(r, world, port, str(tmp_path))) for r in range(world)]
+    procs = [ctx.Process(target=_worker_model, args=(r, world, port, str(tmp_path))) for r in range(world)]
     for p in procs:
         p.start()
     for p in procs:
-        p.join(timeout=180)
+        p.join(timeout=600)
         assert p.exitcode == 0
-    outs = [torch.load(os.path.join(str(tmp_path), f"s{r}.pt"), weights_only=False) for r in range(world)]
-    torch.manual_seed(5)
-    wa, wb = torch.randn(5, 6, requires_grad=True), torch.randn(2, 5, requires_grad=True)
-    g = torch.Generator().manual_seed(100)
-    data = torch.randn(8, 6, generator=g)
-    ((data @ wa.t()) @ wb.t()).pow(2).mean().backward()       # equal shards: mean of per-rank means = global mean
-    for r in range(world):
-        assert torch.allclose(outs[r][0], wa.grad, atol=1e-6)
-        assert torch.allclose(outs[r][1], wb.grad, atol=1e-6)   # averaged once, not twice
-        assert torch.allclose(outs[r][2], torch.full((3,), 1.5), atol=1e-6)
+    outs = [torch.load(os.path.join(str(tmp_path), f"m{r}.pt"), weights_only=False) for r in range(world)]
+    saw_skip = False
+    for step in range(3):
+        l0, r0, n0 = outs[0][1][step]
+        l1, r1, n1 = outs[1][1][step]
+        assert set(l0) == set(l1) == set(r0) == set(r1)           # LayerDrop decisions identical on both ranks
+        saw_skip = saw_skip or not any(".layers.0." in k for k in r0) or not any(".layers.1." in k for k in r0)
+        for k in l0:
+            want = 0.5 * (l0[k] + l1[k])
+            assert torch.allclose(r0[k], want, rtol=1e-5, atol=1e-8), (step, k)
+            assert torch.equal(r0[k], r1[k]), (step, k)
+        total = torch.sqrt(sum((v.double() ** 2).sum() for v in r0.values())).item()
+        assert abs(n0 - total) < 1e-5 * total and abs(n1 - total) < 1e-5 * total   # clip saw the averaged gradients
+    assert saw_skip, "layerdrop=0.5 over 3 steps should have skipped a layer at least once (seeded)"

@@ -63,3 +63,58 @@ def test_frozen_w2v_backward_skips_weight_gradients_only(engine_mod, name):
     assert not any(k.endswith(".weight") and v is not None and v.dim() >= 2 and "depthwise" not in k for k, v in G.items())
     for k, v in Gb.items():
         assert torch.equal(v, G_full[k]), k
+
+
+@pytest.mark.parametrize("name", ["tiny_base", "tiny_conformer"])
+def test_flat_gradient_arena_through_the_model_classes(engine_mod, monkeypatch, name):
+    """The model classes on the emulator: with the flat gradient arena every .grad is a view of one buffer at the
+    parameter's slot (no copy at the end of the node except for a handful of tiny GRU bias tensors), and the values are
+    bit-identical to the arena-less path."""
+    from wav2vec2forbrain_b200 import models
+    from wav2vec2forbrain_b200.config import W2VConfig
+    monkeypatch.setattr(models, "_EMULATED", True)
+    rec, _, _, sd, batch = load_case(name)
+    be, w = rec["be"], rec["w2v"]
+    ck = "golden/arena_" + name
+    models.register_architecture(ck, lambda **kw: W2VConfig(**dict(dict(
+        kind=w["kind"], hidden=w["hidden"], layers=w["layers"], heads=w["heads"], ffn=w["ffn"], vocab=w["vocab"],
+        pos_conv_k=w["pos_conv_k"], pos_conv_groups=w["pos_conv_groups"], dw_kernel=w["dw_kernel"],
+        hidden_act="gelu" if w["kind"] == "base" else "swish", hidden_dropout=0.0, attention_dropout=0.0,
+        activation_dropout=0.0, final_dropout=0.0, conv_dropout=0.0, layerdrop=0.0), **kw)), be["out_size"])
+    args = models.BrainEncoderArgs(encoder_gru_hidden_size=be["gru_hidden"], encoder_num_gru_layers=be["gru_layers"],
+                                   encoder_fc_hidden_sizes=tuple(be["fc_hidden"]), gaussian_smooth_width=be["smooth_sigma"])
+    brain = models.B2P2TModel(args, models.B2TBrainFeatureExtractor(args, ck, 256 * 32), wav2vec_checkpoint=ck)
+    m = models.W2VBrainEncoderModel(args, brain, ck, None, True) if w["kind"] == "base" else \
+        models.W2VConformerBrainEncoderModel(brain, ck)
+    m.load_state_dict(sd, strict=True)
+    m.train()
+    mb = models.B2tSampleBatch(batch["input"], batch["target"])
+    mb.day_idxs, mb.input_lens, mb.target_lens = batch["day_idxs"], batch["input_lens"], batch["target_lens"]
+
+    def grads(use_arena):
+        m.runtime.use_arena = use_arena
+        m.zero_grad(set_to_none=True)
+        m.runtime.step = 0
+        m.forward(mb).loss.backward()
+        return {k: p.grad for k, p in m.named_parameters() if p.grad is not None}
+    plain = {k: v.clone() for k, v in grads(False).items()}
+    assert m.runtime.engine.arena_copies == 0
+    flat = grads(True)
+    arena = m.runtime.grad_arena()
+    assert set(flat) == set(plain)
+    for k, g in flat.items():
+        assert arena.owns(k, g), k                      # .grad IS the arena slot
+        assert torch.equal(g, plain[k]), k
+    n_gru_bias_hh = sum(1 for k in flat if ".gru.bias_hh_" in k)
+    assert m.runtime.engine.arena_copies <= n_gru_bias_hh
+    # a second step reuses the same slots (stable gradient addresses for the optimizer tables)
+    ptrs = {k: g.data_ptr() for k, g in flat.items()}
+    flat2 = grads(True)
+    assert {k: g.data_ptr() for k, g in flat2.items()} == ptrs
+    # parameters that still hold a .grad (no zero_grad): the engine must not overwrite their slots -> accumulation works
+    before = {k: g.clone() for k, g in flat2.items()}
+    m.runtime.step = 0
+    m.forward(mb).loss.backward()
+    for k, p in m.named_parameters():
+        if p.grad is not None:
+            assert torch.allclose(p.grad, 2 * before[k], rtol=1e-6, atol=1e-12), k

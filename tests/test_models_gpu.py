@@ -46,13 +46,28 @@ def test_state_dict_and_training_step(name):
     assert {k: tuple(v.shape) for k, v in m.state_dict().items()} == rec["state_dict_keys"]
     res = m.load_state_dict(sd, strict=True)
     assert not res.missing_keys and not res.unexpected_keys
+    conformer = rec["w2v"]["kind"] == "conformer"
+    # eval mode / no_grad path first (the train pass below moves the conformer's BatchNorm running statistics, and the
+    # golden's eval outputs were recorded before its train pass): greedy decode ids identical to the reference's argmax
+    m.eval()
+    with torch.no_grad():
+        ev = m.forward(make_batch(models, batch))
+    assert rel_l2(ev.logits.cpu(), rec["logits_eval"]) < 2e-4
+    assert torch.equal(ev.logits.argmax(-1).cpu().to(torch.int16), rec["argmax_eval"])
+    # sub-module calls used by the analysis helpers (latent_analysis_util.py:196-201)
+    with torch.no_grad():
+        enc = m.brain_encoder.forward(make_batch(models, batch))
+        res = m.w2v_encoder.forward(enc.logits)
+        lg = res if conformer else res[0]      # conformer: logits only (w2v_conformer_custom_feat_extractor.py:67-76)
+        assert isinstance(res, torch.Tensor) == conformer
+    assert rel_l2(enc.logits.cpu(), rec["features"]) < 2e-4
+    assert rel_l2(lg.cpu(), rec["logits_eval"]) < 2e-4
     m.train()
     out = m.forward(make_batch(models, batch))
     assert isinstance(out.metrics["ctc_loss"], float)
     out.loss.backward()
     assert rel_l2(out.logits.detach().cpu(), rec["logits_train"]) < 2e-4
     assert abs(out.loss.item() - rec["loss_train"].item()) < 2e-4 * abs(rec["loss_train"].item())
-    conformer = rec["w2v"]["kind"] == "conformer"
     if conformer:
         # W2VConformerBrainEncoderModel.forward returns neither logit_lens nor hidden_states
         # (w2v_conformer_custom_feat_extractor.py:55-59)
@@ -67,20 +82,6 @@ def test_state_dict_and_training_step(name):
         ref, sl = golden_grad(rec, k)
         err = (sl(got[k].cpu()).double() - ref.double()).norm().item()
         assert err <= 1e-3 * ref.double().norm().item() + 1e-6 * gmax, k
-    # eval mode / no_grad path, greedy decode ids identical to the reference's argmax
-    m.eval()
-    with torch.no_grad():
-        ev = m.forward(make_batch(models, batch))
-    assert rel_l2(ev.logits.cpu(), rec["logits_eval"]) < 2e-4
-    assert torch.equal(ev.logits.argmax(-1).cpu().to(torch.int16), rec["argmax_eval"])
-    # sub-module calls used by the analysis helpers (latent_analysis_util.py:196-201)
-    with torch.no_grad():
-        enc = m.brain_encoder.forward(make_batch(models, batch))
-        res = m.w2v_encoder.forward(enc.logits)
-        lg = res if conformer else res[0]      # conformer: logits only (w2v_conformer_custom_feat_extractor.py:67-76)
-        assert isinstance(res, torch.Tensor) == conformer
-    assert rel_l2(enc.logits.cpu(), rec["features"]) < 2e-4
-    assert rel_l2(lg.cpu(), rec["logits_eval"]) < 2e-4
 
 
 def test_adam_step_moves_only_trained_parameters():

@@ -137,11 +137,16 @@ def _zeros(n: int, dev) -> Tensor:
     return _e.ops.zeros(n, device=dev)
 
 
+def _gz(eng, name: str, n: int, dev) -> Tensor:
+    """zero-initialised gradient accumulator of parameter `name` (its arena slot when one is attached)"""
+    return eng._gout(name, (n,), dev, zero=True)
+
+
 def _ln_bwd(eng, P, G, name: str, dy: Tensor, x: Tensor, ln, **kw):
     """LayerNorm backward; parameter gradients go to G[name.weight / name.bias]."""
     dev = dy.device
     n = x.shape[1]
-    G[name + ".weight"], G[name + ".bias"] = _zeros(n, dev), _zeros(n, dev)
+    G[name + ".weight"], G[name + ".bias"] = _gz(eng, name + ".weight", n, dev), _gz(eng, name + ".bias", n, dev)
     return _e.ops.layernorm_bwd(dy, x, P[name + ".weight"], ln[0], ln[1], G[name + ".weight"], G[name + ".bias"],
                                 three=eng.three, **kw)
 
@@ -154,13 +159,15 @@ def _ffn_backward(eng, P, G, pfx: str, ln: str, st: dict, g_hi, g_lo, db_out: Te
     D, F = cfg.hidden, cfg.ffn
     p_act = cfg.activation_dropout if training else 0.0
     G[pfx + "output_dense.bias"] = ops.axpby(db_out, None, alpha=0.5, out=db_out)
-    G[pfx + "output_dense.weight"] = eng._wgrad(g_hi, g_lo, st["f_hi"], st["f_lo"], D, F, M, alpha=0.5)
-    db1 = _zeros(F, g_hi.device)
+    G[pfx + "output_dense.weight"] = eng._wgrad(g_hi, g_lo, st["f_hi"], st["f_lo"], D, F, M, alpha=0.5,
+                                                name=pfx + "output_dense.weight")
+    db1 = _gz(eng, pfx + "intermediate_dense.bias", F, g_hi.device)
     _, dp_hi, dp_lo = eng._dgrad(g_hi, g_lo, eng._w(P, pfx + "output_dense.weight"), M, D, F, want_f32=False, want_split=True,
                                  aux=st["pre"], aux_mode=cfg.hidden_act, drop_p=p_act, drop_seed=_seed(seed, layer, site),
                                  colsum=db1, alpha=0.5)
     G[pfx + "intermediate_dense.bias"] = db1
-    G[pfx + "intermediate_dense.weight"] = eng._wgrad(dp_hi, dp_lo, st["u_hi"], st["u_lo"], F, D, M)
+    G[pfx + "intermediate_dense.weight"] = eng._wgrad(dp_hi, dp_lo, st["u_hi"], st["u_lo"], F, D, M,
+                                                      name=pfx + "intermediate_dense.weight")
     du, _, _ = eng._dgrad(dp_hi, dp_lo, eng._w(P, pfx + "intermediate_dense.weight"), M, F, D)
     return _ln_bwd(eng, P, G, ln, du, st["x"], st["ln"], dres=d_res, **ln_kw)
 
@@ -185,7 +192,7 @@ def backward(eng, P, S: dict, dh: Tensor, G: Dict[str, Tensor]) -> Tensor:
             continue
         L = Q + f"layers.{i}."
         # ---- final LayerNorm; its masked copy is the operand of the ffn2 output GEMMs ----
-        db = _zeros(D, dev)
+        db = _gz(eng, L + "ffn2.output_dense.bias", D, dev)
         d4, g_hi, g_lo = _ln_bwd(eng, P, G, L + "final_layer_norm", dh, st["final"]["x"], st["final"]["ln"], dcol=db,
                                  br_drop_p=p_h, br_seed=_seed(seed, i, 7))
         # ---- 1/2 ffn2: x = conv output h3; the masked copy of d h3 feeds pointwise_conv2's backward ----
@@ -195,43 +202,49 @@ def backward(eng, P, S: dict, dh: Tensor, G: Dict[str, Tensor]) -> Tensor:
         cm = L + "conv_module."
         cs = st["conv"]
         w2 = _w2d(eng, P, cm + "pointwise_conv2.weight")
-        G[cm + "pointwise_conv2.weight"] = _v3(eng._wgrad(g_hi, g_lo, cs["s_hi"], cs["s_lo"], D, D, M))
+        G[cm + "pointwise_conv2.weight"] = _v3(eng._wgrad(g_hi, g_lo, cs["s_hi"], cs["s_lo"], D, D, M,
+                                                          name=cm + "pointwise_conv2.weight"))
         dsil, _, _ = eng._dgrad(g_hi, g_lo, w2, M, D, D)
         gam, bet = P[cm + "batch_norm.weight"], P[cm + "batch_norm.bias"]
         bn_mean, bn_rstd = cs["bn"]
-        dgam, dbet = ops.bn_silu_bwd_stats(dsil, cs["dwo"], bn_mean, bn_rstd, gam, bet)
+        dgam, dbet = ops.bn_silu_bwd_stats(dsil, cs["dwo"], bn_mean, bn_rstd, gam, bet,
+                                           dgamma_out=_gz(eng, cm + "batch_norm.weight", D, dev),
+                                           dbeta_out=_gz(eng, cm + "batch_norm.bias", D, dev))
         G[cm + "batch_norm.weight"], G[cm + "batch_norm.bias"] = dgam, dbet
         dg_hi, dg_lo, ddw = ops.glu_dwconv_bwd(dsil, cs["dwo"], cs["g"], P[cm + "depthwise_conv.weight"], bn_mean, bn_rstd, gam,
-                                               bet, dgam, dbet, B, T, training, three=three)
+                                               bet, dgam, dbet, B, T, training, three=three,
+                                               dw_out=eng._gout(cm + "depthwise_conv.weight", P[cm + "depthwise_conv.weight"].shape,
+                                                                dev, zero=True))
         G[cm + "depthwise_conv.weight"] = ddw
-        G[cm + "pointwise_conv1.weight"] = _v3(eng._wgrad(dg_hi, dg_lo, cs["n_hi"], cs["n_lo"], 2 * D, D, M))
+        G[cm + "pointwise_conv1.weight"] = _v3(eng._wgrad(dg_hi, dg_lo, cs["n_hi"], cs["n_lo"], 2 * D, D, M,
+                                                          name=cm + "pointwise_conv1.weight"))
         dn, _, _ = eng._dgrad(dg_hi, dg_lo, _w2d(eng, P, cm + "pointwise_conv1.weight"), M, 2 * D, D)
-        dbo = _zeros(D, dev)
+        dbo = _gz(eng, L + "self_attn.linear_out.bias", D, dev)
         d2, g_hi, g_lo = _ln_bwd(eng, P, G, cm + "layer_norm", dn, cs["x"], cs["ln"], dres=d3, dcol=dbo, br_drop_p=p_att,
                                  br_seed=_seed(seed, i, 4))
         # ---- self-attention ----
         sa = L + "self_attn."
         at = st["attn"]
         G[sa + "linear_out.bias"] = dbo
-        G[sa + "linear_out.weight"] = eng._wgrad(g_hi, g_lo, at["c_hi"], at["c_lo"], D, D, M)
+        G[sa + "linear_out.weight"] = eng._wgrad(g_hi, g_lo, at["c_hi"], at["c_lo"], D, D, M, name=sa + "linear_out.weight")
         dctx, _, _ = eng._dgrad(g_hi, g_lo, eng._w(P, sa + "linear_out.weight"), M, D, D)
         dqkv, dq_hi, dq_lo = ops.attention_bwd(at["qkv"], at["probs"], dctx, ds_ws, B, T, NH, hd, three=three, drop_p=p_att,
                                                seed=_seed(seed, i, 3))
-        dbq = _zeros(3 * D, dev)
+        dbq = eng._gout_cat([sa + nm + ".bias" for nm in ("linear_q", "linear_k", "linear_v")], (3 * D,), dev, zero=True)
         ops.colsum(dqkv, dbq)
         for j, nm in enumerate(("linear_q", "linear_k", "linear_v")):
             G[sa + nm + ".bias"] = dbq[j * D:(j + 1) * D]
         qk_hi, qk_lo = dq_hi[:, :2 * D], (None if dq_lo is None else dq_lo[:, :2 * D])
         v_hi, v_lo = dq_hi[:, 2 * D:], (None if dq_lo is None else dq_lo[:, 2 * D:])
-        dwqk = eng._wgrad(qk_hi, qk_lo, at["r_hi"], at["r_lo"], 2 * D, D, M)
+        dwqk = eng._wgrad(qk_hi, qk_lo, at["r_hi"], at["r_lo"], 2 * D, D, M, name=[sa + "linear_q.weight", sa + "linear_k.weight"])
         if dwqk is not None:
             G[sa + "linear_q.weight"], G[sa + "linear_k.weight"] = dwqk[:D], dwqk[D:]
-        G[sa + "linear_v.weight"] = eng._wgrad(v_hi, v_lo, at["y_hi"], at["y_lo"], D, D, M)
+        G[sa + "linear_v.weight"] = eng._wgrad(v_hi, v_lo, at["y_hi"], at["y_lo"], D, D, M, name=sa + "linear_v.weight")
         wqk = eng._w_cat(P, sa + "qk", [sa + "linear_q.weight", sa + "linear_k.weight"])
         du_rot, _, _ = eng._dgrad(qk_hi, qk_lo, wqk, M, 2 * D, D)
         du_v, _, _ = eng._dgrad(v_hi, v_lo, eng._w(P, sa + "linear_v.weight"), M, D, D)
         du = ops.rope_bwd_add(du_rot, du_v, cos, sin, T, hd)
-        db = _zeros(D, dev)
+        db = _gz(eng, L + "ffn1.output_dense.bias", D, dev)
         d1, g_hi, g_lo = _ln_bwd(eng, P, G, L + "self_attn_layer_norm", du, at["x"], at["ln"], dres=d2, dcol=db, br_drop_p=p_h,
                                  br_seed=_seed(seed, i, 2))
         # ---- 1/2 ffn1 ----

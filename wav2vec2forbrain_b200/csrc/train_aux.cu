@@ -35,10 +35,11 @@ __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, 
     // torch.optim.Adam (single-tensor path, amsgrad=False, maximize=False), same operation order
     g *= gs;
     g = fmaf(h.weight_decay, p, g);                 // grad.add(param, alpha=weight_decay)
-    m = m + (g - m) * (1.0f - h.beta1);             // exp_avg.lerp_(grad, 1 - beta1)
-    v = fmaf(v, h.beta2, (1.0f - h.beta2) * g * g); // exp_avg_sq.mul_(beta2).addcmul_(grad, grad, value=1 - beta2)
+    m = m + (g - m) * h.one_minus_beta1;            // exp_avg.lerp_(grad, 1 - beta1)
+    v = v * h.beta2;                                // exp_avg_sq.mul_(beta2)
+    v = fmaf(h.one_minus_beta2 * g, g, v);          //           .addcmul_(grad, grad, value=1 - beta2)
     const float denom = sqrtf(v) / h.bias_c2_sqrt + h.eps;
-    p = p - (h.lr / h.bias_c1) * (m / denom);       // param.addcdiv_(exp_avg, denom, value=-step_size)
+    p = p - h.step_size * (m / denom);              // param.addcdiv_(exp_avg, denom, value=-step_size)
 }
 
 __global__ void __launch_bounds__(MT_THREADS) adam_multi_kernel(const MtTensor* __restrict__ tensors,
@@ -405,7 +406,7 @@ extern "C" int b2t_adam_multi(const b2t_mt_tensor* tensors, const int32_t* chunk
     memset(&g, 0, sizeof(g));
     for (int i = 0; i < n_groups; ++i) {
         g.g[i] = groups[i];
-        B2T_CHECK_ARG(groups[i].bias_c1 > 0.f && groups[i].bias_c2_sqrt > 0.f, "b2t_adam_multi: group %d: step must be >= 1", i);
+        B2T_CHECK_ARG(groups[i].bias_c2_sqrt > 0.f, "b2t_adam_multi: group %d: step must be >= 1", i);
     }
     adam_multi_kernel<<<n_chunks, MT_THREADS, 0, (cudaStream_t)stream>>>(reinterpret_cast<const MtTensor*>(tensors),
                                                                          reinterpret_cast<const int2*>(chunks), g, grad_scale);

@@ -1,17 +1,22 @@
-"""Data-parallel training across the GPUs of one box: one process per GPU, torch.distributed (NCCL
-over NVLink 5 / NVSwitch), bucketed gradient all-reduce launched as soon as a bucket's gradients
-exist, on a side stream, overlapped with the rest of backward.
+"""Data-parallel training across the GPUs of one box: one process per GPU, torch.distributed (NCCL over NVLink 5 /
+NVSwitch), gradient buckets all-reduced IN PLACE on a side stream as soon as their last gradient exists, overlapped with
+the rest of backward.
 
-The reference is single-process (no torch.distributed anywhere); the semantics kept
-are those of SURVEY.md §5.4 / §8(e): each rank runs the reference step on its shard of the batch,
-gradients are averaged (CTC reduction is a batch mean, so equal shards reproduce the global-batch
-gradient), parameters that never receive a gradient (unused inpLayer*, hidden_start, conformer
-pos_conv_embed, LayerDrop-skipped layers) are tolerated, LayerDrop decisions are identical on all
-ranks, dropout masks differ per rank.
+The reference is single-process (no torch.distributed anywhere); the semantics kept are those of
+SURVEY.md §5.4 / §8(e): each rank runs the reference step on its shard of the batch, gradients are averaged (CTC
+reduction is a batch mean, so equal shards reproduce the global-batch gradient), parameters that never receive a
+gradient (unused inpLayer*, hidden_start, conformer pos_conv_embed, LayerDrop-skipped layers) are tolerated, LayerDrop
+decisions are identical on all ranks, dropout masks differ per rank, BatchNorm statistics stay per rank.
 
-Our backward produces gradients in two bursts (w2v encoder + head first, brain encoder second: the
-two autograd nodes of models.py), so the w2v buckets travel while the brain-encoder backward
-(GRU recurrence, ~30 % of the step) still computes.
+Two bucket implementations:
+  * `ArenaBuckets` (the product path): the model's gradients live in one flat buffer (flat.GradArena); a bucket is a
+    contiguous range of it, so `all_reduce` runs on the gradients themselves — no flatten copy, no copy back.  The
+    engine reports finished gradients after every encoder layer (`Engine.emit_grads`), so buckets leave while the
+    layers below are still being back-propagated, not only when the whole autograd node returns.
+  * `GradientBuckets` (any nn.Module): classic post-accumulate-grad hooks + flatten / all-reduce / copy back.
+Both finish (wait for the collectives and make the averaged values visible to the compute stream) in a callback the
+autograd engine runs when `loss.backward()` ends, so `clip_grad_norm_` (src/train/train_loop.py:72-75) and
+`optimizer.step()` (:78) of the unmodified Trainer see reduced gradients without any extra call.
 """
 from __future__ import annotations
 
@@ -46,38 +51,151 @@ def shard_indices(n: int, rank: int, world: int) -> List[int]:
     return list(range(rank, n, world))
 
 
-class _null:
-    def __enter__(self):
-        return self
-
-    def __exit__(self, *exc):
+def _queue_backward_callback(fn) -> bool:
+    """Run `fn` when the current loss.backward() finishes (what DDP does); False outside a backward pass."""
+    try:
+        torch.autograd.Variable._execution_engine.queue_callback(fn)
+        return True
+    except RuntimeError:
         return False
 
 
-class GradientBuckets:
-    """Bucketed asynchronous all-reduce(mean) of parameter gradients.
-
-    Buckets are formed over the parameters that may receive a gradient, in reverse registration
-    order (≈ reverse execution order: lm_head, encoder layers L-1..0, FC, GRU, day weights), capped
-    at `bucket_bytes`.  A bucket is launched from the post-accumulate-grad hook of its last arriving
-    parameter; parameters whose gradient never arrives (LayerDrop, unused) are flushed as zeros at
-    `finish()`, which every rank calls before optimizer.step / clip_grad_norm_."""
-
-    def __init__(self, params: List[nn.Parameter], bucket_bytes: int = 48 << 20, process_group=None,
-                 overlap: bool = True):
+class _BucketBase:
+    def __init__(self, process_group, overlap: bool):
         self.group = process_group
         self.world = dist.get_world_size(process_group)
-        self.params = [p for p in params if p.requires_grad]
         self.overlap = overlap and torch.cuda.is_available()
         self.stream = torch.cuda.Stream() if self.overlap else None
+        self._avg = dist.get_backend(process_group) == "nccl"      # gloo has no ReduceOp.AVG
+        self.enabled = True          # bench.py switches the collective off to measure the exposed communication
+        self.bytes_per_step = 0
+        self._bytes_now = 0
+        self._cb_queued = False
+        self._active = False
+
+    def _all_reduce(self, flat: torch.Tensor):
+        """mean over ranks, in place, asynchronously on the side stream when overlapping"""
+        self._bytes_now += flat.numel() * flat.element_size()
+        if not self.enabled:
+            return None
+        if self.overlap:
+            self.stream.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(self.stream):
+                if self._avg:
+                    return dist.all_reduce(flat, op=dist.ReduceOp.AVG, group=self.group, async_op=True)
+                flat.div_(self.world)
+                return dist.all_reduce(flat, group=self.group, async_op=True)
+        if self._avg:
+            dist.all_reduce(flat, op=dist.ReduceOp.AVG, group=self.group)
+        else:
+            flat.div_(self.world)
+            dist.all_reduce(flat, group=self.group)
+        return None
+
+    def _mark_active(self) -> None:
+        if not self._active:
+            self._active = True
+            self._cb_queued = _queue_backward_callback(self._backward_done)
+
+    def _backward_done(self) -> None:
+        self._cb_queued = False
+        self.finish()
+
+    def finish(self) -> None:       # pragma: no cover - interface
+        raise NotImplementedError
+
+
+class ArenaBuckets(_BucketBase):
+    """In-place bucketed all-reduce over a flat gradient arena (see module docstring)."""
+
+    def __init__(self, arena, bucket_bytes: int = 48 << 20, process_group=None, overlap: bool = True,
+                 boundaries=("brain_encoder.", "w2v_encoder."), early: bool = True):
+        super().__init__(process_group, overlap)
+        self.arena = arena
+        self.early = early
+        self.boundaries = tuple(boundaries)
+        raw = arena.make_buckets(bucket_bytes, self.boundaries)
+        self.buckets = [arena.buf[s:e] for s, e, _ in raw]
+        self.bucket_names = [names for _, _, names in raw]
+        self.bucket_tag = [self._tag(names[0]) for names in self.bucket_names]
+        self.bucket_of: Dict[str, int] = {n: bi for bi, names in enumerate(self.bucket_names) for n in names}
+        self._pending: List[int] = []
+        self._seen: List[int] = []
+        self._launched: List[bool] = []
+        self._work: list = []
+        self._reset()
+
+    def _tag(self, name: str) -> str:
+        for b in self.boundaries:
+            if name.startswith(b):
+                return b
+        return ""
+
+    def _reset(self) -> None:
+        self._pending = [len(n) for n in self.bucket_names]
+        self._seen = [0] * len(self.buckets)
+        self._launched = [False] * len(self.buckets)
+        self._work = []
+        self._active = False
+        self.bytes_per_step, self._bytes_now = self._bytes_now or self.bytes_per_step, 0
+
+    # ---- called by the engine -------------------------------------------------------------------------------
+    def sink(self, named) -> None:
+        """named: [(parameter name, finished gradient = its arena slot)].  A bucket whose every gradient has arrived
+        starts its all-reduce right away, behind everything issued so far on the compute stream."""
+        self._mark_active()
+        for name, _ in named:
+            bi = self.bucket_of.get(name)
+            if bi is None:
+                continue
+            self._pending[bi] -= 1
+            self._seen[bi] += 1
+            if self._pending[bi] < 0:
+                raise RuntimeError(f"gradient of {name} arrived twice before finish(): one backward pass per "
+                                   "optimizer step (gradient accumulation is not supported by ArenaBuckets)")
+            if self.early and self._pending[bi] == 0 and not self._launched[bi]:
+                self._launch(bi)
+
+    def node_end(self, prefix: str = "") -> None:
+        """End of an autograd node: everything of that node which received at least one gradient leaves now (LayerDrop
+        or unused parameters keep some buckets from ever completing; their slots hold zeros on every rank, and the
+        launch order is the same on every rank because LayerDrop decisions are shared)."""
+        for bi in range(len(self.buckets) - 1, -1, -1):       # backward fills the arena from its end
+            if not self._launched[bi] and self._seen[bi] > 0 and (not prefix or self.bucket_tag[bi] == prefix):
+                self._launch(bi)
+
+    def _launch(self, bi: int) -> None:
+        self._launched[bi] = True
+        work = self._all_reduce(self.buckets[bi])
+        self._work.append(work)
+
+    # ---- end of backward ------------------------------------------------------------------------------------
+    def finish(self) -> None:
+        if not self._active:
+            return
+        self.node_end("")
+        if self.overlap:
+            with torch.cuda.stream(self.stream):
+                for w in self._work:
+                    if w is not None:
+                        w.wait()
+            torch.cuda.current_stream().wait_stream(self.stream)
+        self._reset()
+
+
+class GradientBuckets(_BucketBase):
+    """Bucketed asynchronous all-reduce(mean) of parameter gradients of ANY module (hook driven).
+
+    Buckets are formed over the parameters that may receive a gradient, in reverse registration order (≈ reverse
+    execution order), capped at `bucket_bytes`.  A bucket is launched from the post-accumulate-grad hook of its last
+    arriving parameter; parameters whose gradient never arrives (LayerDrop, unused) are left out at `finish()`, which
+    runs when loss.backward() ends.  Gradients are flattened into a bucket copy and copied back (the arena path avoids
+    both)."""
+
+    def __init__(self, params: List[nn.Parameter], bucket_bytes: int = 48 << 20, process_group=None, overlap: bool = True):
+        super().__init__(process_group, overlap)
+        self.params = [p for p in params if p.requires_grad]
         self.bucket_bytes = bucket_bytes
-        # early path (sink / sync_early): gradients handed over by the engine while the backward schedule of the
-        # same autograd node is still being issued; keyed by parameter name
-        self.param_of_name: Dict[str, nn.Parameter] = {}
-        self._early: List[torch.Tensor] = []
-        self._early_bytes = 0
-        self._early_work = []
-        self._early_done = set()
         self.buckets: List[List[nn.Parameter]] = []
         cur, size = [], 0
         for p in reversed(self.params):
@@ -104,84 +222,32 @@ class GradientBuckets:
         self._launched = [False] * len(self.buckets)
         self._work = []
         self._active = False
-        self._early_done = set()
-
-    # ---- early path ---------------------------------------------------------------------------------
-    def sink(self, named) -> None:
-        """named: [(parameter name, finished gradient tensor)].  The three autograd nodes of the model return all
-        their gradients at once, so post-accumulate hooks alone cannot overlap anything with the node's own
-        backward; the engine calls this after every encoder layer instead.  Full buckets start their all-reduce on
-        the side stream right away (behind everything issued so far on the compute stream)."""
-        for name, g in named:
-            p = self.param_of_name.get(name)
-            if p is None or not p.requires_grad:
-                continue
-            self._active = True
-            self._early.append(g)
-            self._early_done.add(id(p))
-            self._early_bytes += g.numel() * g.element_size()
-        if self._early_bytes >= self.bucket_bytes:
-            self._flush_early()
-
-    def _flush_early(self) -> None:
-        grads, self._early, self._early_bytes = self._early, [], 0
-        if not grads:
-            return
-        if self.overlap:
-            self.stream.wait_stream(torch.cuda.current_stream())
-            with torch.cuda.stream(self.stream):
-                flat = torch.cat([g.reshape(-1) for g in grads])
-                flat.div_(self.world)
-                work = dist.all_reduce(flat, group=self.group, async_op=True)
-        else:
-            flat = torch.cat([g.reshape(-1) for g in grads])
-            flat.div_(self.world)
-            dist.all_reduce(flat, group=self.group)
-            work = None
-        self._early_work.append((work, flat, grads))
-
-    def sync_early(self) -> None:
-        """End of an autograd node: reduce what is left and write every averaged value back into the tensors
-        the node is about to return, ordered before anything autograd does with them."""
-        self._flush_early()
-        for work, flat, grads in self._early_work:
-            ctx = torch.cuda.stream(self.stream) if self.overlap else _null()
-            with ctx:
-                if work is not None:
-                    work.wait()
-                off = 0
-                for g in grads:
-                    n = g.numel()
-                    g.copy_(flat[off:off + n].view_as(g))
-                    off += n
-        if self.overlap and self._early_work:
-            torch.cuda.current_stream().wait_stream(self.stream)
-        self._early_work = []
+        self.bytes_per_step, self._bytes_now = self._bytes_now or self.bytes_per_step, 0
 
     def _on_grad(self, p: nn.Parameter) -> None:
-        self._active = True
+        self._mark_active()
         bi = self._bucket_of[id(p)]
         self._pending[bi] -= 1
-        if self._pending[bi] == 0 and not self._launched[bi]:
+        if self._pending[bi] < 0 or self._launched[bi]:
+            raise RuntimeError("a gradient arrived for a bucket that was already reduced: call finish() (it runs by itself "
+                               "at the end of loss.backward()) before the next backward pass; gradient accumulation "
+                               "over several backward passes is not supported")
+        if self._pending[bi] == 0:
             self._launch(bi)
 
     def _launch(self, bi: int) -> None:
         self._launched[bi] = True
-        grads = [p.grad for p in self.buckets[bi] if p.grad is not None and id(p) not in self._early_done]
+        grads = [p.grad for p in self.buckets[bi] if p.grad is not None]
         if not grads:
             return
         if self.overlap:
             self.stream.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(self.stream):
                 flat = torch.cat([g.reshape(-1) for g in grads])
-                flat.div_(self.world)
-                work = dist.all_reduce(flat, group=self.group, async_op=True)
-            self._work.append((work, flat, grads))
         else:
             flat = torch.cat([g.reshape(-1) for g in grads])
-            flat.div_(self.world)
-            dist.all_reduce(flat, group=self.group)
-            self._work.append((None, flat, grads))
+        work = self._all_reduce(flat)
+        self._work.append((work, flat, grads))
 
     def finish(self) -> None:
         """Launch what has not been launched (identical bucket composition on every rank is guaranteed by
@@ -192,21 +258,12 @@ class GradientBuckets:
             if not self._launched[bi]:
                 self._launch(bi)
         for work, flat, grads in self._work:
-            if self.overlap:
-                with torch.cuda.stream(self.stream):
-                    if work is not None:
-                        work.wait()
-                    off = 0
-                    for g in grads:
-                        n = g.numel()
-                        g.copy_(flat[off:off + n].view_as(g))
-                        off += n
-            else:
-                off = 0
-                for g in grads:
-                    n = g.numel()
-                    g.copy_(flat[off:off + n].view_as(g))
-                    off += n
+            ctx = torch.cuda.stream(self.stream) if self.overlap else _null()
+            with ctx:
+                if work is not None:
+                    work.wait()
+                if self.enabled:
+                    torch._foreach_copy_(grads, [v.view_as(g) for v, g in zip(flat.split([g.numel() for g in grads]), grads)])
         if self.overlap:
             torch.cuda.current_stream().wait_stream(self.stream)
         self.reset()
@@ -216,33 +273,44 @@ class GradientBuckets:
             h.remove()
 
 
+class _null:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        return False
+
+
 class DataParallel:
-    """Wraps a model for the unmodified reference Trainer loop (train_loop.py:44-78): broadcasts the
-    initial weights/buffers from rank 0, installs the bucket hooks, and waits for the all-reduce in an
-    optimizer step pre-hook (call `finish()` yourself before clip_grad_norm_)."""
+    """Wraps a model for the unmodified reference Trainer loop (train_loop.py:44-78): broadcasts the initial
+    weights / buffers from rank 0, installs the gradient buckets, and finishes the reduction when loss.backward()
+    ends (so clip_grad_norm_ and optimizer.step see averaged gradients)."""
 
     def __init__(self, model: nn.Module, bucket_bytes: int = 48 << 20, process_group=None, overlap: bool = True,
                  early_reduce: Optional[bool] = None):
         self.model = model
         self.group = process_group
-        for t in list(model.parameters()) + list(model.buffers()):
-            dist.broadcast(t.data, src=0, group=process_group)
+        with torch.no_grad():
+            for t in list(model.parameters()) + list(model.buffers()):
+                dist.broadcast(t, src=0, group=process_group)
         rt = getattr(model, "runtime", None)
         if rt is not None:
             rt.rank = dist.get_rank(process_group)   # per-rank dropout masks; LayerDrop generator stays shared
-        self.buckets = GradientBuckets(list(model.parameters()), bucket_bytes, process_group, overlap)
-        # early_reduce: start each bucket's all-reduce from inside the encoder's backward schedule (engine.emit_grads)
-        # instead of after the whole autograd node.  Off by default: measured on 2 B200 (conformer-large, B = 32 per
-        # GPU) the early path is SLOWER (963 vs 991 trials/s) - NCCL's CTAs take SMs from the persistent one-CTA-per-SM
-        # GEMM grid, whose statically strided tiles then need a second wave.  B2T_DP_EARLY=1 turns it on.
+            # the engine caches bf16 operand copies per parameter version: whatever ran before the broadcast is stale
+            rt.engine.weights._cache.clear()
         if early_reduce is None:
-            early_reduce = os.environ.get("B2T_DP_EARLY", "0") == "1"
-        if early_reduce and rt is not None and hasattr(rt, "engine"):
-            self.buckets.param_of_name = dict(model.named_parameters())
+            early_reduce = os.environ.get("B2T_DP_EARLY", "1") == "1"
+        arena = rt.grad_arena() if (rt is not None and hasattr(rt, "grad_arena")) else None
+        if arena is not None:
+            self.buckets = ArenaBuckets(arena, bucket_bytes, process_group, overlap, early=early_reduce)
             rt.engine.grad_sink = self.buckets.sink
-            rt.engine.grad_sync = self.buckets.sync_early
+            rt.engine.grad_sync = self.buckets.node_end
+        else:
+            self.buckets = GradientBuckets(list(model.parameters()), bucket_bytes, process_group, overlap)
 
     def attach_optimizer(self, optimizer: torch.optim.Optimizer) -> None:
+        """Belt and braces: finish() is idempotent, and backward passes driven outside autograd's engine (where the
+        end-of-backward callback cannot be queued) are still reduced before the step."""
         optimizer.register_step_pre_hook(lambda opt, args, kwargs: self.finish())
 
     def finish(self) -> None:

@@ -87,18 +87,23 @@ class Engine:
         done = getattr(self, "_emitted", None)
         if done is None:
             done = self._emitted = set()
-        new = [(k, v) for k, v in G.items() if k not in done and v is not None]
+        new = [k for k, v in G.items() if k not in done and v is not None]
         if new:
-            done.update(k for k, _ in new)
-            self.grad_sink(new)
+            if not self._arena_on:
+                raise RuntimeError("data-parallel gradient buckets reduce the flat gradient arena in place, but this backward "
+                                   "pass is not writing into it (parameters still hold a .grad from an earlier backward: "
+                                   "gradient accumulation is not supported under DataParallel; call optimizer.zero_grad())")
+            self.finalize_grads(G, only=new)       # a gradient is reduced where it lives: in its arena slot
+            done.update(new)
+            self.grad_sink([(k, G[k]) for k in new])
 
-    def sync_grads(self, G: Dict[str, Tensor]) -> None:
-        """End of an autograd node: the rest is handed over and every early all-reduce is written back before
-        autograd sees the tensors."""
+    def sync_grads(self, G: Dict[str, Tensor], prefix: str = "") -> None:
+        """End of an autograd node: the rest is handed over, and every bucket of this node that has not left yet is
+        launched (dist.ArenaBuckets.node_end)."""
         if self.grad_sink is None:
             return
         self.emit_grads(G)
-        self.grad_sync()
+        self.grad_sync(prefix)
         self._emitted = set()
 
     # ------------------------------------------------------------------------------------------
@@ -152,19 +157,90 @@ class Engine:
                  out_hi=hi, out_lo=lo, bias=bias, **kw)
         return out, pre, hi, lo
 
+    # ------------------------------------------------------------------------------------------
+    # gradient outputs: slots of the flat arena (flat.GradArena) when one is attached and the node's parameters hold
+    # no .grad yet (models sets _arena_on per autograd node), else fresh tensors exactly as before
+    # ------------------------------------------------------------------------------------------
+    grad_arena = None
+    _arena_on = False
+    arena_copies = 0        # gradients that had to be copied into their slot at the end of a node (diagnostic)
+
+    def _gout(self, name: str, shape, device, zero: bool) -> Tensor:
+        """Tensor the gradient of parameter `name` is written to.  Arena slots are zero at the start of the node."""
+        if self._arena_on:
+            v = self.grad_arena.view(name)
+            if v is not None:
+                return v if tuple(v.shape) == tuple(shape) else v.view(shape)
+        if zero:
+            return ops.zeros(tuple(shape), device=device)
+        return torch.empty(tuple(shape), dtype=torch.float32, device=device)
+
+    def _gout_cat(self, names, shape, device, zero: bool) -> Tensor:
+        """One tensor covering the gradients of several parameters produced by one kernel (row-stacked)."""
+        if self._arena_on:
+            v = self.grad_arena.view_cat(names, shape)
+            if v is not None:
+                return v
+        if zero:
+            return ops.zeros(tuple(shape), device=device)
+        return torch.empty(tuple(shape), dtype=torch.float32, device=device)
+
+    def finalize_grads(self, G: Dict[str, Tensor], only=None) -> None:
+        """End of an autograd node: every gradient that was not produced in its arena slot is copied there, so that
+        .grad tensors, all-reduce buckets and optimizer tables always see the slot."""
+        if not self._arena_on:
+            return
+        for k in (list(G) if only is None else only):
+            v = G[k]
+            if v is None:
+                continue
+            slot = self.grad_arena.view(k)
+            if slot is None or self.grad_arena.owns(k, v):
+                continue
+            slot.copy_(v.view(slot.shape) if v.is_contiguous() else v.reshape(slot.shape))
+            G[k] = slot
+            self.arena_copies += 1
+
+    @staticmethod
+    def grad_groups(be: BrainEncoderConfig, w2v: W2VConfig):
+        """Parameter names whose gradients one kernel writes as one row-stacked tensor (arena layout constraint)."""
+        groups = []
+        e = "brain_encoder.neural_decoder.encoder."
+        if be.bidirectional:
+            for l in range(be.gru_layers):
+                groups.append([e + f"gru.weight_ih_l{l}", e + f"gru.weight_ih_l{l}_reverse"])
+                groups.append([e + f"gru.bias_ih_l{l}", e + f"gru.bias_ih_l{l}_reverse"])
+        for i in range(w2v.layers):
+            if w2v.kind == "base":
+                a = f"w2v_encoder.wav2vec2.encoder.layers.{i}.attention."
+                groups.append([a + "q_proj.weight", a + "k_proj.weight", a + "v_proj.weight"])
+                groups.append([a + "q_proj.bias", a + "k_proj.bias", a + "v_proj.bias"])
+            else:
+                a = f"w2v_encoder.wav2vec2_conformer.encoder.layers.{i}.self_attn."
+                groups.append([a + "linear_q.weight", a + "linear_k.weight"])
+                groups.append([a + "linear_q.bias", a + "linear_k.bias", a + "linear_v.bias"])
+        return groups
+
     # frozen-w2v mode (unfreeze_strategy == "brain_encoder", b2t_gru_w2v_experiment.py:129-133): the optimizer never
     # reads the w2v weight gradients, so the encoder backward is data-gradient only (SURVEY.md §5.4); set by
     # models._EncoderFn.backward around the encoder's schedule, never during the brain encoder's
     _skip_wgrad = False
 
-    def _wgrad(self, dy_hi, dy_lo, x_hi, x_lo, N, K, M, out: Optional[Tensor] = None, alpha: float = 1.0) -> Optional[Tensor]:
-        """dW[N,K] = dY[M,N]^T . X[M,K]  (both operands row-major, contracted over rows)."""
+    def _wgrad(self, dy_hi, dy_lo, x_hi, x_lo, N, K, M, out: Optional[Tensor] = None, alpha: float = 1.0,
+               name=None) -> Optional[Tensor]:
+        """dW[N,K] = dY[M,N]^T . X[M,K]  (both operands row-major, contracted over rows).  `name`: the parameter
+        (or the list of row-stacked parameters) whose gradient this is -> written into its arena slot."""
         if self._skip_wgrad:
             return None
         kb = (M + 63) // 64
         sk = _split_k_for(N, K, kb)
         if out is None:
-            out = ops.zeros(N, K, device=dy_hi.device) if sk > 1 else torch.empty(N, K, dtype=torch.float32, device=dy_hi.device)
+            if isinstance(name, (list, tuple)):
+                out = self._gout_cat(name, (N, K), dy_hi.device, zero=sk > 1)
+            elif name is not None:
+                out = self._gout(name, (N, K), dy_hi.device, zero=sk > 1)
+            else:
+                out = ops.zeros(N, K, device=dy_hi.device) if sk > 1 else torch.empty(N, K, dtype=torch.float32, device=dy_hi.device)
         ops.gemm(ops.mnmajor(dy_hi, dy_lo), ops.mnmajor(x_hi, x_lo), m_per_batch=N, n=K, k=M, out_f32=out,
                  atomic=sk > 1, split_k=sk, alpha=alpha)
         return out
@@ -277,15 +353,15 @@ class Engine:
         for i in reversed(range(len(sizes) - 1)):
             st = S["fc"][i]
             wname = e + f"fc.{2 * i}.weight"
-            G[wname] = self._wgrad(d_hi, d_lo, st["a_hi"], st["a_lo"], sizes[i + 1], sizes[i], M)
+            G[wname] = self._wgrad(d_hi, d_lo, st["a_hi"], st["a_lo"], sizes[i + 1], sizes[i], M, name=wname)
             if d_f32 is not None:
-                db = ops.zeros(sizes[i + 1], device=dev)
+                db = self._gout(e + f"fc.{2 * i}.bias", (sizes[i + 1],), dev, zero=True)
                 ops.colsum(d_f32, db)
                 G[e + f"fc.{2 * i}.bias"] = db
             w_hl = self._w(P, wname)
             if i > 0:
                 # gradient w.r.t. the previous Linear's pre-activation, its column sums = that bias gradient
-                db_prev = ops.zeros(sizes[i], device=dev)
+                db_prev = self._gout(e + f"fc.{2 * (i - 1)}.bias", (sizes[i],), dev, zero=True)
                 _, d_hi, d_lo = self._dgrad(d_hi, d_lo, w_hl, M, sizes[i + 1], sizes[i], want_f32=False, want_split=True,
                                             aux=S["fc"][i - 1]["pre"], aux_mode=be.fc_act, colsum=db_prev)
                 G[e + f"fc.{2 * (i - 1)}.bias"] = db_prev
@@ -303,8 +379,9 @@ class Engine:
             for d, s in enumerate(sfx):
                 G[e + f"gru.weight_hh_l{l}{s}"] = self._wgrad(bw["dgh_hi"][d], None if bw["dgh_lo"] is None else bw["dgh_lo"][d],
                                                               fw["hprev_hi"][d],
-                                                              None if fw["hprev_lo"] is None else fw["hprev_lo"][d], 3 * H, H, M)
-            db_ih = ops.zeros(ndir * 3 * H, device=dev)
+                                                              None if fw["hprev_lo"] is None else fw["hprev_lo"][d], 3 * H, H, M,
+                                                              name=e + f"gru.weight_hh_l{l}{s}")
+            db_ih = self._gout_cat([e + f"gru.bias_ih_l{l}{s}" for s in sfx], (ndir * 3 * H,), dev, zero=True)
             ops.colsum(bw["dgi"], db_ih)
             dbn = ops.zeros(ndir * H, device=dev)
             ops.colsum(bw["dghn"].reshape(ndir * M, H), dbn[:H], rows=M)
@@ -318,7 +395,7 @@ class Engine:
             names = [e + f"gru.weight_ih_l{l}{s}" for s in sfx]
             if l > 0:
                 w_hl = self._w_cat(P, f"gru_ih_l{l}_cat", names)
-                dw = self._wgrad(bw["dgi_hi"], bw["dgi_lo"], fw["in_hi"], fw["in_lo"], ndir * 3 * H, ndir * H, M)
+                dw = self._wgrad(bw["dgi_hi"], bw["dgi_lo"], fw["in_hi"], fw["in_lo"], ndir * 3 * H, ndir * H, M, name=names)
                 for d, n_ in enumerate(names):
                     G[n_] = dw[d * 3 * H:(d + 1) * 3 * H]
                 dout, _, _ = self._dgrad(bw["dgi_hi"], bw["dgi_lo"], w_hl, M, ndir * 3 * H, ndir * H)
@@ -333,7 +410,7 @@ class Engine:
                 uv = ops.unfold_view(S["s_hi"], S["s_lo"], KL, ST, mn_major=True)
                 ops.gemm(ops.mnmajor(dgi_hi3, dgi_lo3), uv, m_per_batch=ndir * 3 * H, n=C * KL, k=Tp, out_f32=dwp,
                          k_spans_batches=True, atomic=True, split_k=sk)
-                dw = ops.unpermute_unfold_cols(dwp, C, KL)
+                dw = ops.unpermute_unfold_cols(dwp, C, KL, out=self._gout_cat(names, (ndir * 3 * H, C * KL), dev, zero=False))
                 for d, n_ in enumerate(names):
                     G[n_] = dw[d * 3 * H:(d + 1) * 3 * H]
                 # ds: dgrad folded through the overlapping unfold view (red.add)
@@ -341,10 +418,10 @@ class Engine:
                 ops.gemm(ops.kmajor(dgi_hi3, dgi_lo3), ops.mnmajor(w_hl[0], w_hl[1]), m_per_batch=Tp, batches=B, n=C * KL,
                          k=ndir * 3 * H, out_f32=ds, a_batched=True, atomic=True, ldc=ST * C, c_batch_stride=T * C)
         # ---- softsign + day affine ----
-        dbias = torch.zeros_like(P[pre + "day_bias"])
+        dbias = self._gout(pre + "day_bias", P[pre + "day_bias"].shape, dev, zero=True)
         dz_hi, dz_lo = ops.softsign_bwd(ds, S["z"], S["day"], dbias, three=three)
         G[pre + "day_bias"] = dbias
-        dW = torch.zeros_like(P[pre + "day_weights"])
+        dW = self._gout(pre + "day_weights", P[pre + "day_weights"].shape, dev, zero=True)
         ops.gemm(ops.mnmajor(S["y_hi"], S["y_lo"]), ops.mnmajor(dz_hi, dz_lo), m_per_batch=C, batches=B, n=C, k=T, out_f32=dW,
                  a_batched=True, b_batched=True, c_batch_idx=S["day"], c_batch_stride=C * C, atomic=True)
         G[pre + "day_weights"] = dW
@@ -398,7 +475,7 @@ class Engine:
         gk, v = self._posconv_params(P, q)
         wg_hi, wg_lo, norm = self.weights.get(q + "pos_conv", _ver(gk, v), lambda: ops.posconv_pack_weight(gk, v, G, three))
         dpre, dp_hi, dp_lo = ops.act_bwd(dsum, st["pre"], "gelu", three=three, want_f32=True, want_split=True)
-        db = ops.zeros(D, device=dev)
+        db = self._gout(q + "pos_conv_embed.conv.bias", (D,), dev, zero=True)
         ops.colsum(dpre, db)
         G_[q + "pos_conv_embed.conv.bias"] = db
         Tpad = st["Tpad"]
@@ -438,12 +515,12 @@ class Engine:
             uv.d1 = T
             ops.gemm(a_k.as_mn(), uv, m_per_batch=Cg, n=K * CP, k=T, out_f32=dwg[wsl], k_spans_batches=True, atomic=True,
                      split_k=max(1, min(8, B)))
-        dg, dv = ops.posconv_weight_bwd(dwg, gk, v, norm)
         k0 = q + "pos_conv_embed.conv.parametrizations.weight.original0"
-        if k0 in P:
-            G_[k0], G_[q + "pos_conv_embed.conv.parametrizations.weight.original1"] = dg, dv
-        else:
-            G_[q + "pos_conv_embed.conv.weight_g"], G_[q + "pos_conv_embed.conv.weight_v"] = dg, dv
+        kg, kv = (k0, q + "pos_conv_embed.conv.parametrizations.weight.original1") if k0 in P else \
+            (q + "pos_conv_embed.conv.weight_g", q + "pos_conv_embed.conv.weight_v")
+        dg, dv = ops.posconv_weight_bwd(dwg, gk, v, norm, dg_out=self._gout(kg, gk.shape, dev, zero=False),
+                                        dv_out=self._gout(kv, v.shape, dev, zero=False))
+        G_[kg], G_[kv] = dg, dv
         return dx
 
     def _posconv_batch_idx(self, B: int, T: int, G: int, dev):
@@ -558,13 +635,13 @@ class Engine:
         p_h, p_att, p_act = S["p"]
         seed = S["seed"]
 
-        def zeros(n):
-            return ops.zeros(n, device=dev)
+        def gz(name, n):
+            return self._gout(name, (n,), dev, zero=True)
 
         ds_ws = torch.empty(B, NH, T, T, dtype=torch.float32, device=dev)
         if cfg.stable_ln:
             mf, rf, hin = S["lnf"]
-            G[q + "layer_norm.weight"], G[q + "layer_norm.bias"] = zeros(D), zeros(D)
+            G[q + "layer_norm.weight"], G[q + "layer_norm.bias"] = gz(q + "layer_norm.weight", D), gz(q + "layer_norm.bias", D)
             dh, _, _ = ops.layernorm_bwd(dh, hin, P[q + "layer_norm.weight"], mf, rf, G[q + "layer_norm.weight"],
                                          G[q + "layer_norm.bias"], three=three, want_split=False)
         for i in reversed(range(cfg.layers)):
@@ -575,7 +652,7 @@ class Engine:
             Lq = q + f"layers.{i}."
             s2, s3, s4, s1 = (_mix(seed, 1000 + 10 * i + k) for k in (2, 3, 4, 1))
             # ---- FFN block ----
-            db2 = zeros(D)
+            db2 = gz(Lq + "feed_forward.output_dense.bias", D)
             if cfg.stable_ln:
                 # u2 = u + drop(FFN(LN(u)));  dh is d(u2)
                 du2 = dh
@@ -583,25 +660,29 @@ class Engine:
                 ops.colsum(ops.dropout(du2, p_h, s4, three=three)[0] if p_h > 0 else du2, db2)
             else:
                 m3, r3 = st["ln3"]
-                G[Lq + "final_layer_norm.weight"], G[Lq + "final_layer_norm.bias"] = zeros(D), zeros(D)
+                G[Lq + "final_layer_norm.weight"], G[Lq + "final_layer_norm.bias"] = (gz(Lq + "final_layer_norm.weight", D),
+                                                                                      gz(Lq + "final_layer_norm.bias", D))
                 du2, g_hi, g_lo = ops.layernorm_bwd(dh, st["u2"], P[Lq + "final_layer_norm.weight"], m3, r3,
                                                     G[Lq + "final_layer_norm.weight"], G[Lq + "final_layer_norm.bias"], db2,
                                                     three=three, br_drop_p=p_h, br_seed=s4)
             G[Lq + "feed_forward.output_dense.bias"] = db2
-            G[Lq + "feed_forward.output_dense.weight"] = self._wgrad(g_hi, g_lo, st["f_hi"], st["f_lo"], D, F, M)
-            db1 = zeros(F)
+            G[Lq + "feed_forward.output_dense.weight"] = self._wgrad(g_hi, g_lo, st["f_hi"], st["f_lo"], D, F, M,
+                                                                     name=Lq + "feed_forward.output_dense.weight")
+            db1 = gz(Lq + "feed_forward.intermediate_dense.bias", F)
             _, dp_hi, dp_lo = self._dgrad(g_hi, g_lo, self._w(P, Lq + "feed_forward.output_dense.weight"), M, D, F,
                                           want_f32=False, want_split=True, aux=st["pre1"], aux_mode=cfg.hidden_act,
                                           drop_p=p_act, drop_seed=s3, colsum=db1)
             G[Lq + "feed_forward.intermediate_dense.bias"] = db1
-            G[Lq + "feed_forward.intermediate_dense.weight"] = self._wgrad(dp_hi, dp_lo, st["h1_hi"], st["h1_lo"], F, D, M)
+            G[Lq + "feed_forward.intermediate_dense.weight"] = self._wgrad(dp_hi, dp_lo, st["h1_hi"], st["h1_lo"], F, D, M,
+                                                                           name=Lq + "feed_forward.intermediate_dense.weight")
             w1 = self._w(P, Lq + "feed_forward.intermediate_dense.weight")
             m2, r2 = st["ln2"]
-            dbo = zeros(D)
+            dbo = gz(Lq + "attention.out_proj.bias", D)
             if cfg.stable_ln:
                 # d(LN2 out) -> LN2 backward on u, plus the residual du2
                 dl, _, _ = self._dgrad(dp_hi, dp_lo, w1, M, F, D)
-                G[Lq + "final_layer_norm.weight"], G[Lq + "final_layer_norm.bias"] = zeros(D), zeros(D)
+                G[Lq + "final_layer_norm.weight"], G[Lq + "final_layer_norm.bias"] = (gz(Lq + "final_layer_norm.weight", D),
+                                                                                      gz(Lq + "final_layer_norm.bias", D))
                 dxl, _, _ = ops.layernorm_bwd(dl, st["u"], P[Lq + "final_layer_norm.weight"], m2, r2,
                                               G[Lq + "final_layer_norm.weight"], G[Lq + "final_layer_norm.bias"], three=three,
                                               want_split=False)
@@ -610,18 +691,20 @@ class Engine:
                 ops.colsum(ops.dropout(du, p_h, s2, three=three)[0] if p_h > 0 else du, dbo)
             else:
                 dh1, _, _ = self._dgrad(dp_hi, dp_lo, w1, M, F, D, residual=du2)
-                G[Lq + "layer_norm.weight"], G[Lq + "layer_norm.bias"] = zeros(D), zeros(D)
+                G[Lq + "layer_norm.weight"], G[Lq + "layer_norm.bias"] = gz(Lq + "layer_norm.weight", D), gz(Lq + "layer_norm.bias", D)
                 du, b_hi, b_lo = ops.layernorm_bwd(dh1, st["u"], P[Lq + "layer_norm.weight"], m2, r2, G[Lq + "layer_norm.weight"],
                                                    G[Lq + "layer_norm.bias"], dbo, three=three, br_drop_p=p_h, br_seed=s2)
             # ---- attention block ----
             G[Lq + "attention.out_proj.bias"] = dbo
-            G[Lq + "attention.out_proj.weight"] = self._wgrad(b_hi, b_lo, st["c_hi"], st["c_lo"], D, D, M)
+            G[Lq + "attention.out_proj.weight"] = self._wgrad(b_hi, b_lo, st["c_hi"], st["c_lo"], D, D, M,
+                                                              name=Lq + "attention.out_proj.weight")
             dctx, _, _ = self._dgrad(b_hi, b_lo, self._w(P, Lq + "attention.out_proj.weight"), M, D, D)
             dqkv, dq_hi, dq_lo = ops.attention_bwd(st["qkv"], st["probs"], dctx, ds_ws, B, T, NH, hd, three=three,
                                                    drop_p=p_att, seed=s1)
-            dbq = zeros(3 * D)
+            qkv_names = [Lq + f"attention.{nm}" for nm in ("q_proj", "k_proj", "v_proj")]
+            dbq = self._gout_cat([n_ + ".bias" for n_ in qkv_names], (3 * D,), dev, zero=True)
             ops.colsum(dqkv, dbq)
-            dwq = self._wgrad(dq_hi, dq_lo, st["in_hi"], st["in_lo"], 3 * D, D, M)
+            dwq = self._wgrad(dq_hi, dq_lo, st["in_hi"], st["in_lo"], 3 * D, D, M, name=[n_ + ".weight" for n_ in qkv_names])
             for j, nm in enumerate(("q_proj", "k_proj", "v_proj")):
                 G[Lq + f"attention.{nm}.weight"] = None if dwq is None else dwq[j * D:(j + 1) * D]
                 G[Lq + f"attention.{nm}.bias"] = dbq[j * D:(j + 1) * D]
@@ -630,7 +713,7 @@ class Engine:
             if cfg.stable_ln:
                 dl, _, _ = self._dgrad(dq_hi, dq_lo, wqkv, M, 3 * D, D)
                 m1, r1 = st["ln1"]
-                G[Lq + "layer_norm.weight"], G[Lq + "layer_norm.bias"] = zeros(D), zeros(D)
+                G[Lq + "layer_norm.weight"], G[Lq + "layer_norm.bias"] = gz(Lq + "layer_norm.weight", D), gz(Lq + "layer_norm.bias", D)
                 dxl, _, _ = ops.layernorm_bwd(dl, st["ln1_in"], P[Lq + "layer_norm.weight"], m1, r1, G[Lq + "layer_norm.weight"],
                                               G[Lq + "layer_norm.bias"], three=three, want_split=False)
                 dh = ops.axpby(dxl, du)
@@ -639,7 +722,7 @@ class Engine:
         # ---- encoder input: [LN ->] dropout, positional conv ----
         if not cfg.stable_ln:
             mean, rstd = S["ln0"]
-            G[q + "layer_norm.weight"], G[q + "layer_norm.bias"] = zeros(D), zeros(D)
+            G[q + "layer_norm.weight"], G[q + "layer_norm.bias"] = gz(q + "layer_norm.weight", D), gz(q + "layer_norm.bias", D)
             dxs, _, _ = ops.layernorm_bwd(dh, S["xs"], P[q + "layer_norm.weight"], mean, rstd, G[q + "layer_norm.weight"],
                                           G[q + "layer_norm.bias"], three=three, want_split=False, out_drop_p=p_h,
                                           out_seed=_mix(seed, 200))
@@ -664,10 +747,11 @@ class Engine:
         M = B * T
         d2 = dlogits.reshape(M, cfg.vocab)
         _, d_hi, d_lo = ops.dropout(d2, 0.0, 0, three=self.three, want_f32=False, want_split=True)
-        db = ops.zeros(cfg.vocab, device=d2.device)
+        db = self._gout("w2v_encoder.lm_head.bias", (cfg.vocab,), d2.device, zero=True)
         ops.colsum(d2, db)
         G["w2v_encoder.lm_head.bias"] = db
-        G["w2v_encoder.lm_head.weight"] = self._wgrad(d_hi, d_lo, S["hd_hi"], S["hd_lo"], cfg.vocab, cfg.hidden, M)
+        G["w2v_encoder.lm_head.weight"] = self._wgrad(d_hi, d_lo, S["hd_hi"], S["hd_lo"], cfg.vocab, cfg.hidden, M,
+                                                      name="w2v_encoder.lm_head.weight")
         dh, _, _ = self._dgrad(d_hi, d_lo, self._w(P, "w2v_encoder.lm_head.weight"), M, cfg.vocab, cfg.hidden,
                                drop_p=S["p_f"], drop_seed=S["seed"])
         return dh

@@ -141,6 +141,44 @@ class _Runtime:
         # frozen-w2v training (unfreeze_strategy == "brain_encoder"): skip the w2v weight gradients nobody reads
         # (set by compat's _create_model swap and by bench.py --workload frozen)
         self.skip_w2v_wgrad = False
+        # flat gradient arena (flat.GradArena): built lazily from the owning top-level model's parameters
+        self.use_arena = True
+        self._owner = None          # weakref to the W2V*BrainEncoderModel
+        self._arena = None
+
+    def grad_arena(self):
+        """The model's flat gradient buffer (None for a stand-alone brain encoder or when switched off)."""
+        if not self.use_arena or self._owner is None:
+            return None
+        if self._arena is not None:       # invalidated by _TopModel._apply (.cuda() / .to() / dtype changes)
+            return self._arena
+        owner = self._owner()
+        if owner is None:
+            return None
+        named = [(n, p) for n, p in owner.named_parameters() if p.requires_grad]
+        if not named or (not named[0][1].is_cuda and not _EMULATED):
+            return None
+        from .flat import GradArena
+        self._arena = GradArena(named, _engine.Engine.grad_groups(self.engine.be, self.engine.w2v), named[0][1].device)
+        self.engine.grad_arena = self._arena
+        return self._arena
+
+    def begin_node(self, prefix: str) -> bool:
+        """Start of an autograd node's backward: switch the engine to the arena slots of `prefix` (zeroed with one
+        memset) when none of those parameters holds a .grad yet."""
+        eng = self.engine
+        arena = self.grad_arena()
+        on = arena is not None and arena.free_for(prefix)
+        eng.grad_arena, eng._arena_on = arena, on
+        if on:
+            arena.zero_prefix(prefix)
+        return on
+
+    def end_node(self, G, prefix: str) -> None:
+        eng = self.engine
+        eng.finalize_grads(G)
+        eng.sync_grads(G, prefix)
+        eng._arena_on = False
 
     def next_seed(self) -> int:
         self.step += 1
@@ -173,8 +211,12 @@ class _BrainFn(torch.autograd.Function):
         G: Dict[str, Tensor] = {}
         d = dfeats.reshape(-1, dfeats.shape[-1]).contiguous()
         with _ops.zero_arena(("brain", id(ctx.rt)), d.device):
-            ctx.rt.engine.brain_backward(ctx.P, ctx.saved, d, G)
-            ctx.rt.engine.sync_grads(G)
+            ctx.rt.begin_node("brain_encoder.")
+            try:
+                ctx.rt.engine.brain_backward(ctx.P, ctx.saved, d, G)
+                ctx.rt.end_node(G, "brain_encoder.")
+            finally:
+                ctx.rt.engine._arena_on = False
         return (None, None, None, None, None, None) + tuple(G.get(n) for n in ctx.names)
 
 
@@ -203,6 +245,7 @@ class _EncoderFn(torch.autograd.Function):
         skip = ctx.rt.skip_w2v_wgrad
         with _ops.zero_arena(("w2v", id(ctx.rt)), dlogits.device):
             eng._skip_wgrad = skip
+            ctx.rt.begin_node("w2v_encoder.")
             try:
                 dh = eng.head_backward(ctx.P, ctx.Sh, dlogits.contiguous(), G)
                 if dhidden is not None:
@@ -212,11 +255,12 @@ class _EncoderFn(torch.autograd.Function):
                 else:
                     from . import conformer
                     dfeats = conformer.backward(eng, ctx.P, ctx.Se, dh, G)
+                if skip:
+                    G = {}      # data gradient only: no w2v parameter receives a .grad
+                ctx.rt.end_node(G, "w2v_encoder.")
             finally:
                 eng._skip_wgrad = False
-            if skip:
-                G = {}      # data gradient only: no w2v parameter receives a .grad
-            eng.sync_grads(G)
+                eng._arena_on = False
         B, T = ctx.Sh["B"], ctx.Sh["T"]
         return (None, None, None, None, None, dfeats.view(B, T, -1)) + tuple(G.get(n) for n in ctx.names)
 
@@ -361,7 +405,7 @@ class B2P2TModel(B2TModel):
     def _features(self, batch, seed: Optional[int] = None) -> Tensor:
         rt = self._runtime()
         x = batch.input
-        if not x.is_cuda:
+        if not x.is_cuda and not _EMULATED:
             raise RuntimeError("wav2vec2forbrain_b200 runs on CUDA (sm_100a) only: call batch.cuda() first")
         day = batch.day_idxs.to(device=x.device, dtype=torch.int32)
         tensors = _named_tensors(self, self._prefix)
@@ -558,10 +602,26 @@ def _load_pretrained_if_present(module: nn.Module, wav2vec_checkpoint: str) -> b
     return False
 
 
+# True only inside the CPU test-suite, which substitutes tests/abi_emulator.py for `engine.ops` to check the host-side
+# schedule, the arena and the data-parallel logic without a GPU; the product never sets it (and without the emulator a
+# CPU tensor fails in the first kernel wrapper anyway)
+_EMULATED = False
+
+
 class _TopModel(B2TModel):
+    def _apply(self, fn, *a, **kw):
+        out = super()._apply(fn, *a, **kw)
+        rt = getattr(self, "_rt", None)
+        if rt is not None:
+            rt._arena = None            # parameters may have moved: the arena is rebuilt on the next backward
+            rt.engine.grad_arena = None
+        return out
+
     def _attach(self, brain_encoder: B2P2TModel, w2v_cfg: W2VConfig, precision: str):
         be_cfg = _be_config_from_args(brain_encoder.config, brain_encoder._ckpt)
         rt = _Runtime(be_cfg, w2v_cfg, precision)
+        import weakref
+        rt._owner = weakref.ref(self)
         brain_encoder._rt = rt
         self.w2v_encoder._rt = rt
         self._rt = rt

@@ -94,9 +94,10 @@ def permute_unfold_cols(w: Tensor, C: int, KL: int, three: bool = True):
     return hi, lo
 
 
-def unpermute_unfold_cols(g: Tensor, C: int, KL: int) -> Tensor:
+def unpermute_unfold_cols(g: Tensor, C: int, KL: int, out: Optional[Tensor] = None) -> Tensor:
     """gradient in k*C+c column order -> reference order c*KL+k (fp32)."""
-    out = torch.empty_like(g)
+    out = torch.empty_like(g) if out is None else out
+    assert out.is_contiguous() and out.shape == g.shape
     check(lib().b2t_permute_unfold_cols(ptr(g), ptr(None), ptr(None), ptr(out), c_int64(g.shape[0]), c_int(C), c_int(KL),
                                         c_int(1), stream()), "b2t_permute_unfold_cols")
     _count()
@@ -482,10 +483,11 @@ def posconv_unpack_dx(dxg: Tensor, dx: Tensor, B: int, T: int, G: int, pad_left:
     _count()
 
 
-def posconv_weight_bwd(dwg: Tensor, g: Tensor, v: Tensor, norm: Tensor):
+def posconv_weight_bwd(dwg: Tensor, g: Tensor, v: Tensor, norm: Tensor, dg_out: Optional[Tensor] = None,
+                       dv_out: Optional[Tensor] = None):
     D, Cg, K = v.shape
-    dg = torch.empty_like(g)
-    dv = torch.empty_like(v)
+    dg = torch.empty_like(g) if dg_out is None else dg_out
+    dv = torch.empty_like(v) if dv_out is None else dv_out
     check(lib().b2t_posconv_weight_bwd(ptr(dwg), ptr(g), ptr(v), ptr(norm), ptr(dg), ptr(dv), c_int(D), c_int(Cg), c_int(K),
                                        stream()), "b2t_posconv_weight_bwd")
     _count()
@@ -571,11 +573,12 @@ def bn_silu_fwd(x: Tensor, stats: Optional[Tensor], gamma: Tensor, beta: Tensor,
     return y_hi, y_lo, mean, rstd
 
 
-def bn_silu_bwd_stats(ds: Tensor, x: Tensor, mean: Tensor, rstd: Tensor, gamma: Tensor, beta: Tensor):
-    """-> (dgamma [D], dbeta [D]) of BatchNorm behind the SiLU."""
+def bn_silu_bwd_stats(ds: Tensor, x: Tensor, mean: Tensor, rstd: Tensor, gamma: Tensor, beta: Tensor,
+                      dgamma_out: Optional[Tensor] = None, dbeta_out: Optional[Tensor] = None):
+    """-> (dgamma [D], dbeta [D]) of BatchNorm behind the SiLU (accumulated into the zero-initialised *_out if given)."""
     M, D = x.shape
-    dgamma = zeros(D, device=x.device)
-    dbeta = zeros(D, device=x.device)
+    dgamma = zeros(D, device=x.device) if dgamma_out is None else dgamma_out
+    dbeta = zeros(D, device=x.device) if dbeta_out is None else dbeta_out
     check(lib().b2t_bn_silu_bwd_stats(ptr(ds), ptr(x), ptr(mean), ptr(rstd), ptr(gamma), ptr(beta), ptr(dgamma), ptr(dbeta),
                                       c_int64(M), c_int(D), stream()), "b2t_bn_silu_bwd_stats")
     _count()
@@ -583,12 +586,13 @@ def bn_silu_bwd_stats(ds: Tensor, x: Tensor, mean: Tensor, rstd: Tensor, gamma: 
 
 
 def glu_dwconv_bwd(ds: Tensor, x: Tensor, g: Tensor, w: Tensor, mean: Tensor, rstd: Tensor, gamma: Tensor, beta: Tensor,
-                   dgamma: Tensor, dbeta: Tensor, B: int, T: int, training: bool, three: bool = True):
+                   dgamma: Tensor, dbeta: Tensor, B: int, T: int, training: bool, three: bool = True,
+                   dw_out: Optional[Tensor] = None):
     """-> (dg_hi, dg_lo [B*T, 2D], dw [D, 1, K]): gradient w.r.t. the pointwise_conv1 output and the depthwise weight."""
     D = x.shape[1]
     K = w.shape[-1]
     dg_hi, dg_lo = _bf16_like(g), _bf16_like(g, three)
-    dw = zeros(tuple(w.shape), device=w.device)
+    dw = zeros(tuple(w.shape), device=w.device) if dw_out is None else dw_out
     check(lib().b2t_glu_dwconv_bwd(ptr(ds), ptr(x), ptr(g), ptr(w), ptr(mean), ptr(rstd), ptr(gamma), ptr(beta), ptr(dgamma),
                                    ptr(dbeta), ptr(dg_hi), ptr(dg_lo), ptr(dw), c_int(B), c_int(T), c_int(D), c_int(K),
                                    c_int(1 if training else 0), stream()), "b2t_glu_dwconv_bwd")

@@ -33,9 +33,9 @@ _TENSOR_DT = np.dtype([("p", "<u8"), ("g", "<u8"), ("m", "<u8"), ("v", "<u8"), (
 
 class AdamGroup(ctypes.Structure):
     """Mirror of b2t_adam_group (include/b2t_sm100.h)."""
-    _fields_ = [("lr", ctypes.c_float), ("beta1", ctypes.c_float), ("beta2", ctypes.c_float), ("eps", ctypes.c_float),
-                ("weight_decay", ctypes.c_float), ("bias_c1", ctypes.c_float), ("bias_c2_sqrt", ctypes.c_float),
-                ("pad_", ctypes.c_int32)]
+    _fields_ = [("beta2", ctypes.c_float), ("eps", ctypes.c_float), ("weight_decay", ctypes.c_float),
+                ("one_minus_beta1", ctypes.c_float), ("one_minus_beta2", ctypes.c_float), ("step_size", ctypes.c_float),
+                ("bias_c2_sqrt", ctypes.c_float), ("pad_", ctypes.c_int32)]
 
 
 class _Table:
@@ -114,8 +114,9 @@ class FusedAdam(torch.optim.Optimizer):
                 hi = hyper.get(hk)
                 if hi is None:
                     hi = hyper[hk] = len(hlist)
-                    hlist.append(AdamGroup(group["lr"], b1, b2, group["eps"], group["weight_decay"], 1.0 - b1 ** t,
-                                           math.sqrt(1.0 - b2 ** t), 0))
+                    # derived scalars in double (Python floats), rounded to fp32 once — torch's _single_tensor_adam
+                    hlist.append(AdamGroup(b2, group["eps"], group["weight_decay"], 1.0 - b1, 1.0 - b2,
+                                           group["lr"] / (1.0 - b1 ** t), math.sqrt(1.0 - b2 ** t), 0))
                 device = p.device
                 rows.append((p.data_ptr(), g.data_ptr(), st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr(), p.numel(), hi))
                 sig.append((rows[-1][0], rows[-1][1], hi))
