@@ -197,6 +197,27 @@ def test_ctc_matches_torch(B, T, S, ragged):
     assert rel(grad, x.grad) < 1e-4      # fp32 log-space sums vs the fp64 reference
 
 
+def test_ctc_label_outside_vocabulary_is_contained():
+    """A label >= V or < 0 inside target_len (wrong tokenizer vocabulary, a -100 padding value) must not read or add
+    out of bounds in the kernel's shared-memory tables: that trial reports an infinite loss (0 under zero_infinity) and
+    gets no gradient; the other trials are unaffected."""
+    ops = _ops()
+    g = torch.Generator().manual_seed(21)
+    B, T, S = 4, 40, 6
+    logits = torch.randn(B, T, 32, generator=g).cuda()
+    targets = torch.randint(1, 32, (B, S), generator=g)
+    good = targets.clone()
+    targets[1, 2] = 77
+    targets[3, 0] = -100
+    il, tl = torch.full((B,), T).int(), torch.full((B,), S)
+    loss, nll, grad = ops.ctc_fwd_bwd(logits, targets.cuda(), il.cuda(), tl.cuda())
+    loss_g, nll_g, grad_g = ops.ctc_fwd_bwd(logits, good.cuda(), il.cuda(), tl.cuda())
+    assert nll[1].item() == 0.0 and nll[3].item() == 0.0 and grad[1].abs().sum().item() == 0.0 and grad[3].abs().sum().item() == 0.0
+    for b in (0, 2):
+        assert torch.equal(nll[b], nll_g[b]) and torch.equal(grad[b], grad_g[b])
+    assert torch.isfinite(loss)
+
+
 def test_greedy_decode():
     from oracle import b2t_oracle as O
     ops = _ops()

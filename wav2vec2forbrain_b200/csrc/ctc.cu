@@ -52,12 +52,21 @@ __global__ void __launch_bounds__(32) ctc_kernel(const float* __restrict__ logit
     // lattice bookkeeping for this lane's KS states
     int lab[KS];
     bool skip_a[KS], skip_b[KS], valid[KS];
+    bool bad_label = false;
 #pragma unroll
     for (int i = 0; i < KS; ++i) {
         const int s = lane * KS + i;
         valid[i] = s < L;
         const int tgt_i = (s - 1) >> 1;
         lab[i] = (valid[i] && (s & 1)) ? (int)targets[(long)b * s_max + tgt_i] : 0;
+        // a label outside the vocabulary (wrong tokenizer, a -100 padding value inside target_len) would index the
+        // shared-memory log-prob / occupancy tables out of bounds: clamp it for memory safety and treat the trial as
+        // infeasible below (ATen's CTCLoss raises here; a kernel cannot, so the trial reports an infinite loss — 0 under
+        // zero_infinity — and gets no gradient)
+        if (lab[i] < 0 || lab[i] >= V) {
+            bad_label = true;
+            lab[i] = 0;
+        }
         // transitions s-2 -> s and s -> s+2 are allowed between different non-blank labels
         skip_a[i] = valid[i] && (s & 1) && s >= 3 && targets[(long)b * s_max + tgt_i] != targets[(long)b * s_max + tgt_i - 1];
         skip_b[i] = valid[i] && (s & 1) && (s + 2 < L) &&
@@ -107,6 +116,7 @@ __global__ void __launch_bounds__(32) ctc_kernel(const float* __restrict__ logit
         if (m != NEG) ll = m + logf(warp_sum(mine == NEG ? 0.0f : expf(mine - m)));
         nll = -ll;
     }
+    if (__any_sync(0xffffffffu, bad_label)) nll = CUDART_INF_F;
     const bool infinite = !(nll < CUDART_INF_F);   // inf or nan
     const float denom = (float)(S > 0 ? S : 1) * (float)B;
     if (lane == 0) {

@@ -428,6 +428,7 @@ def ctc_fwd_bwd(logits: Tensor, targets: Tensor, input_lens: Tensor, target_lens
     grad = torch.empty_like(logits) if want_grad else None
     assert targets.dtype == torch.int64 and target_lens.dtype == torch.int64 and input_lens.dtype == torch.int32
     assert targets.is_contiguous() and logits.stride(2) == 1
+    assert V <= 32, "the CTC kernel keeps one vocabulary entry per lane (V <= 32)"
     check(lib().b2t_ctc_fwd_bwd(ptr(logits), c_int64(logits.stride(1)), c_int64(logits.stride(0)), ptr(targets), c_int(S),
                                 ptr(input_lens), ptr(target_lens), ptr(ws), ptr(nll), ptr(loss), ptr(grad), c_int(B),
                                 c_int(T), c_int(V), c_int(1), stream()), "b2t_ctc_fwd_bwd")
