@@ -68,20 +68,25 @@ struct Item {
     int split, batch, m_blk, n_blk, kb0, kb1, mode, n_contrib, owner;
 };
 
+// `idx` / `G`: this CTA's position among, and the number of, scheduling units of the grid - CTAs for cta_group::1,
+// CTA pairs for cta_group::2 (both CTAs of a pair walk the same item list; the pair's tile is 2 x BM rows, the
+// CTA of cluster rank r owns row block m_blk = 2 * (pair row block) + r, kept in it.m_blk).
 struct Sched {
     const KParams& p;
+    const int idx, G, cg, rank;
     int item;
     long long u, u_end;
-    __device__ __forceinline__ explicit Sched(const KParams& p_) : p(p_), item((int)blockIdx.x), u(0), u_end(0) {
+    __device__ __forceinline__ Sched(const KParams& p_, int cg_, int rank_)
+        : p(p_), idx((int)blockIdx.x / cg_), G((int)gridDim.x / cg_), cg(cg_), rank(rank_), item((int)blockIdx.x / cg_), u(0), u_end(0) {
         if (p.stream_k) {
-            u = (long long)blockIdx.x * p.sk_units / gridDim.x;
-            u_end = (long long)(blockIdx.x + 1) * p.sk_units / gridDim.x;
+            u = (long long)idx * p.sk_units / G;
+            u_end = (long long)(idx + 1) * p.sk_units / G;
         }
     }
     __device__ __forceinline__ void decode_tile(int t, Item& it) const {
         it.n_blk = t % p.n_tiles;
         t /= p.n_tiles;
-        it.m_blk = t % p.m_tiles;
+        it.m_blk = (t % p.m_tiles) * cg + rank;   // p.m_tiles counts pair row blocks when cg == 2
         it.batch = t / p.m_tiles;
     }
     __device__ __forceinline__ bool next(Item& it) {
@@ -93,11 +98,11 @@ struct Sched {
             it.kb0 = (int)(((long long)it.split * p.num_k_blocks) / p.split_k);
             it.kb1 = (int)(((long long)(it.split + 1) * p.num_k_blocks) / p.split_k);
             it.mode = 0, it.n_contrib = 0, it.owner = 0;
-            item += gridDim.x;
+            item += G;
             return true;
         }
         if (u >= u_end) return false;
-        const long long KB = p.num_k_blocks, G = gridDim.x;
+        const long long KB = p.num_k_blocks;
         const long long t = u / KB, t0 = t * KB;
         const long long e = u_end < t0 + KB ? u_end : t0 + KB;
         it.split = 0;
@@ -109,7 +114,7 @@ struct Sched {
             it.mode = 0;
         } else if (it.kb0 == 0) {
             it.mode = 2;   // CTA holding unit x is ((x + 1) * G - 1) / units
-            it.n_contrib = (int)(((t0 + KB) * G - 1) / p.sk_units) - (int)blockIdx.x;
+            it.n_contrib = (int)(((t0 + KB) * G - 1) / p.sk_units) - idx;
         } else {
             it.mode = 1;
             it.owner = (int)(((t0 + 1) * G - 1) / p.sk_units);
@@ -158,6 +163,48 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map
         ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
         : "memory");
 }
+// ---- cta_group::2 (CTA pair) forms ----
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrive on a barrier of another CTA of the cluster (address from mapa)
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
+}
+// the load lands in THIS CTA's shared memory, its bytes are counted on the pair leader's barrier
+__device__ __forceinline__ void tma_load_3d_pair(uint32_t dst, const CUtensorMap* map, uint32_t cluster_bar, int c0, int c1,
+                                                 int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(dst), "l"(map), "r"(cluster_bar), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+__device__ __forceinline__ void tc_commit_pair(uint32_t bar) {   // arrives on `bar` of BOTH CTAs of the pair
+    asm volatile(
+        "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+        "h"((uint16_t)3)
+        : "memory");
+}
+__device__ __forceinline__ void tc_mma_bf16_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                                 uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
 __device__ __forceinline__ bool elect_one() {
     uint32_t pred;
     asm volatile(
@@ -213,10 +260,15 @@ __host__ __device__ constexpr uint32_t make_idesc(int m, int n, bool a_mn, bool 
            ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
-template <int NTERMS, int BN>
+// CG = 2: the tile is 2*BM x BN, computed by a CTA pair with tcgen05 cta_group::2 (UMMA M = 256).  Each CTA stages its
+// own BM rows of A and HALF of the B tile (BN/2 rows) and holds its BM x BN half of the accumulator in its own TMEM,
+// so per MMA a CTA's shared memory is read for 4 KB of A + BN/2 * 32 B of B instead of 4 KB + BN * 32 B: at BN = 256
+// that is 8 KB per 128 tensor clocks (50 % of the 128 B/clk port) where the single-CTA 128x128 tile needs 8 KB per 64.
+template <int NTERMS, int BN, int CG>
 struct Cfg {
     static constexpr int A_BYTES = BM * BK * 2;
-    static constexpr int B_BYTES = BN * BK * 2;
+    static constexpr int B_ROWS = BN / CG;
+    static constexpr int B_BYTES = B_ROWS * BK * 2;
     static constexpr int STAGE_BYTES = (NTERMS == 3 ? 2 : 1) * (A_BYTES + B_BYTES);
     static constexpr int EPI_BYTES = NUM_EPI_WARPS * 32 * 32 * 4;   // one 32x32 fp32 transpose buffer per epilogue warp
     static constexpr int AUX_BYTES = 1024;   // barriers + tmem pointer
@@ -646,16 +698,19 @@ __device__ __forceinline__ void epi_chunk32(const KParams& p, const uint32_t F, 
     __syncwarp();   // the buffer is rewritten by the next chunk
 }
 
-template <int NTERMS, bool A_MN, bool B_MN, int BN>
+template <int NTERMS, bool A_MN, bool B_MN, int BN, int CG>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ CUtensorMap tmAl,
                const __grid_constant__ CUtensorMap tmBh, const __grid_constant__ CUtensorMap tmBl, const KParams p) {
-    using C = Cfg<NTERMS, BN>;
+    using C = Cfg<NTERMS, BN, CG>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
     const uint32_t bar_base = smem_base + C::STAGES * C::STAGE_BYTES + C::EPI_BYTES;
     // barrier layout: full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2], then tmem ptr
+    // CG == 2: every CTA of the pair has the whole set at the same offsets; `full` and `tmem_empty` are used in the
+    // leader (cluster rank 0) only - it issues the MMAs - while `empty` and `tmem_full` are signalled in both CTAs by
+    // multicast tcgen05.commit.
     auto full_bar = [&](int s) { return bar_base + 8u * s; };
     auto empty_bar = [&](int s) { return bar_base + 8u * (C::STAGES + s); };
     auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * C::STAGES + s); };
@@ -666,6 +721,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
+    const int rank = CG == 2 ? (int)cluster_ctarank() : 0;
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&tmAh) : "memory");
@@ -680,18 +736,28 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(tfull_bar(s), 1);
-            mbar_init(tempty_bar(s), NUM_EPI_WARPS);
+            mbar_init(tempty_bar(s), CG * NUM_EPI_WARPS);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_ptr_addr),
-                     "r"((uint32_t)C::TMEM_COLS)
-                     : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        if (CG == 2) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_ptr_addr),
+                         "r"((uint32_t)C::TMEM_COLS)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_ptr_addr),
+                         "r"((uint32_t)C::TMEM_COLS)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     tc_fence_before();
-    __syncthreads();
+    if (CG == 2)
+        cluster_sync_all();   // the peer's barriers are initialised before any remote arrive / complete_tx reaches them
+    else
+        __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr_gen;
 
@@ -700,24 +766,32 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            Sched sch(p);
+            Sched sch(p, CG, rank);
             Item it;
+            auto tma_load = [&](uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2) {
+                if (CG == 2)
+                    tma_load_3d_pair(dst, map, bar, c0, c1, c2);
+                else
+                    tma_load_3d(dst, map, bar, c0, c1, c2);
+            };
             while (sch.next(it)) {
                 const int batch = it.batch, m_blk = it.m_blk, n_blk = it.n_blk, kb0 = it.kb0, kb1 = it.kb1;
                 const int bbatch = p.b_batch_idx ? p.b_batch_idx[batch] : (p.b_batched ? batch : 0);
                 const int abatch = p.a_batched ? batch : 0;
+                const int n_row0 = n_blk * BN + rank * C::B_ROWS;   // this CTA's rows of the B tile
                 for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(empty_bar(stage), phase ^ 1u);
-                    const uint32_t fb = full_bar(stage);
+                    // CG == 2: both CTAs' bytes are counted on the leader's barrier (the MMA issuer waits there)
+                    const uint32_t fb = CG == 2 ? mapa_u32(full_bar(stage), 0) : full_bar(stage);
                     if (p.debug & 4) {
-                        mbar_arrive(fb);
+                        if (rank == 0) mbar_arrive(full_bar(stage));
                         if (++stage == C::STAGES) {
                             stage = 0;
                             phase ^= 1u;
                         }
                         continue;
                     }
-                    mbar_expect_tx(fb, (uint32_t)C::STAGE_BYTES);
+                    if (rank == 0) mbar_expect_tx(full_bar(stage), (uint32_t)(CG * C::STAGE_BYTES));
                     const uint32_t sA = smem_base + stage * C::STAGE_BYTES;
                     const uint32_t sB = sA + (NTERMS == 3 ? 2 : 1) * C::A_BYTES;
                     int krow = kb * BK, kslice = 0;
@@ -730,20 +804,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
                         const CUtensorMap* ma = t == 0 ? &tmAh : &tmAl;
                         const CUtensorMap* mb = t == 0 ? &tmBh : &tmBl;
                         if (!A_MN) {
-                            tma_load_3d(sA + t * C::A_BYTES, ma, fb, kb * BK, m_blk * BM, abatch);
+                            tma_load(sA + t * C::A_BYTES, ma, fb, kb * BK, m_blk * BM, abatch);
                         } else {
 #pragma unroll
                             for (int i = 0; i < BM / 64; ++i)
-                                tma_load_3d(sA + t * C::A_BYTES + i * (BK * 128), ma, fb, m_blk * BM + i * 64, krow,
-                                            p.k_spans_batches ? kslice : abatch);
+                                tma_load(sA + t * C::A_BYTES + i * (BK * 128), ma, fb, m_blk * BM + i * 64, krow,
+                                         p.k_spans_batches ? kslice : abatch);
                         }
                         if (!B_MN) {
-                            tma_load_3d(sB + t * C::B_BYTES, mb, fb, kb * BK, n_blk * BN, bbatch);
+                            tma_load(sB + t * C::B_BYTES, mb, fb, kb * BK, n_row0, bbatch);
                         } else {
 #pragma unroll
-                            for (int i = 0; i < BN / 64; ++i)
-                                tma_load_3d(sB + t * C::B_BYTES + i * (BK * 128), mb, fb, n_blk * BN + i * 64, krow,
-                                            p.k_spans_batches ? kslice : bbatch);
+                            for (int i = 0; i < C::B_ROWS / 64; ++i)
+                                tma_load(sB + t * C::B_BYTES + i * (BK * 128), mb, fb, n_row0 + i * 64, krow,
+                                         p.k_spans_batches ? kslice : bbatch);
                         }
                     }
                     if (++stage == C::STAGES) {
@@ -753,13 +827,25 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
                 }
             }
         }
-    } else if (warp == 1) {
-        // ================================ MMA issuer ==================================
+    } else if (warp == 1 && rank == 0) {
+        // ================================ MMA issuer (pair leader only when CG == 2) ==================================
         // The WHOLE warp walks the loops so that every address / descriptor stays warp-uniform (uniform
         // registers feed UTCHMMA directly); one elected lane issues the tcgen05 instructions.  With the loop
         // inside `if (lane == 0)` ptxas rebuilt each descriptor in vector registers and moved it over with
         // R2UR per MMA: ~230 instructions per k-block, slower than the 12 MMAs they issue (ncu, round 1).
-        constexpr uint32_t idesc = make_idesc(BM, BN, A_MN, B_MN);
+        constexpr uint32_t idesc = make_idesc(CG * BM, BN, A_MN, B_MN);
+        auto mma = [&](uint32_t d, uint64_t da, uint64_t db, uint32_t acc_flag) {
+            if (CG == 2)
+                tc_mma_bf16_pair(d, da, db, idesc, acc_flag);
+            else
+                tc_mma_bf16(d, da, db, idesc, acc_flag);
+        };
+        auto commit = [&](uint32_t bar) {
+            if (CG == 2)
+                tc_commit_pair(bar);
+            else
+                tc_commit(bar);
+        };
         // K-major SW128: 8-row groups 1024 B apart (SBO), k-step = +32 B inside the swizzle row
         // MN-major SW128: 64-element MN atoms BK*128 B apart (LBO), 8 k-rows = 1024 B (SBO),
         //                 k-step of 16 rows = +2048 B
@@ -773,7 +859,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
         int stage = 0;
         uint32_t phase = 0;
         int local_iter = 0;
-        Sched sch(p);
+        Sched sch(p, CG, rank);
         Item it;
         for (; sch.next(it); ++local_iter) {
             const int kb0 = it.kb0, kb1 = it.kb1;
@@ -791,14 +877,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
                     for (int k = 0; k < ((p.debug & 2) ? 0 : BK / UMMA_K); ++k) {
                         const uint64_t dAh = dA + (uint64_t)((k * A_KSTEP) >> 4);
                         const uint64_t dBh = dB + (uint64_t)((k * B_KSTEP) >> 4);
-                        tc_mma_bf16(tmem_d, dAh, dBh, idesc, k == 0 ? accumulate : 1u);
+                        mma(tmem_d, dAh, dBh, k == 0 ? accumulate : 1u);
                         if (NTERMS == 3) {
-                            tc_mma_bf16(tmem_d, dAh, dBh + (uint64_t)(C::B_BYTES >> 4), idesc, 1);
-                            tc_mma_bf16(tmem_d, dAh + (uint64_t)(C::A_BYTES >> 4), dBh, idesc, 1);
+                            mma(tmem_d, dAh, dBh + (uint64_t)(C::B_BYTES >> 4), 1);
+                            mma(tmem_d, dAh + (uint64_t)(C::A_BYTES >> 4), dBh, 1);
                         }
                     }
-                    tc_commit(empty_bar(stage));
-                    if (kb == kb1 - 1) tc_commit(tfull_bar(acc));
+                    commit(empty_bar(stage));
+                    if (kb == kb1 - 1) commit(tfull_bar(acc));
                 }
                 __syncwarp();
                 accumulate = 1;
@@ -812,7 +898,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
                 }
             }
         }
-    } else {
+    } else if (warp >= 2) {
         // ================================ epilogue ====================================
         // 8 warps: TMEM lane quadrant q = warp & 3 (hardware restriction), the two warps of a
         // quadrant take alternate 32-column chunks.  A thread owns ONE output row (its TMEM lane)
@@ -822,8 +908,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
         int local_iter = 0;
         uint32_t F = p.flags;
         asm volatile("" : "+r"(F));   // pin the stage bits in a register (else ptxas re-reads the constant bank per test)
-        Sched sch(p);
+        Sched sch(p, CG, rank);
         Item it;
+        const uint32_t tempty_remote0 = CG == 2 ? mapa_u32(tempty_bar(0), 0) : 0u;   // the leader's tmem_empty barriers
         float* const epi_buf =
             reinterpret_cast<float*>(smem_gen + C::STAGES * C::STAGE_BYTES) + (warp - 2) * EPI_CHUNK_FLOATS;
         float* const ws_mine = p.sk_ws + (size_t)blockIdx.x * (BM * BN);
@@ -875,7 +962,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
                     // this warp's share of the accumulator is in registers: hand the TMEM stage back
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(tempty_bar(acc));
+                    if (lane == 0) {
+                        if (CG == 2)
+                            mbar_arrive_cluster(tempty_remote0 + 8u * acc);
+                        else
+                            mbar_arrive(tempty_bar(acc));
+                    }
                 }
                 // workspace layout [chunk c][row in tile][32]: a thread's partial row segment is one 128-byte line
                 const int ws_off = (c * BM + q * 32 + lane) * 32;
@@ -890,7 +982,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
                 if (col_base >= p.n || (p.debug & 1)) continue;   // warp-uniform
                 if (it.mode == 2) {
                     for (int j = 1; j <= it.n_contrib; ++j) {
-                        const float* w = ws_mine + (size_t)j * (BM * BN) + ws_off;
+                        const float* w = ws_mine + (size_t)j * CG * (BM * BN) + ws_off;
 #pragma unroll
                         for (int g = 0; g < 8; ++g) {
                             const float4 t = __ldcg(reinterpret_cast<const float4*>(w + 4 * g));
@@ -906,7 +998,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
             if (it.mode == 1) {
                 __threadfence();
                 __syncwarp();
-                if (lane == 0) red_release_gpu_add(p.sk_flags + it.owner, 1);
+                if (lane == 0) red_release_gpu_add(p.sk_flags + it.owner * CG + rank, 1);
             } else if (it.mode == 2) {
                 // every epilogue warp is past its wait: clear the flag for the next launch on this stream
                 asm volatile("bar.sync 1, %0;" ::"n"(NUM_EPI_WARPS * 32) : "memory");
@@ -916,11 +1008,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
     }
 
     tc_fence_before();
-    __syncthreads();
+    if (CG == 2)
+        cluster_sync_all();   // neither CTA leaves (or frees TMEM) while its peer's MMAs / arrives can still touch it
+    else
+        __syncthreads();
     if (warp == 1) {
         __syncwarp();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)C::TMEM_COLS)
-                     : "memory");
+        if (CG == 2)
+            asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)C::TMEM_COLS)
+                         : "memory");
+        else
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)C::TMEM_COLS)
+                         : "memory");
     }
 }
 
