@@ -89,6 +89,9 @@ typedef struct {
     void*    sk_workspace;
     int64_t  sk_workspace_bytes;
     int32_t  stream_k;
+    /* 0 = auto, 1 = single-CTA tiles (128 x block_n), 2 = CTA pair (tcgen05 cta_group::2, 256 x 256 tiles: each CTA
+     * stages its own 128 rows of A and half of the B tile, UMMA M = 256) */
+    int32_t  cta_group;
 } b2t_gemm_args;
 
 int b2t_gemm(const b2t_gemm_args* args, b2t_stream stream);

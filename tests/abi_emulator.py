@@ -118,7 +118,7 @@ def _dact(a, mode):
 def gemm(a, b, *, m_per_batch, n, k, batches=1, out_f32=None, out_pre=None, out_hi=None, out_lo=None, ldc=None,
          c_batch_stride=None, bias=None, residual=None, aux=None, colsum=None, act=None, aux_mode=None, atomic=False,
          split_k=1, alpha=1.0, k_spans_batches=False, a_batched=False, b_batched=False, b_batch_idx=None,
-         c_batch_idx=None, block_n=0, drop_p=0.0, drop_seed=0, bias_batch_stride=0, out_scale=1.0, stream_k=0):
+         c_batch_idx=None, block_n=0, drop_p=0.0, drop_seed=0, bias_batch_stride=0, out_scale=1.0, stream_k=0, cta_group=0):
     global LAUNCHES
     LAUNCHES += 1
     ldc = n if ldc is None else ldc

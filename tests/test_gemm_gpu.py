@@ -228,3 +228,91 @@ def test_stream_k_wgrad_shape(stream_k):
     out = torch.full((m, n), float("nan"), device="cuda")
     ops.gemm(ops.mnmajor(ah, al), ops.mnmajor(bh, bl), m_per_batch=m, n=n, k=k, out_f32=out, stream_k=stream_k)
     assert rel(out, a.double() @ b.double().t()) < 2e-5
+
+
+# ------------------------------------------------------------------------------------------------------
+# cta_group::2 (CTA pair, 256 x 256 tiles): same contracts as the single-CTA tiles
+# ------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (True, False), (False, True), (True, True)])
+@pytest.mark.parametrize("three", [False, True])
+@pytest.mark.parametrize("m,n,k", [(256, 256, 64), (392, 520, 200), (1000, 768, 520), (3776, 1024, 1024)])
+def test_pair_all_major_combinations(a_mn, b_mn, three, m, n, k):
+    """odd row-block counts (the pair's second CTA has no rows), ragged N (zero-filled B rows), ragged K"""
+    ops = _ops()
+    a, b = rnd(m, k, seed=3), rnd(n, k, seed=4)
+    ah, al = ops.split(a, three, transpose=a_mn)
+    bh, bl = ops.split(b, three, transpose=b_mn)
+    A = ops.mnmajor(ah, al) if a_mn else ops.kmajor(ah, al)
+    Bm = ops.mnmajor(bh, bl) if b_mn else ops.kmajor(bh, bl)
+    out = torch.full((m, n), float("nan"), device="cuda")
+    ops.gemm(A, Bm, m_per_batch=m, n=n, k=k, out_f32=out, cta_group=2)
+    ref = a.double() @ b.double().t() if three else \
+        (ah.double().t() if a_mn else ah.double()) @ (bh.double() if b_mn else bh.double().t())
+    assert rel(out, ref) < (2e-5 if three else 2e-6)
+    # and the single-CTA kernel on the same operands gives the same sums up to accumulation order
+    out1 = torch.empty_like(out)
+    ops.gemm(A, Bm, m_per_batch=m, n=n, k=k, out_f32=out1, cta_group=1)
+    assert rel(out, out1) < 1e-6
+
+
+@pytest.mark.parametrize("stream_k", [-1, 1])
+@pytest.mark.parametrize("m,n,k", [(260, 328, 256), (1000, 768, 520), (3776, 1024, 1024), (3776, 4096, 256)])
+def test_pair_full_epilogue(stream_k, m, n, k):
+    """every fused epilogue stage on a CTA pair, whole-tile and stream-K schedules; twice (flags left clean)"""
+    ops = _ops()
+    a, b = rnd(m, k, seed=5, scale=0.3), rnd(n, k, seed=6, scale=0.3)
+    bias, res = rnd(n, seed=7), rnd(m, n, seed=8)
+    ah, al = ops.split(a)
+    bh, bl = ops.split(b)
+    z = 0.5 * (a.double() @ b.double().t()) + bias.double()
+    ref = torch.nn.functional.gelu(z) + res.double()
+    for _ in range(2):
+        out = torch.full((m, n), float("nan"), device="cuda")
+        pre = torch.empty(m, n, device="cuda")
+        hi = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
+        lo = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
+        colsum = torch.zeros(n, device="cuda")
+        ops.gemm(ops.kmajor(ah, al), ops.kmajor(bh, bl), m_per_batch=m, n=n, k=k, out_f32=out, out_pre=pre, out_hi=hi,
+                 out_lo=lo, bias=bias, residual=res, colsum=colsum, act="gelu", alpha=0.5, stream_k=stream_k, cta_group=2)
+        assert rel(pre, z) < 2e-5
+        assert rel(out, ref) < 2e-5
+        assert rel(hi.double() + lo.double(), ref) < 3e-5
+        assert rel(colsum, ref.sum(0)) < 1e-4
+
+
+def test_pair_split_k_atomic_and_dropout_mask():
+    ops = _ops()
+    m, n, k = 1024, 512, 3776
+    a, b = rnd(m, k, seed=12), rnd(n, k, seed=13)
+    ah, al = ops.split(a, transpose=True)
+    bh, bl = ops.split(b, transpose=True)
+    out = torch.ones(m, n, device="cuda")
+    ops.gemm(ops.mnmajor(ah, al), ops.mnmajor(bh, bl), m_per_batch=m, n=n, k=k, out_f32=out, atomic=True, split_k=5, cta_group=2)
+    assert rel(out, a.double() @ b.double().t() + 1.0) < 2e-5
+    # the dropout mask is a function of (seed, output offset) only: pair and single-CTA tiles agree element by element
+    m, n, k = 520, 768, 128
+    a, b = rnd(m, k, seed=14), rnd(n, k, seed=15)
+    ah, al = ops.split(a)
+    bh, bl = ops.split(b)
+    o1, o2 = torch.empty(m, n, device="cuda"), torch.empty(m, n, device="cuda")
+    for o, cg in ((o1, 1), (o2, 2)):
+        ops.gemm(ops.kmajor(ah, al), ops.kmajor(bh, bl), m_per_batch=m, n=n, k=k, out_f32=o, drop_p=0.3, drop_seed=99, cta_group=cg)
+    assert torch.equal(o1 == 0, o2 == 0)
+    assert 0.25 < (o2 == 0).float().mean().item() < 0.35
+    assert rel(o2, o1) < 1e-6
+
+
+def test_pair_batched_operands():
+    """batches > 1: tile rows never cross a batch, the second CTA of a batch's last pair is empty (T = 300 -> 3 row blocks)"""
+    ops = _ops()
+    Bn, T, D, days = 5, 300, 256, 7
+    y = rnd(Bn, T, D, seed=14)
+    w = rnd(days, D, D, seed=15, scale=0.1)
+    day = torch.tensor([3, 0, 6, 3, 1], device="cuda", dtype=torch.int32)
+    yh, yl = ops.split(y)
+    wh, wl = ops.split(w)
+    out = torch.empty(Bn, T, D, device="cuda")
+    ops.gemm(ops.kmajor(yh, yl), ops.mnmajor(wh, wl), m_per_batch=T, batches=Bn, n=D, k=D, out_f32=out,
+             a_batched=True, b_batch_idx=day, act="softsign", cta_group=2)
+    ref = torch.nn.functional.softsign(torch.einsum("btd,bdk->btk", y.double(), w.double()[day.long()]))
+    assert rel(out, ref) < 2e-5

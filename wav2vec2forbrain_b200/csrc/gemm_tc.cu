@@ -55,7 +55,9 @@ struct KParams {
     int m_tiles, n_tiles, total_items;
     // stream-K: the tiles' k-blocks form one line of `sk_units` units cut into gridDim.x equal ranges
     int stream_k;
+    int sk_tile0;      // tiles [0, sk_tile0) run as whole tiles, tiles [sk_tile0, tiles) form the stream-K line
     long long sk_units;
+    int sk_G;          // units (CTAs / pairs) the line is cut over = min(grid units, sk_units): every one holds >= 1 k-block
     float* sk_ws;      // [gridDim.x][BM * BN] fp32 partial accumulators
     int* sk_flags;     // [gridDim.x] arrivals of partials at the tile's owner CTA (self-cleaning)
 };
@@ -78,9 +80,9 @@ struct Sched {
     long long u, u_end;
     __device__ __forceinline__ Sched(const KParams& p_, int cg_, int rank_)
         : p(p_), idx((int)blockIdx.x / cg_), G((int)gridDim.x / cg_), cg(cg_), rank(rank_), item((int)blockIdx.x / cg_), u(0), u_end(0) {
-        if (p.stream_k) {
-            u = (long long)idx * p.sk_units / G;
-            u_end = (long long)(idx + 1) * p.sk_units / G;
+        if (p.stream_k && idx < p.sk_G) {
+            u = (long long)idx * p.sk_units / p.sk_G;
+            u_end = (long long)(idx + 1) * p.sk_units / p.sk_G;
         }
     }
     __device__ __forceinline__ void decode_tile(int t, Item& it) const {
@@ -101,25 +103,35 @@ struct Sched {
             item += G;
             return true;
         }
-        if (u >= u_end) return false;
-        const long long KB = p.num_k_blocks;
-        const long long t = u / KB, t0 = t * KB;
-        const long long e = u_end < t0 + KB ? u_end : t0 + KB;
+        // Hybrid schedule: the last (tiles mod G) tiles would be a mostly empty wave, so THEIR k-blocks are cut into G
+        // equal ranges (stream-K) and done first - the owners' fix-up epilogues then run under the MMAs of the whole
+        // tiles that follow - and the remaining multiple of G tiles run as whole tiles, one per unit and wave.
         it.split = 0;
-        decode_tile((int)t, it);
-        it.kb0 = (int)(u - t0);
-        it.kb1 = (int)(e - t0);
-        it.n_contrib = 0, it.owner = 0;
-        if (it.kb0 == 0 && it.kb1 == KB) {
-            it.mode = 0;
-        } else if (it.kb0 == 0) {
-            it.mode = 2;   // CTA holding unit x is ((x + 1) * G - 1) / units
-            it.n_contrib = (int)(((t0 + KB) * G - 1) / p.sk_units) - idx;
-        } else {
-            it.mode = 1;
-            it.owner = (int)(((t0 + 1) * G - 1) / p.sk_units);
+        if (u < u_end) {
+            const long long KB = p.num_k_blocks;
+            const long long t = u / KB, t0 = t * KB;
+            const long long e = u_end < t0 + KB ? u_end : t0 + KB;
+            decode_tile(p.sk_tile0 + (int)t, it);
+            it.kb0 = (int)(u - t0);
+            it.kb1 = (int)(e - t0);
+            it.n_contrib = 0, it.owner = 0;
+            if (it.kb0 == 0 && it.kb1 == KB) {
+                it.mode = 0;
+            } else if (it.kb0 == 0) {
+                it.mode = 2;   // the unit holding k-block unit x is ((x + 1) * G - 1) / units
+                it.n_contrib = (int)(((t0 + KB) * p.sk_G - 1) / p.sk_units) - idx;
+            } else {
+                it.mode = 1;
+                it.owner = (int)(((t0 + 1) * p.sk_G - 1) / p.sk_units);
+            }
+            u = e;
+            return true;
         }
-        u = e;
+        if (item >= p.sk_tile0) return false;
+        decode_tile(item, it);
+        it.kb0 = 0, it.kb1 = p.num_k_blocks;
+        it.mode = 0, it.n_contrib = 0, it.owner = 0;
+        item += G;
         return true;
     }
 };
@@ -934,7 +946,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
             }
             mbar_wait(tfull_bar(acc), acc_phase);
             tc_fence_after();
-            if (it.mode == 2) {
+            if (it.mode == 2 && !(p.debug & (8 | 16))) {
                 // stream-K owner: the partials of the following CTAs were written at the START of their ranges
                 if (lane == 0) {
                     const int want = NUM_EPI_WARPS * it.n_contrib;
@@ -969,23 +981,26 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
                             mbar_arrive(tempty_bar(acc));
                     }
                 }
-                // workspace layout [chunk c][row in tile][32]: a thread's partial row segment is one 128-byte line
-                const int ws_off = (c * BM + q * 32 + lane) * 32;
+                // workspace layout [chunk c][quadrant q][j][lane][4]: private to the (contributor, owner) thread pair that
+                // shares (warp, lane), so it is chosen for the memory system - every warp instruction moves 512
+                // contiguous bytes
+                const int ws_off = ((c * 4 + q) * 8 * 32 + lane) * 4;
                 if (it.mode == 1) {
+                    if (p.debug & (8 | 32)) continue;
 #pragma unroll
                     for (int j = 0; j < 8; ++j)
-                        __stcg(reinterpret_cast<float4*>(ws_mine + ws_off + 4 * j),
+                        __stcg(reinterpret_cast<float4*>(ws_mine + ws_off + 128 * j),
                                make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]));
                     continue;
                 }
                 const int col_base = n_blk * BN + c * 32;
                 if (col_base >= p.n || (p.debug & 1)) continue;   // warp-uniform
-                if (it.mode == 2) {
+                if (it.mode == 2 && !(p.debug & (8 | 32))) {
                     for (int j = 1; j <= it.n_contrib; ++j) {
                         const float* w = ws_mine + (size_t)j * CG * (BM * BN) + ws_off;
 #pragma unroll
                         for (int g = 0; g < 8; ++g) {
-                            const float4 t = __ldcg(reinterpret_cast<const float4*>(w + 4 * g));
+                            const float4 t = __ldcg(reinterpret_cast<const float4*>(w + 128 * g));
                             v[4 * g] += t.x, v[4 * g + 1] += t.y, v[4 * g + 2] += t.z, v[4 * g + 3] += t.w;
                         }
                     }
@@ -995,7 +1010,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
                 else
                     epi_chunk32<false>(p, F, epi_buf, v, lane, m_blk * BM + q * 32, base_off, col_base, bias_ptr);
             }
-            if (it.mode == 1) {
+            if (p.debug & 8) {
+            } else if (it.mode == 1) {
                 __threadfence();
                 __syncwarp();
                 if (lane == 0) red_release_gpu_add(p.sk_flags + it.owner * CG + rank, 1);
@@ -1042,9 +1058,62 @@ EncodeTiledFn get_encode_fn() {
     return fn;
 }
 
+// A tensor map is a pure function of (pointer, extents, strides, box): a training step re-issues the same few hundred
+// GEMMs on the same buffers every iteration (caching allocator), so the encoded maps are kept in a direct-mapped
+// table instead of calling cuTensorMapEncodeTiled four times per launch.
+struct MapKey {
+    const void* ptr;
+    int64_t d0, d1, d2, s1, s2;
+    int64_t box1;
+    bool operator==(const MapKey& o) const {
+        return ptr == o.ptr && d0 == o.d0 && d1 == o.d1 && d2 == o.d2 && s1 == o.s1 && s2 == o.s2 && box1 == o.box1;
+    }
+};
+struct MapSlot {
+    MapKey key;
+    CUtensorMap map;
+    bool used;
+};
+constexpr int MAP_CACHE_SLOTS = 8192;
+MapSlot* map_cache() {
+    static thread_local MapSlot* tab = nullptr;   // per host thread: no locking on the launch path
+    if (!tab) tab = (MapSlot*)calloc(MAP_CACHE_SLOTS, sizeof(MapSlot));
+    return tab;
+}
+inline uint64_t mix64(uint64_t x) {
+    x ^= x >> 33, x *= 0xff51afd7ed558ccdULL, x ^= x >> 33, x *= 0xc4ceb9fe1a85ec53ULL, x ^= x >> 33;
+    return x;
+}
+
+int encode_map(CUtensorMap* map, const void* ptr, int64_t d0, int64_t d1, int64_t d2, int64_t s1, int64_t s2, int box1,
+               const char* what);
+
 // 3-D bf16 map, d0 contiguous, box {64, box1, 1}, 128B swizzle, zero OOB fill
 int make_map(CUtensorMap* map, const void* ptr, int64_t d0, int64_t d1, int64_t d2, int64_t s1, int64_t s2, int box1,
              const char* what) {
+    MapSlot* tab = map_cache();
+    const MapKey key{ptr, d0, d1, d2, s1, s2, box1};
+    if (tab) {
+        uint64_t h = mix64((uint64_t)(uintptr_t)ptr ^ mix64((uint64_t)d1 * 0x9e3779b97f4a7c15ULL + (uint64_t)s1) ^
+                           mix64((uint64_t)d0 + 31 * (uint64_t)d2 + 977 * (uint64_t)s2 + 7919 * (uint64_t)box1));
+        MapSlot& sl = tab[h & (MAP_CACHE_SLOTS - 1)];
+        if (sl.used && sl.key == key) {
+            *map = sl.map;
+            return 0;
+        }
+        const int rc = encode_map(map, ptr, d0, d1, d2, s1, s2, box1, what);
+        if (rc == 0) {
+            sl.key = key;
+            sl.map = *map;
+            sl.used = true;
+        }
+        return rc;
+    }
+    return encode_map(map, ptr, d0, d1, d2, s1, s2, box1, what);
+}
+
+int encode_map(CUtensorMap* map, const void* ptr, int64_t d0, int64_t d1, int64_t d2, int64_t s1, int64_t s2, int box1,
+               const char* what) {
     EncodeTiledFn fn = get_encode_fn();
     B2T_CHECK_ARG(fn != nullptr, "b2t_gemm: cuTensorMapEncodeTiled entry point not found");
     B2T_CHECK_ARG(((uintptr_t)ptr & 15) == 0, "b2t_gemm: operand %s not 16-byte aligned", what);
@@ -1080,12 +1149,12 @@ int num_sms() {
     return (g_sm_limit > 0 && g_sm_limit < n) ? g_sm_limit : n;
 }
 
-template <int NTERMS, bool A_MN, bool B_MN, int BN>
+template <int NTERMS, bool A_MN, bool B_MN, int BN, int CG>
 int launch(const b2t_gemm_args* a, const KParams& kp, cudaStream_t stream) {
-    using C = Cfg<NTERMS, BN>;
+    using C = Cfg<NTERMS, BN, CG>;
     CUtensorMap mAh, mAl, mBh, mBl;
     const int a_box1 = A_MN ? BK : BM;
-    const int b_box1 = B_MN ? BK : BN;
+    const int b_box1 = B_MN ? BK : C::B_ROWS;
     int rc;
     if ((rc = make_map(&mAh, a->a_hi, a->a_d0, a->a_d1, a->a_d2, a->a_s1, a->a_s2, a_box1, "a_hi"))) return rc;
     if ((rc = make_map(&mBh, a->b_hi, a->b_d0, a->b_d1, a->b_d2, a->b_s1, a->b_s2, b_box1, "b_hi"))) return rc;
@@ -1096,36 +1165,60 @@ int launch(const b2t_gemm_args* a, const KParams& kp, cudaStream_t stream) {
         mAl = mAh;
         mBl = mBh;
     }
-    auto kern = gemm_tc_kernel<NTERMS, A_MN, B_MN, BN>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        B2T_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
-        attr_set = true;
-    }
-    int grid = kp.total_items < num_sms() ? kp.total_items : num_sms();
-    KParams kq = kp;
-    if (kq.stream_k) {
-        // one line of tiles x k-blocks units cut into `grid` equal ranges; every CTA is resident (grid <= #SMs, 1 CTA/SM)
-        grid = kq.sk_units < num_sms() ? (int)kq.sk_units : num_sms();
-        const size_t need = SK_FLAG_BYTES + (size_t)grid * BM * BN * sizeof(float);
-        if (need > (size_t)a->sk_workspace_bytes) {
-            kq.stream_k = 0;   // workspace too small for this tile shape: plain persistent schedule
-            grid = kp.total_items < num_sms() ? kp.total_items : num_sms();
+    auto kern = gemm_tc_kernel<NTERMS, A_MN, B_MN, BN, CG>;
+    {
+        // per device: the attribute belongs to the function in ONE device's context
+        static bool attr_set[64] = {};
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+            B2T_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+            if (dev >= 0 && dev < 64) attr_set[dev] = true;
         }
     }
-    kern<<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(mAh, mAl, mBh, mBl, kq);
+    const int units_max = num_sms() / CG;   // CTAs (CG == 1) or CTA pairs (CG == 2) of the persistent grid
+    int units = kp.total_items < units_max ? kp.total_items : units_max;
+    KParams kq = kp;
+    if (kq.stream_k) {
+        // the stream-K line is cut into one range per unit of the FULL grid (the host computed sk_tile0 for it); every
+        // CTA is resident (grid <= #SMs, 1 CTA/SM), which the owners' waits rely on
+        units = units_max;
+        const size_t need = SK_FLAG_BYTES + (size_t)units * CG * BM * BN * sizeof(float);
+        if (need > (size_t)a->sk_workspace_bytes || units * CG * (int)sizeof(int) > SK_FLAG_BYTES) {
+            kq.stream_k = 0;   // workspace too small for this tile shape: plain persistent schedule
+            units = kp.total_items < units_max ? kp.total_items : units_max;
+        }
+    }
+    if (CG == 1) {
+        kern<<<units, NUM_THREADS, C::SMEM_BYTES, stream>>>(mAh, mAl, mBh, mBl, kq);
+    } else {
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.gridDim = dim3((unsigned)(units * CG), 1, 1);
+        cfg.blockDim = dim3(NUM_THREADS, 1, 1);
+        cfg.dynamicSmemBytes = C::SMEM_BYTES;
+        cfg.stream = stream;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = CG;
+        at[0].val.clusterDim.y = 1;
+        at[0].val.clusterDim.z = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        B2T_CUDA(cudaLaunchKernelEx(&cfg, kern, mAh, mAl, mBh, mBl, kq));
+    }
     B2T_CHECK_LAUNCH("b2t_gemm");
     return 0;
 }
 
-template <int NTERMS, int BN>
+template <int NTERMS, int BN, int CG>
 int dispatch_major(const b2t_gemm_args* a, const KParams& kp, cudaStream_t s) {
     if (a->a_mn_major) {
-        if (a->b_mn_major) return launch<NTERMS, true, true, BN>(a, kp, s);
-        return launch<NTERMS, true, false, BN>(a, kp, s);
+        if (a->b_mn_major) return launch<NTERMS, true, true, BN, CG>(a, kp, s);
+        return launch<NTERMS, true, false, BN, CG>(a, kp, s);
     }
-    if (a->b_mn_major) return launch<NTERMS, false, true, BN>(a, kp, s);
-    return launch<NTERMS, false, false, BN>(a, kp, s);
+    if (a->b_mn_major) return launch<NTERMS, false, true, BN, CG>(a, kp, s);
+    return launch<NTERMS, false, false, BN, CG>(a, kp, s);
 }
 
 }  // namespace
@@ -1216,7 +1309,26 @@ extern "C" int b2t_gemm(const b2t_gemm_args* a, b2t_stream stream_) {
         }
         kp.debug = dbg;
     }
+    // Tile shape.  cta_group::2 (a CTA pair on 256 x 256 tiles, see Cfg) is what feeds the tensor pipe without hitting the
+    // shared-memory port, so it is taken whenever the problem has 256-row blocks to give it; single-CTA tiles
+    // (128 x 64/128/256) remain for narrow outputs and short batches (lm_head, day affine, unfold / pos-conv views).
     int bn = a->block_n;
+    int cg = a->cta_group;
+    B2T_CHECK_ARG(cg == 0 || cg == 1 || cg == 2, "b2t_gemm: cta_group must be 0 (auto), 1 or 2");
+    {
+        static int force_cg = -1;
+        if (force_cg < 0) {
+            const char* e = getenv("B2T_GEMM_CG");
+            force_cg = e ? atoi(e) : 0;
+        }
+        if (cg == 0 && (force_cg == 1 || force_cg == 2)) cg = force_cg;
+    }
+    if (cg == 0) cg = (bn == 0 || bn == 256) && a->n >= 256 && a->n % 128 == 0 && a->m_per_batch > BM && num_sms() >= 2 ? 2 : 1;
+    if (cg == 2 && (kp.debug & 7)) cg = 1;   // the component-timing switches exist for the single-CTA kernel only
+    if (cg == 2) {
+        B2T_CHECK_ARG(bn == 0 || bn == 256, "b2t_gemm: cta_group 2 uses block_n 256");
+        bn = 256;
+    }
     if (bn == 0) {
         bn = a->n <= 64 ? 64 : 128;
         // 128 x 256 tiles move 25 % fewer operand bytes per MMA through shared memory, but halve the tile count:
@@ -1230,37 +1342,43 @@ extern "C" int b2t_gemm(const b2t_gemm_args* a, b2t_stream stream_) {
         }
     }
     B2T_CHECK_ARG(bn == 64 || bn == 128 || bn == 256, "b2t_gemm: block_n must be 64, 128 or 256");
-    kp.m_tiles = ceil_div_i(a->m_per_batch, BM);
+    kp.m_tiles = ceil_div_i(ceil_div_i(a->m_per_batch, BM), cg);   // row blocks of one scheduling unit (CTA or CTA pair)
     kp.n_tiles = ceil_div_i(a->n, bn);
     kp.total_items = kp.m_tiles * kp.n_tiles * kp.batches * a->split_k;
 
-    // stream-K (needs a caller-owned workspace): replaces whole-tile waves (148 SMs rarely divide the tile
-    // count: M = 3776 x N = 1024 is 240 tiles = 1.62 waves) and split-K + red.add by equal k-block ranges per CTA.
+    // stream-K (needs a caller-owned workspace).  148 SMs rarely divide the tile count (M = 3776 x N = 4096 is 240 pair
+    // tiles on 74 pairs = 3.24 waves): the tiles of the last, partial wave are cut along K into one equal range per unit
+    // (partial tiles summed through the workspace by the owner, which runs the full fused epilogue), the other tiles run
+    // whole.  stream_k = 1 forces it, 0 = when the partial wave would leave a worthwhile part of the device idle.
     kp.stream_k = 0;
     if (a->sk_workspace && a->stream_k >= 0) {
         const long long tiles = (long long)kp.m_tiles * kp.n_tiles * kp.batches;
-        const int G = num_sms();
-        const long long waves = (tiles + G - 1) / G;
-        const bool uneven = tiles * 100 < waves * G * 95;
-        const bool want = a->stream_k > 0 || ((uneven || a->split_k > 1) && tiles * kp.num_k_blocks >= 2ll * G);
+        const int G = num_sms() / cg;
+        const long long tail = tiles % G;
+        // auto: the partial wave is under 3/4 full, its ranges are at least 2 k-blocks long
+        const bool worth = tail > 0 && (tail * 4 <= 3ll * G || a->split_k > 1) && tail * kp.num_k_blocks >= 2ll * G;
+        const bool want = a->stream_k > 0 ? tail > 0 : worth;
         if (want && kp.num_k_blocks >= 2) {
             B2T_CHECK_ARG(((uintptr_t)a->sk_workspace & 15) == 0, "b2t_gemm: sk_workspace must be 16-byte aligned");
             kp.stream_k = 1;
             kp.split_k = 1;
             kp.total_items = (int)tiles;
-            kp.sk_units = tiles * kp.num_k_blocks;
+            kp.sk_tile0 = (int)(tiles - tail);
+            kp.sk_units = tail * kp.num_k_blocks;
+            kp.sk_G = kp.sk_units < G ? (int)kp.sk_units : G;
             kp.sk_flags = (int*)a->sk_workspace;
             kp.sk_ws = (float*)((char*)a->sk_workspace + SK_FLAG_BYTES);
         }
     }
 
     const bool three = a->a_lo != nullptr;
+    if (cg == 2) return three ? dispatch_major<3, 256, 2>(a, kp, stream) : dispatch_major<1, 256, 2>(a, kp, stream);
     if (three) {
-        if (bn == 64) return dispatch_major<3, 64>(a, kp, stream);
-        if (bn == 128) return dispatch_major<3, 128>(a, kp, stream);
-        return dispatch_major<3, 256>(a, kp, stream);
+        if (bn == 64) return dispatch_major<3, 64, 1>(a, kp, stream);
+        if (bn == 128) return dispatch_major<3, 128, 1>(a, kp, stream);
+        return dispatch_major<3, 256, 1>(a, kp, stream);
     }
-    if (bn == 64) return dispatch_major<1, 64>(a, kp, stream);
-    if (bn == 128) return dispatch_major<1, 128>(a, kp, stream);
-    return dispatch_major<1, 256>(a, kp, stream);
+    if (bn == 64) return dispatch_major<1, 64, 1>(a, kp, stream);
+    if (bn == 128) return dispatch_major<1, 128, 1>(a, kp, stream);
+    return dispatch_major<1, 256, 1>(a, kp, stream);
 }

@@ -187,7 +187,7 @@ def gemm(a: Operand, b: Operand, *, m_per_batch: int, n: int, k: int, batches: i
          alpha: float = 1.0, k_spans_batches: bool = False, a_batched: bool = False, b_batched: bool = False,
          b_batch_idx: Optional[Tensor] = None, c_batch_idx: Optional[Tensor] = None, block_n: int = 0,
          drop_p: float = 0.0, drop_seed: int = 0, bias_batch_stride: int = 0, out_scale: float = 1.0,
-         stream_k: int = 0) -> None:
+         stream_k: int = 0, cta_group: int = 0) -> None:
     """D = epilogue(alpha * A . B^T) on the tcgen05 GEMM (see b2t_gemm in include/b2t_sm100.h)."""
     _lib.ensure_device()
     g = GemmArgs()
@@ -218,6 +218,7 @@ def gemm(a: Operand, b: Operand, *, m_per_batch: int, n: int, k: int, batches: i
     g.drop_seed = drop_seed & 0xFFFFFFFFFFFFFFFF
     g.bias_batch_stride = bias_batch_stride
     g.out_scale = out_scale
+    g.cta_group = cta_group
     check(lib().b2t_gemm(ctypes.byref(g), stream()), "b2t_gemm")
     _count()
 
