@@ -34,7 +34,7 @@ def bench(name, m, n, k, three, a_mn=False, b_mn=False, split_k=1, bn=0, iters=2
     print(f"{name:34s} m={m:5d} n={n:5d} k={k:5d} terms={'3' if three else '1'} cg={cg or 'auto':>4} bn={bn or 'auto':>4} splitk={split_k:2d} sk={stream_k:2d}  {us:8.1f} us  "
           f"{tf:7.1f} TF/s alg  {tf * (3 if three else 1):7.1f} TF/s mma", flush=True)
 
-def bench_epi(name, m, n, k, bn=128, b_mn=False, iters=20, **flags):
+def bench_epi(name, m, n, k, bn=128, b_mn=False, iters=20, cg=0, **flags):
     """ffn-shaped GEMM with a chosen set of fused epilogue stages (bf16x3)."""
     dev = "cuda"
     ncopy = 3
@@ -54,15 +54,16 @@ def bench_epi(name, m, n, k, bn=128, b_mn=False, iters=20, **flags):
     if flags.get("drop"): kw["drop_p"] = 0.1; kw["drop_seed"] = 7
     def run(i):
         a, b = As[i % ncopy], Bs[i % ncopy]
-        ops.gemm(ops.kmajor(*a), ops.mnmajor(*b) if b_mn else ops.kmajor(*b), m_per_batch=m, n=n, k=k, block_n=bn, **kw)
+        ops.gemm(ops.kmajor(*a), ops.mnmajor(*b) if b_mn else ops.kmajor(*b), m_per_batch=m, n=n, k=k, block_n=bn, cta_group=cg, **kw)
     for i in range(3): run(i)
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda._sleep(6_000_000)
     e0.record()
     for i in range(iters): run(i)
     e1.record(); torch.cuda.synchronize()
     us = e0.elapsed_time(e1) / iters * 1e3
-    print(f"{name:44s} bn={bn} {us:8.1f} us  {2.0 * m * n * k / us / 1e6:7.1f} TF/s alg", flush=True)
+    print(f"{name:44s} cg={cg} bn={bn} {us:8.1f} us  {2.0 * m * n * k / us / 1e6:7.1f} TF/s alg", flush=True)
 
 
 def shapes_cg():
@@ -132,8 +133,21 @@ def shapes_fixed():
                 bench(f"fixed cost K={kk} hi/lo out", M, n, kk, True, cg=cg, stream_k=-1, out="split")
 
 
+EPI_CASES = [("f32", dict(f32=1)), ("hi/lo", dict(hi=1)), ("f32+hi/lo", dict(f32=1, hi=1)), ("hi/lo+aux(silu')", dict(hi=1, aux="silu")),
+             ("hi/lo+colsum", dict(hi=1, colsum=1)), ("hi/lo+aux(silu')+colsum+drop", dict(hi=1, aux="silu", colsum=1, drop=1)),
+             ("pre+hi/lo+bias+silu+drop", dict(pre=1, hi=1, bias=1, act="silu", drop=1)), ("pre+hi/lo+bias+gelu", dict(pre=1, hi=1, bias=1, act="gelu")),
+             ("f32+bias", dict(f32=1, bias=1)), ("f32+bias+res", dict(f32=1, bias=1, res=1)), ("f32+bias+drop+res", dict(f32=1, bias=1, res=1, drop=1))]
+
+
 if __name__ == "__main__":
     M = 3776
+    if len(sys.argv) > 1 and sys.argv[1] == "epi2":   # fused epilogues on pair tiles (env B2T_GEMM_NO_TMA_EPILOGUE=1: transposing epilogue)
+        ops.STREAM_K = False
+        for nm, fl in EPI_CASES:
+            bench_epi("ffn1 (N=4096,K=1024) " + nm, M, 4096, 1024, bn=0, cg=2, **fl)
+        for nm, fl in EPI_CASES:
+            bench_epi("outproj (N=1024,K=1024) " + nm, M, 1024, 1024, bn=0, cg=2, **fl)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "prof2":   # short run for ncu --set full: the pair kernel, epilogue-bound and MMA-bound
         ops.STREAM_K = False
         bench("ffn1 K=64 (epilogue-bound)", M, 4096, 64, True, cg=2, stream_k=-1, out="split", iters=1)

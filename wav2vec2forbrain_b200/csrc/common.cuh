@@ -111,4 +111,23 @@ __device__ __forceinline__ float hash_uniform(unsigned long long seed, unsigned 
     h ^= h >> 16;
     return (float)(h >> 8) * (1.0f / 16777216.0f);
 }
+// The same decision `hash_uniform(seed, idx) < p` in integer form for inner loops: (h >> 8) * 2^-24 < p  <=>  (h >> 8) < thr
+// with thr = ceil(p * 2^24) (exact: p * 2^24 is computed in double).  hash_fold() is the index-dependent first step.
+__host__ __device__ __forceinline__ uint32_t drop_threshold(float p) {
+    const double t = (double)p * 16777216.0;
+    const uint32_t f = (uint32_t)t;
+    return (double)f < t ? f + 1u : f;
+}
+__device__ __forceinline__ uint32_t hash_fold(unsigned long long idx) { return (uint32_t)idx + (uint32_t)(idx >> 32) * 0x85EBCA77u; }
+__device__ __forceinline__ bool hash_drop(uint32_t folded, uint32_t seed_lo, uint32_t seed_hi, uint32_t thr) {
+    uint32_t h = folded ^ seed_lo;
+    h *= 0x9E3779B1u;
+    h ^= seed_hi;
+    h ^= h >> 16;
+    h *= 0x85EBCA6Bu;
+    h ^= h >> 13;
+    h *= 0xC2B2AE35u;
+    h ^= h >> 16;
+    return (h >> 8) < thr;
+}
 #endif

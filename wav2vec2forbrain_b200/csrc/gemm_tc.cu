@@ -26,7 +26,13 @@ namespace {
 constexpr int BM = 128;
 constexpr int BK = 64;          // 64 bf16 = 128 B = one swizzle-128B row
 constexpr int UMMA_K = 16;
-constexpr int NUM_THREADS = 320;       // warp 0 TMA, warp 1 MMA, warps 2-9 epilogue
+// warp group 0 = warp 0 TMA, warp 1 MMA, warps 2-3 idle; warp groups 1-2 = the 8 epilogue warps.  Roles are cut on warp-group
+// boundaries so that setmaxnreg can move registers from the control group (REGS_CTRL each) to the epilogue (REGS_EPI
+// each): with 10 warps the fullest scheduler held 3 and the whole kernel was capped at 168 registers, which the
+// row-per-thread epilogue (32 accumulators + a prefetched 32-register input chunk + 32 packed outputs) spilled.
+constexpr int NUM_THREADS = 384;
+constexpr int EPI_WARP0 = 4;
+constexpr int REGS_CTRL = 56, REGS_EPI = 224;   // 128 * 56 + 256 * 224 = 64512 <= 65536
 constexpr int NUM_EPI_WARPS = 8;
 constexpr int SMEM_LIMIT = 227 * 1024;
 constexpr int SK_FLAG_BYTES = 1024;    // stream-K workspace: 256 int flags, then gridDim.x fp32 tile slots
@@ -191,7 +197,9 @@ __device__ __forceinline__ void cluster_sync_all() {
 }
 // arrive on a barrier of another CTA of the cluster (address from mapa)
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar) {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
+    // relaxed: the TMEM reads this arrive publishes are ordered by tcgen05.wait::ld + tcgen05.fence::before_thread_sync; a
+    // release at cluster scope would first drain the warp's outstanding global stores (MEMBAR, seen as stall_membar in ncu)
+    asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
 }
 // the load lands in THIS CTA's shared memory, its bytes are counted on the pair leader's barrier
 __device__ __forceinline__ void tma_load_3d_pair(uint32_t dst, const CUtensorMap* map, uint32_t cluster_bar, int c0, int c1,
@@ -381,6 +389,7 @@ enum : uint32_t {
     F_ALPHA = 1u << 0, F_BIAS = 1u << 1, F_PRE = 1u << 2, F_ACT = 1u << 3, F_AUX = 1u << 4, F_DROP = 1u << 5,
     F_SCALE = 1u << 6, F_RES = 1u << 7, F_F32 = 1u << 8, F_ATOMIC = 1u << 9, F_HI = 1u << 10, F_LO = 1u << 11,
     F_COLSUM = 1u << 12, F_VEC = 1u << 13,
+    F_TMA = 1u << 14,   // aligned AND rows / batches of the output do not overlap in memory: TMA-store epilogue
 };
 
 __device__ __forceinline__ void st_f8(float* o, const float (&v)[8], int nvalid) {
@@ -710,10 +719,225 @@ __device__ __forceinline__ void epi_chunk32(const KParams& p, const uint32_t F, 
     __syncwarp();   // the buffer is rewritten by the next chunk
 }
 
+
+// ------------------------------------------------------------------------------------------
+// TMA-store epilogue (aligned outputs: F_VEC).  ncu on the transposing epilogue above (round 2, pair kernel,
+// profiles/ncu_gemm_pair_r02_summary.txt): 690 warp instructions per 32 x 32 chunk at one issue per ~6 clocks and two
+// warps per scheduler = 22 k clocks per 128 x 256 tile - as long as the tile's MMAs, and fully exposed behind the
+// last tile of every launch.  Here a thread keeps the accumulator row tcgen05.ld gave it (32 independent dependency
+// chains per stage, no per-element address arithmetic or bounds predicates), writes it once into the warp's 4 KB
+// staging buffer in the swizzle pattern of the output tensor map, and one lane issues a bulk tensor store (or
+// reduce-add) - the TMA unit clips rows / columns outside the matrix and writes whole lines.  The aux / residual
+// inputs are still read with coalesced 16-byte loads (8 lanes per 128-byte row segment), issued before the TMEM
+// load, and turned into rows through the same buffer.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2) {
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(map), "r"(src), "r"(c0),
+                 "r"(c1), "r"(c2)
+                 : "memory");
+}
+__device__ __forceinline__ void tma_reduce_add_3d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2) {
+    asm volatile("cp.reduce.async.bulk.tensor.3d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(map),
+                 "r"(src), "r"(c0), "r"(c1), "r"(c2)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+struct EpiMaps {
+    const CUtensorMap* f32;
+    const CUtensorMap* pre;
+    const CUtensorMap* hi;
+    const CUtensorMap* lo;
+};
+
+// coalesced read of a 32 x 32 fp32 chunk: instruction i covers rows 4 i + (lane >> 3), lane & 7 picks the 16-byte unit
+__device__ __forceinline__ void chunk_ldg(const KParams& p, const float* src, long long base_off, int row0, int col_base,
+                                          int lane, float4 (&t)[8]) {
+    const int c4 = lane & 7, rsub = lane >> 3;
+    const int col = col_base + c4 * 4;
+    const bool col_ok = col < p.n;   // n % 4 == 0 on this path
+    const int last_row = p.m_per_batch - 1;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int row = row0 + i * 4 + rsub;
+        const long long off = base_off + (long long)(row <= last_row ? row : last_row) * p.ldc + (col_ok ? col : 0);
+        t[i] = __ldcg(reinterpret_cast<const float4*>(src + off));
+    }
+}
+// ... and its transposition into "lane = row": through the staging buffer, same XOR swizzle as the stores
+__device__ __forceinline__ void chunk_to_rows_store(float* st, int lane, const float4 (&t)[8]) {
+    const int c4 = lane & 7, rsub = lane >> 3;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int r = i * 4 + rsub;
+        *reinterpret_cast<float4*>(st + r * 32 + ((c4 ^ (r & 7)) << 2)) = t[i];
+    }
+}
+__device__ __forceinline__ float4 chunk_row_unit(const float* st, int lane, int j) {
+    return *reinterpret_cast<const float4*>(st + lane * 32 + ((j ^ (lane & 7)) << 2));
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(bf16 a, bf16 b) {
+    __nv_bfloat162 t = __halves2bfloat162(a, b);
+    return *reinterpret_cast<uint32_t*>(&t);
+}
+
+// v: the lane's accumulator row (row0 + lane inside the batch), 32 columns from col_base.  st / st_addr: this warp's
+// 4 KB staging buffer (generic pointer / shared address, 1024-byte aligned).  `pending`: a bulk store of this warp may
+// still be reading the buffer (lane 0 is the only lane that commits and waits).
+__device__ __forceinline__ void epi_row32(const KParams& p, const uint32_t F, float* st, uint32_t st_addr, float (&v)[32],
+                                          int lane, int row0, int cbatch, long long base_off, int col_base,
+                                          const float* bias_ptr, const EpiMaps& maps, float4 (&t)[8]) {
+#define EPI32(stmt) _Pragma("unroll") for (int e = 0; e < 32; ++e) { stmt; }
+    auto buffer_free = [&]() {   // every earlier bulk store of this warp has read the buffer, every lane is past its own reads
+        if (lane == 0 && !(p.debug & 64)) bulk_wait_read0();
+        __syncwarp();
+    };
+    const int row = row0 + lane;
+    const bool row_ok = row < p.m_per_batch;
+    const long long off_row = base_off + (long long)(row_ok ? row : p.m_per_batch - 1) * p.ldc + col_base;   // dropout counter
+    if (F & F_ALPHA) { EPI32(v[e] *= p.alpha) }
+    if (bias_ptr) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            if (col_base + 4 * j < p.n) {   // warp-uniform
+                const float4 b = *reinterpret_cast<const float4*>(bias_ptr + col_base + 4 * j);
+                v[4 * j] += b.x, v[4 * j + 1] += b.y, v[4 * j + 2] += b.z, v[4 * j + 3] += b.w;
+            }
+        }
+    }
+    if (F & F_PRE) {
+        buffer_free();
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4*>(st + lane * 32 + ((j ^ (lane & 7)) << 2)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+            tma_store_3d(maps.pre, st_addr, col_base, row0, cbatch);
+            bulk_commit();
+        }
+    }
+    if (F & F_ACT) {
+        if (p.act == 1) { EPI32(v[e] = gelu_erf(v[e])) }
+        else if (p.act == 2) { EPI32(v[e] = silu_f(v[e])) }
+        else { EPI32(v[e] = v[e] * rcp_approx(1.0f + fabsf(v[e]))) }
+    }
+    if (F & F_AUX) {
+        // t holds the aux chunk (coalesced layout, loaded before the TMEM load)
+        buffer_free();
+        chunk_to_rows_store(st, lane, t);
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float4 a = chunk_row_unit(st, lane, j);
+            const float ax[4] = {a.x, a.y, a.z, a.w};
+            if (p.aux_mode == 1) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) v[4 * j + e] *= gelu_erf_grad(ax[e]);
+            } else if (p.aux_mode == 2) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) v[4 * j + e] *= silu_grad(ax[e]);
+            } else {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float d = 1.0f + fabsf(ax[e]);
+                    v[4 * j + e] *= rcp_approx(d * d);
+                }
+            }
+        }
+        __syncwarp();
+        if (F & F_RES) chunk_ldg(p, p.residual, base_off, row0, col_base, lane, t);   // both inputs: the second read is exposed
+    }
+    if (F & F_DROP) {
+        // same keep / drop decision as hash_uniform(seed, offset) < p, with the 64-bit index folded once per row segment
+        const uint32_t thr = drop_threshold(p.drop_p), s_lo = (uint32_t)p.drop_seed, s_hi = (uint32_t)(p.drop_seed >> 32);
+        const unsigned long long o0 = (unsigned long long)off_row;
+        if ((uint32_t)o0 <= 0xFFFFFFFFu - 32u) {   // no carry into the high word inside the segment
+            const uint32_t f0 = hash_fold(o0);
+            EPI32(v[e] = hash_drop(f0 + (uint32_t)e, s_lo, s_hi, thr) ? 0.0f : v[e] * p.drop_scale)
+        } else {
+            EPI32(v[e] = hash_drop(hash_fold(o0 + e), s_lo, s_hi, thr) ? 0.0f : v[e] * p.drop_scale)
+        }
+    }
+    if (F & F_SCALE) { EPI32(v[e] *= p.out_scale) }
+    if (F & F_RES) {
+        buffer_free();
+        chunk_to_rows_store(st, lane, t);
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float4 a = chunk_row_unit(st, lane, j);
+            v[4 * j] += a.x, v[4 * j + 1] += a.y, v[4 * j + 2] += a.z, v[4 * j + 3] += a.w;
+        }
+        __syncwarp();
+    }
+    if (F & (F_F32 | F_COLSUM)) {
+        buffer_free();
+        if (F & F_COLSUM) {
+            // rows / columns outside the matrix must not reach the column sums (the stores clip them by themselves)
+            EPI32(v[e] = (row_ok && col_base + e < p.n) ? v[e] : 0.0f)
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4*>(st + lane * 32 + ((j ^ (lane & 7)) << 2)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        if (F & F_F32) fence_proxy_async_smem();
+        __syncwarp();
+        if ((F & F_F32) && lane == 0) {
+            if (F & F_ATOMIC)
+                tma_reduce_add_3d(maps.f32, st_addr, col_base, row0, cbatch);
+            else
+                tma_store_3d(maps.f32, st_addr, col_base, row0, cbatch);
+            bulk_commit();
+        }
+        if (F & F_COLSUM) {   // lane = column: 32 conflict-free reads down the staged chunk
+            float s = 0.0f;
+#pragma unroll
+            for (int r = 0; r < 32; ++r) s += st[r * 32 + ((((lane >> 2) ^ (r & 7)) << 2) | (lane & 3))];
+            if (col_base + lane < p.n) atomicAdd(p.colsum + col_base + lane, s);
+            __syncwarp();
+        }
+    }
+    if (F & F_HI) {
+        // bf16 hi / lo rows: 64 bytes each, 64-byte swizzle (16-byte unit ^ ((row >> 1) & 3)), hi at +0, lo at +2 KB
+        uint32_t h[16], l[16];
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+            // two values per conversion (F2FP.BF16.PACK_AB on the ALU; a scalar cvt.rn.bf16 is an F2F on the quarter-rate pipe)
+            __nv_bfloat162 hh = __floats2bfloat162_rn(v[2 * e], v[2 * e + 1]);
+            const float2 hf = __bfloat1622float2(hh);
+            __nv_bfloat162 ll = __floats2bfloat162_rn(v[2 * e] - hf.x, v[2 * e + 1] - hf.y);
+            h[e] = *reinterpret_cast<uint32_t*>(&hh);
+            l[e] = *reinterpret_cast<uint32_t*>(&ll);
+        }
+        buffer_free();
+        uint8_t* sb = reinterpret_cast<uint8_t*>(st);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int o = lane * 64 + ((j ^ ((lane >> 1) & 3)) << 4);
+            *reinterpret_cast<uint4*>(sb + o) = make_uint4(h[4 * j], h[4 * j + 1], h[4 * j + 2], h[4 * j + 3]);
+            if (F & F_LO) *reinterpret_cast<uint4*>(sb + 2048 + o) = make_uint4(l[4 * j], l[4 * j + 1], l[4 * j + 2], l[4 * j + 3]);
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+            tma_store_3d(maps.hi, st_addr, col_base, row0, cbatch);
+            if (F & F_LO) tma_store_3d(maps.lo, st_addr + 2048, col_base, row0, cbatch);
+            bulk_commit();
+        }
+    }
+#undef EPI32
+}
+
 template <int NTERMS, bool A_MN, bool B_MN, int BN, int CG>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ CUtensorMap tmAl,
-               const __grid_constant__ CUtensorMap tmBh, const __grid_constant__ CUtensorMap tmBl, const KParams p) {
+               const __grid_constant__ CUtensorMap tmBh, const __grid_constant__ CUtensorMap tmBl,
+               const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmPre,
+               const __grid_constant__ CUtensorMap tmHi, const __grid_constant__ CUtensorMap tmLo, const KParams p) {
     using C = Cfg<NTERMS, BN, CG>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -773,6 +997,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr_gen;
 
+    if (warp < EPI_WARP0) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(REGS_CTRL));
     if (warp == 0) {
         // ================================ TMA producer ================================
         if (lane == 0) {
@@ -910,13 +1136,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
                 }
             }
         }
-    } else if (warp >= 2) {
+    }
+    } else {
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(REGS_EPI));
         // ================================ epilogue ====================================
         // 8 warps: TMEM lane quadrant q = warp & 3 (hardware restriction), the two warps of a
         // quadrant take alternate 32-column chunks.  A thread owns ONE output row (its TMEM lane)
         // and 32 consecutive columns of it: all global traffic is 16-byte vectors on that row.
         const int q = warp & 3;
-        const int half = (warp - 2) >> 2;
+        const int half = (warp - EPI_WARP0) >> 2;
         int local_iter = 0;
         uint32_t F = p.flags;
         asm volatile("" : "+r"(F));   // pin the stage bits in a register (else ptxas re-reads the constant bank per test)
@@ -924,19 +1152,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
         Item it;
         const uint32_t tempty_remote0 = CG == 2 ? mapa_u32(tempty_bar(0), 0) : 0u;   // the leader's tmem_empty barriers
         float* const epi_buf =
-            reinterpret_cast<float*>(smem_gen + C::STAGES * C::STAGE_BYTES) + (warp - 2) * EPI_CHUNK_FLOATS;
+            reinterpret_cast<float*>(smem_gen + C::STAGES * C::STAGE_BYTES) + (warp - EPI_WARP0) * EPI_CHUNK_FLOATS;
+        const uint32_t epi_buf_addr = smem_base + C::STAGES * C::STAGE_BYTES + (warp - EPI_WARP0) * (EPI_CHUNK_FLOATS * 4);
+        const EpiMaps emaps{&tmC, &tmPre, &tmHi, &tmLo};
         float* const ws_mine = p.sk_ws + (size_t)blockIdx.x * (BM * BN);
         for (; sch.next(it); ++local_iter) {
             const int split = it.split, batch = it.batch, m_blk = it.m_blk, n_blk = it.n_blk;
             const int acc = local_iter & 1;
             const uint32_t acc_phase = (uint32_t)(local_iter >> 1) & 1u;
+            const int cbatch = p.c_batch_idx ? p.c_batch_idx[batch] : batch;
+            const long long base_off = (long long)cbatch * p.c_batch_stride;
             if ((F & (F_AUX | F_RES)) && it.mode != 1) {
                 // the tile's MMAs are still running: pull this warp's aux / residual lines (cold in HBM inside a
                 // training step) into L2 now, one 128-byte line per lane (= row) and 32-column chunk
                 const int prow = m_blk * BM + q * 32 + lane;
                 if (prow < p.m_per_batch) {
-                    const long long poff = (long long)(p.c_batch_idx ? p.c_batch_idx[batch] : batch) * p.c_batch_stride +
-                                           (long long)prow * p.ldc + n_blk * BN;
+                    const long long poff = base_off + (long long)prow * p.ldc + n_blk * BN;
                     for (int c = half; c < BN / 32; c += 2) {
                         if (n_blk * BN + c * 32 >= p.n) break;
                         if (F & F_AUX) prefetch_l2(p.aux + poff + c * 32);
@@ -944,6 +1175,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
                     }
                 }
             }
+            // TMA-store epilogue: the aux (else residual) chunk is read one chunk ahead of its use - the first one
+            // here, under the tile's MMAs - so that no chunk waits for a memory round trip
+            const bool tin_on = (F & F_TMA) && (F & (F_AUX | F_RES)) && it.mode != 1 && !(p.debug & 1);
+            const float* const tin_src = (F & F_AUX) ? p.aux : p.residual;
+            float4 tin[8], tnext[8];
+            if (tin_on && n_blk * BN + half * 32 < p.n)
+                chunk_ldg(p, tin_src, base_off, m_blk * BM + q * 32, n_blk * BN + half * 32, lane, tnext);
             mbar_wait(tfull_bar(acc), acc_phase);
             tc_fence_after();
             if (it.mode == 2 && !(p.debug & (8 | 16))) {
@@ -960,14 +1198,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
                 }
                 __syncwarp();
             }
-            const int cbatch = p.c_batch_idx ? p.c_batch_idx[batch] : batch;
-            const long long base_off = (long long)cbatch * p.c_batch_stride;
             const int bslot = p.b_batch_idx ? p.b_batch_idx[batch] : (p.b_batched ? batch : 0);
             const float* bias_ptr =
                 (p.bias != nullptr && split == 0) ? p.bias + (long long)bslot * p.bias_batch_stride : nullptr;
 #pragma unroll 1
             for (int c = half; c < BN / 32; c += 2) {
                 float v[32];
+                if (tin_on) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) tin[i] = tnext[i];
+                    if (c + 2 < BN / 32 && n_blk * BN + (c + 2) * 32 < p.n)
+                        chunk_ldg(p, tin_src, base_off, m_blk * BM + q * 32, n_blk * BN + (c + 2) * 32, lane, tnext);
+                }
                 const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + c * 32);
                 tmem_ld_32x32(taddr, v);
                 if (c + 2 >= BN / 32) {
@@ -1005,7 +1247,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
                         }
                     }
                 }
-                if (F & F_VEC)
+                if (F & F_TMA)
+                    epi_row32(p, F, epi_buf, epi_buf_addr, v, lane, m_blk * BM + q * 32, cbatch, base_off, col_base, bias_ptr, emaps, tin);
+                else if (F & F_VEC)
                     epi_chunk32<true>(p, F, epi_buf, v, lane, m_blk * BM + q * 32, base_off, col_base, bias_ptr);
                 else
                     epi_chunk32<false>(p, F, epi_buf, v, lane, m_blk * BM + q * 32, base_off, col_base, bias_ptr);
@@ -1018,9 +1262,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
             } else if (it.mode == 2) {
                 // every epilogue warp is past its wait: clear the flag for the next launch on this stream
                 asm volatile("bar.sync 1, %0;" ::"n"(NUM_EPI_WARPS * 32) : "memory");
-                if (threadIdx.x == 64) p.sk_flags[blockIdx.x] = 0;
+                if (threadIdx.x == EPI_WARP0 * 32) p.sk_flags[blockIdx.x] = 0;
             }
         }
+        if (lane == 0) bulk_wait0();   // this warp's bulk stores are complete before the CTA may leave
     }
 
     tc_fence_before();
@@ -1112,20 +1357,26 @@ int make_map(CUtensorMap* map, const void* ptr, int64_t d0, int64_t d1, int64_t 
     return encode_map(map, ptr, d0, d1, d2, s1, s2, box1, what);
 }
 
+// box1 > 0: bf16 operand map, box {64, box1, 1}, 128-byte swizzle.  box1 == MAP_OUT_F32 / MAP_OUT_BF16: output maps of the
+// TMA-store epilogue, box {32, 32, 1} (one warp chunk), fp32 rows = 128-byte swizzle, bf16 rows = 64-byte swizzle.
+constexpr int MAP_OUT_F32 = -1, MAP_OUT_BF16 = -2;
 int encode_map(CUtensorMap* map, const void* ptr, int64_t d0, int64_t d1, int64_t d2, int64_t s1, int64_t s2, int box1,
                const char* what) {
     EncodeTiledFn fn = get_encode_fn();
     B2T_CHECK_ARG(fn != nullptr, "b2t_gemm: cuTensorMapEncodeTiled entry point not found");
-    B2T_CHECK_ARG(((uintptr_t)ptr & 15) == 0, "b2t_gemm: operand %s not 16-byte aligned", what);
-    B2T_CHECK_ARG(s1 % 8 == 0 && s2 % 8 == 0, "b2t_gemm: operand %s strides (%lld, %lld) must be multiples of 8 elements",
+    B2T_CHECK_ARG(((uintptr_t)ptr & 15) == 0, "b2t_gemm: %s not 16-byte aligned", what);
+    const bool f32 = box1 == MAP_OUT_F32;
+    const int esz = f32 ? 4 : 2;
+    B2T_CHECK_ARG((s1 * esz) % 16 == 0 && (s2 * esz) % 16 == 0, "b2t_gemm: %s strides (%lld, %lld) must be multiples of 16 bytes",
                   what, (long long)s1, (long long)s2);
     cuuint64_t dims[3] = {(cuuint64_t)d0, (cuuint64_t)d1, (cuuint64_t)d2};
-    cuuint64_t strides[2] = {(cuuint64_t)s1 * 2, (cuuint64_t)s2 * 2};
-    cuuint32_t box[3] = {64, (cuuint32_t)box1, 1};
+    cuuint64_t strides[2] = {(cuuint64_t)s1 * esz, (cuuint64_t)s2 * esz};
+    cuuint32_t box[3] = {box1 > 0 ? 64u : 32u, box1 > 0 ? (cuuint32_t)box1 : 32u, 1};
     cuuint32_t estr[3] = {1, 1, 1};
-    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    CUresult r = fn(map, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims,
+                    strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    box1 == MAP_OUT_BF16 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+                    box1 > 0 ? CU_TENSOR_MAP_L2_PROMOTION_L2_256B : CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     B2T_CHECK_ARG(r == CUDA_SUCCESS,
                   "b2t_gemm: cuTensorMapEncodeTiled(%s) failed with %d (dims %lld %lld %lld strides %lld %lld box1 %d)", what,
                   (int)r, (long long)d0, (long long)d1, (long long)d2, (long long)s1, (long long)s2, box1);
@@ -1165,6 +1416,17 @@ int launch(const b2t_gemm_args* a, const KParams& kp, cudaStream_t stream) {
         mAl = mAh;
         mBl = mBh;
     }
+    // output maps of the TMA-store epilogue (aligned outputs only; the kernel ignores them otherwise): columns x rows of
+    // one batch x batch slots - rows past m_per_batch and columns past n are clipped by the TMA unit
+    CUtensorMap mC = mAh, mPre = mAh, mHi = mAh, mLo = mAh;
+    if (kp.flags & F_TMA) {
+        const int64_t slots = a->c_batch_idx ? (int64_t)1 << 16 : a->batches;
+        const int64_t s2 = slots > 1 ? a->c_batch_stride : (int64_t)a->m_per_batch * a->ldc;
+        if (a->out_f32 && (rc = make_map(&mC, a->out_f32, a->n, a->m_per_batch, slots, a->ldc, s2, MAP_OUT_F32, "out_f32"))) return rc;
+        if (a->out_pre && (rc = make_map(&mPre, a->out_pre, a->n, a->m_per_batch, slots, a->ldc, s2, MAP_OUT_F32, "out_pre"))) return rc;
+        if (a->out_hi && (rc = make_map(&mHi, a->out_hi, a->n, a->m_per_batch, slots, a->ldc, s2, MAP_OUT_BF16, "out_hi"))) return rc;
+        if (a->out_lo && (rc = make_map(&mLo, a->out_lo, a->n, a->m_per_batch, slots, a->ldc, s2, MAP_OUT_BF16, "out_lo"))) return rc;
+    }
     auto kern = gemm_tc_kernel<NTERMS, A_MN, B_MN, BN, CG>;
     {
         // per device: the attribute belongs to the function in ONE device's context
@@ -1190,7 +1452,7 @@ int launch(const b2t_gemm_args* a, const KParams& kp, cudaStream_t stream) {
         }
     }
     if (CG == 1) {
-        kern<<<units, NUM_THREADS, C::SMEM_BYTES, stream>>>(mAh, mAl, mBh, mBl, kq);
+        kern<<<units, NUM_THREADS, C::SMEM_BYTES, stream>>>(mAh, mAl, mBh, mBl, mC, mPre, mHi, mLo, kq);
     } else {
         cudaLaunchConfig_t cfg;
         memset(&cfg, 0, sizeof(cfg));
@@ -1205,7 +1467,7 @@ int launch(const b2t_gemm_args* a, const KParams& kp, cudaStream_t stream) {
         at[0].val.clusterDim.z = 1;
         cfg.attrs = at;
         cfg.numAttrs = 1;
-        B2T_CUDA(cudaLaunchKernelEx(&cfg, kern, mAh, mAl, mBh, mBl, kq));
+        B2T_CUDA(cudaLaunchKernelEx(&cfg, kern, mAh, mAl, mBh, mBl, mC, mPre, mHi, mLo, kq));
     }
     B2T_CHECK_LAUNCH("b2t_gemm");
     return 0;
@@ -1300,6 +1562,17 @@ extern "C" int b2t_gemm(const b2t_gemm_args* a, b2t_stream stream_) {
                (kp.aux_mode ? F_AUX : 0u) | (kp.drop_p > 0.0f ? F_DROP : 0u) | (kp.out_scale != 1.0f ? F_SCALE : 0u) |
                (kp.residual ? F_RES : 0u) | (kp.out_f32 ? F_F32 : 0u) | (kp.atomic ? F_ATOMIC : 0u) | (kp.out_hi ? F_HI : 0u) |
                (kp.out_lo ? F_LO : 0u) | (kp.colsum ? F_COLSUM : 0u) | (kp.vec4 ? F_VEC : 0u);
+    {
+        // overlapping-stride outputs (the folded unfold gradient: ldc < n) keep the per-element red.add path
+        static int no_tma = -1;
+        if (no_tma < 0) {
+            const char* e = getenv("B2T_GEMM_NO_TMA_EPILOGUE");
+            no_tma = e ? atoi(e) : 0;
+        }
+        const bool rows_apart = a->ldc >= a->n;
+        const bool batches_apart = (a->batches == 1 && !a->c_batch_idx) || a->c_batch_stride >= (int64_t)(a->m_per_batch - 1) * a->ldc + a->n;
+        if (kp.vec4 && rows_apart && batches_apart && !no_tma) kp.flags |= F_TMA;
+    }
 
     {
         static int dbg = -1;
@@ -1323,7 +1596,12 @@ extern "C" int b2t_gemm(const b2t_gemm_args* a, b2t_stream stream_) {
         }
         if (cg == 0 && (force_cg == 1 || force_cg == 2)) cg = force_cg;
     }
-    if (cg == 0) cg = (bn == 0 || bn == 256) && a->n >= 256 && a->n % 128 == 0 && a->m_per_batch > BM && num_sms() >= 2 ? 2 : 1;
+    if (cg == 0) {
+        // pairs when there are enough 256 x 256 work items to occupy a good part of the 74 pairs (few, large items lose to
+        // many 128 x 128 tiles: measured on the 2048 x 1024 and 1024 x 1024 weight gradients, profiles/gemm_table_r02*)
+        const long long items2 = (long long)ceil_div_i(ceil_div_i(a->m_per_batch, BM), 2) * ceil_div_i(a->n, 256) * a->batches * a->split_k;
+        cg = (bn == 0 || bn == 256) && a->n >= 256 && a->n % 128 == 0 && a->m_per_batch > BM && num_sms() >= 2 && items2 >= 30 ? 2 : 1;
+    }
     if (cg == 2 && (kp.debug & 7)) cg = 1;   // the component-timing switches exist for the single-CTA kernel only
     if (cg == 2) {
         B2T_CHECK_ARG(bn == 0 || bn == 256, "b2t_gemm: cta_group 2 uses block_n 256");

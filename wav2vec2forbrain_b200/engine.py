@@ -52,6 +52,13 @@ def _ver(*ts) -> tuple:
 
 
 def _split_k_for(m: int, n: int, k_blocks: int, bn: int = 128) -> int:
+    """split-K factor of a weight-gradient GEMM ([m, n] output, k_blocks 64-row blocks of contraction): enough work
+    items for the 74 CTA pairs of the 256 x 256 pair tiles (b2t_gemm cta_group 2), 148 CTAs for narrow outputs."""
+    if n % 128 == 0 and n >= 256 and m > 128:
+        tiles = ((m + 255) // 256) * ((n + 255) // 256)
+        if tiles >= 56:
+            return 1
+        return max(1, min(74 // tiles, max(1, k_blocks // 4), 16))
     tiles = ((m + 127) // 128) * ((n + bn - 1) // bn)
     if tiles >= 96:
         return 1
