@@ -164,8 +164,9 @@ if __name__ == "__main__":
         sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "epi1":   # the two heavy in-step epilogues, short (for ncu --set full)
         ops.STREAM_K = False
-        bench_epi("ffn1 dgrad hi/lo+aux(silu')+colsum+drop", M, 4096, 1024, bn=128, b_mn=True, iters=2, hi=1, aux="silu", colsum=1, drop=1)
-        bench_epi("ffn1 fwd pre+hi/lo+bias+silu+drop", M, 4096, 1024, bn=128, iters=2, pre=1, hi=1, bias=1, act="silu", drop=1)
+        bench_epi("ffn1 dgrad hi/lo+aux(silu')+colsum+drop", M, 4096, 1024, bn=0, b_mn=True, iters=2, hi=1, aux="silu", colsum=1, drop=1)
+        bench_epi("ffn1 fwd pre+hi/lo+bias+silu+drop", M, 4096, 1024, bn=0, iters=2, pre=1, hi=1, bias=1, act="silu", drop=1)
+        bench_epi("ffn2 fwd f32+bias+drop+res", M, 1024, 4096, bn=0, iters=2, f32=1, bias=1, res=1, drop=1)
         sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "epi":
         ops.STREAM_K = False

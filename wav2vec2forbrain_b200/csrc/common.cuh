@@ -89,7 +89,13 @@ __device__ __forceinline__ float rcp_approx(float x) {   // one MUFU.RCP, no den
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
 }
-__device__ __forceinline__ float sigmoidf_(float x) { return rcp_approx(1.0f + __expf(-x)); }
+// exp(-x) as one FMUL + MUFU.EX2 (ftz): __expf carries a denormal-range fix-up (FSETP + 2 predicated FMULs per value)
+__device__ __forceinline__ float exp_neg_fast(float x) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x * -1.4426950408889634f));
+    return r;
+}
+__device__ __forceinline__ float sigmoidf_(float x) { return rcp_approx(1.0f + exp_neg_fast(x)); }
 __device__ __forceinline__ float silu_f(float x) { return x * sigmoidf_(x); }
 __device__ __forceinline__ float silu_grad(float x) {
     const float s = sigmoidf_(x);

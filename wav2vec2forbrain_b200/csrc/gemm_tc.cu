@@ -54,6 +54,7 @@ struct KParams {
     int act, aux_mode, atomic, split_k;
     float alpha;
     float drop_p, drop_scale, out_scale;
+    uint32_t drop_thr;   // drop_threshold(drop_p): keep / drop as an integer compare (computed on the host, it needs fp64)
     int vec4;
     int debug;   // B2T_GEMM_DEBUG (profiling aid): 1 skip the epilogue body, 2 skip MMA issue, 4 skip TMA loads
     uint32_t flags;
@@ -827,34 +828,27 @@ __device__ __forceinline__ void epi_row32(const KParams& p, const uint32_t F, fl
         else { EPI32(v[e] = v[e] * rcp_approx(1.0f + fabsf(v[e]))) }
     }
     if (F & F_AUX) {
-        // t holds the aux chunk (coalesced layout, loaded before the TMEM load)
+        // t holds the aux chunk (coalesced layout, loaded one chunk ahead)
         buffer_free();
         chunk_to_rows_store(st, lane, t);
         __syncwarp();
+        float a[32];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            const float4 a = chunk_row_unit(st, lane, j);
-            const float ax[4] = {a.x, a.y, a.z, a.w};
-            if (p.aux_mode == 1) {
-#pragma unroll
-                for (int e = 0; e < 4; ++e) v[4 * j + e] *= gelu_erf_grad(ax[e]);
-            } else if (p.aux_mode == 2) {
-#pragma unroll
-                for (int e = 0; e < 4; ++e) v[4 * j + e] *= silu_grad(ax[e]);
-            } else {
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const float d = 1.0f + fabsf(ax[e]);
-                    v[4 * j + e] *= rcp_approx(d * d);
-                }
-            }
+            const float4 q = chunk_row_unit(st, lane, j);
+            a[4 * j] = q.x, a[4 * j + 1] = q.y, a[4 * j + 2] = q.z, a[4 * j + 3] = q.w;
         }
         __syncwarp();
+        // one mode branch around 32 independent chains (inside the unit loop the three variants were interleaved eight
+        // times: 4 chains per segment and an instruction stream scattered over 1600 slots - stall_no_inst in ncu)
+        if (p.aux_mode == 1) { EPI32(v[e] *= gelu_erf_grad(a[e])) }
+        else if (p.aux_mode == 2) { EPI32(v[e] *= silu_grad(a[e])) }
+        else { EPI32(const float d = 1.0f + fabsf(a[e]); v[e] *= rcp_approx(d * d)) }
         if (F & F_RES) chunk_ldg(p, p.residual, base_off, row0, col_base, lane, t);   // both inputs: the second read is exposed
     }
     if (F & F_DROP) {
         // same keep / drop decision as hash_uniform(seed, offset) < p, with the 64-bit index folded once per row segment
-        const uint32_t thr = drop_threshold(p.drop_p), s_lo = (uint32_t)p.drop_seed, s_hi = (uint32_t)(p.drop_seed >> 32);
+        const uint32_t thr = p.drop_thr, s_lo = (uint32_t)p.drop_seed, s_hi = (uint32_t)(p.drop_seed >> 32);
         const unsigned long long o0 = (unsigned long long)off_row;
         if ((uint32_t)o0 <= 0xFFFFFFFFu - 32u) {   // no carry into the high word inside the segment
             const uint32_t f0 = hash_fold(o0);
@@ -894,9 +888,10 @@ __device__ __forceinline__ void epi_row32(const KParams& p, const uint32_t F, fl
             bulk_commit();
         }
         if (F & F_COLSUM) {   // lane = column: 32 conflict-free reads down the staged chunk
-            float s = 0.0f;
+            float s4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-            for (int r = 0; r < 32; ++r) s += st[r * 32 + ((((lane >> 2) ^ (r & 7)) << 2) | (lane & 3))];
+            for (int r = 0; r < 32; ++r) s4[r & 3] += st[r * 32 + ((((lane >> 2) ^ (r & 7)) << 2) | (lane & 3))];
+            const float s = (s4[0] + s4[1]) + (s4[2] + s4[3]);
             if (col_base + lane < p.n) atomicAdd(p.colsum + col_base + lane, s);
             __syncwarp();
         }
@@ -1548,6 +1543,7 @@ extern "C" int b2t_gemm(const b2t_gemm_args* a, b2t_stream stream_) {
     B2T_CHECK_ARG(a->drop_p >= 0.0f && a->drop_p < 1.0f, "b2t_gemm: drop_p must be in [0, 1)");
     kp.drop_p = a->drop_p;
     kp.drop_scale = 1.0f / (1.0f - a->drop_p);
+    kp.drop_thr = drop_threshold(a->drop_p);
     kp.drop_seed = a->drop_seed;
     kp.out_scale = a->out_scale == 0.0f ? 1.0f : a->out_scale;
     {
