@@ -66,6 +66,8 @@ if __name__ == "__main__":
         conv(32); sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "gru":
         gru(32); sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "attn":
+        attn(32, 16); attn(64, 12); sys.exit(0)
     gru(64); gru(32)
     attn(64, 12); attn(32, 16)
     ln(7552, 768); ln(3776, 1024)

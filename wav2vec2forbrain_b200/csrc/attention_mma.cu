@@ -42,11 +42,12 @@ __device__ __forceinline__ void mma3(float (&c)[4], const uint32_t (&ah)[4], con
     mma16816(c, ah, bl0, bl1);
     mma16816(c, al, bh0, bh1);
 }
+// same values as split_bf16 per element; two values per conversion (F2FP.BF16.PACK_AB on the ALU - the scalar
+// cvt.rn.bf16 is an F2F on the quarter-rate pipe and was the top long-scoreboard stall of the prologue in ncu)
 __device__ __forceinline__ void pack_split(float x, float y, uint32_t& hi, uint32_t& lo) {
-    bf16 xh, xl, yh, yl;
-    split_bf16(x, xh, xl);
-    split_bf16(y, yh, yl);
-    __nv_bfloat162 h = __halves2bfloat162(xh, yh), l = __halves2bfloat162(xl, yl);
+    __nv_bfloat162 h = __floats2bfloat162_rn(x, y);
+    const float2 hf = __bfloat1622float2(h);
+    __nv_bfloat162 l = __floats2bfloat162_rn(x - hf.x, y - hf.y);
     hi = *reinterpret_cast<uint32_t*>(&h);
     lo = *reinterpret_cast<uint32_t*>(&l);
 }
@@ -143,11 +144,13 @@ struct Smem {
     static constexpr size_t BWD_BYTES = (size_t)(6 * TILE + 2 * PTILE) * sizeof(bf16);
 };
 
+// two CTAs per SM (110 KB of shared memory each at D = 64, 128 registers): ncu showed one CTA's 8 warps issuing on
+// 28 % of the cycles, stalled on fixed-latency dependencies and instruction fetch of the fully unrolled body
 template <int D>
-__global__ void __launch_bounds__(THREADS, 1)
+__global__ void __launch_bounds__(THREADS, 2)
 attn_fwd_mma_kernel(const float* __restrict__ qkv, long ld, int q_off, int k_off, int v_off, const int* __restrict__ kv_lens,
                     float* __restrict__ probs, float* __restrict__ ctx, bf16* __restrict__ ctx_hi, bf16* __restrict__ ctx_lo,
-                    long ld_ctx, int T, int H, float scale, float drop_p, unsigned long long seed, int vec) {
+                    long ld_ctx, int T, int H, float scale, float drop_p, unsigned long long seed, int vec, uint32_t drop_thr) {
     using S = Smem<D>;
     constexpr int PITCH = S::PITCH;
     extern __shared__ __align__(16) uint8_t smem_raw[];
@@ -225,27 +228,44 @@ attn_fwd_mma_kernel(const float* __restrict__ qkv, long ld, int q_off, int k_off
     const float drop_scale = 1.0f / (1.0f - drop_p);
     const int r0 = row0 + g, r1 = row0 + g + 8;
     const long prow0 = (((long)b * H + h) * T + r0) * T, prow1 = (((long)b * H + h) * T + r1) * T;
+    const uint32_t thr = drop_thr, s_lo = (uint32_t)seed, s_hi = (uint32_t)(seed >> 32);
+    const bool pair_ok = (T & 1) == 0;   // (row * T + even column) is 8-byte aligned: one store per column pair
 #pragma unroll
     for (int nt = 0; nt < 16; ++nt) {
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-            const int col = nt * 8 + c2 + e;
-            float p0 = s[nt][e] * inv0, p1 = s[nt][2 + e] * inv1;
-            if (col < T) {
-                if (r0 < T) {
-                    if (probs) probs[prow0 + col] = p0;
-                    if (drop_p > 0.0f)
-                        p0 = hash_uniform(seed, (unsigned long long)(prow0 + col)) < drop_p ? 0.0f : p0 * drop_scale;
+        const int col = nt * 8 + c2;
+        float p00 = s[nt][0] * inv0, p01 = s[nt][1] * inv0, p10 = s[nt][2] * inv1, p11 = s[nt][3] * inv1;
+        if (col < T) {
+            const bool c1 = col + 1 < T;
+            if (r0 < T) {
+                if (probs) {
+                    if (pair_ok) {
+                        *reinterpret_cast<float2*>(probs + prow0 + col) = make_float2(p00, p01);
+                    } else {
+                        probs[prow0 + col] = p00;
+                        if (c1) probs[prow0 + col + 1] = p01;
+                    }
                 }
-                if (r1 < T) {
-                    if (probs) probs[prow1 + col] = p1;
-                    if (drop_p > 0.0f)
-                        p1 = hash_uniform(seed, (unsigned long long)(prow1 + col)) < drop_p ? 0.0f : p1 * drop_scale;
+                if (drop_p > 0.0f) {
+                    p00 = hash_drop(hash_fold((unsigned long long)(prow0 + col)), s_lo, s_hi, thr) ? 0.0f : p00 * drop_scale;
+                    if (c1) p01 = hash_drop(hash_fold((unsigned long long)(prow0 + col + 1)), s_lo, s_hi, thr) ? 0.0f : p01 * drop_scale;
                 }
             }
-            s[nt][e] = p0;
-            s[nt][2 + e] = p1;
+            if (r1 < T) {
+                if (probs) {
+                    if (pair_ok) {
+                        *reinterpret_cast<float2*>(probs + prow1 + col) = make_float2(p10, p11);
+                    } else {
+                        probs[prow1 + col] = p10;
+                        if (c1) probs[prow1 + col + 1] = p11;
+                    }
+                }
+                if (drop_p > 0.0f) {
+                    p10 = hash_drop(hash_fold((unsigned long long)(prow1 + col)), s_lo, s_hi, thr) ? 0.0f : p10 * drop_scale;
+                    if (c1) p11 = hash_drop(hash_fold((unsigned long long)(prow1 + col + 1)), s_lo, s_hi, thr) ? 0.0f : p11 * drop_scale;
+                }
+            }
         }
+        s[nt][0] = p00, s[nt][1] = p01, s[nt][2] = p10, s[nt][3] = p11;
     }
     // ---- O = P V ----
     float o[D / 8][4];
@@ -277,10 +297,7 @@ attn_fwd_mma_kernel(const float* __restrict__ qkv, long ld, int q_off, int k_off
             if (r >= T) continue;
             const float x = o[nt][2 * hr], y = o[nt][2 * hr + 1];
             const long off = ((long)b * T + r) * ld_ctx + h * D + nt * 8 + c2;
-            if (ctx) {
-                ctx[off] = x;
-                ctx[off + 1] = y;
-            }
+            if (ctx) *reinterpret_cast<float2*>(ctx + off) = make_float2(x, y);   // ld_ctx, h * D, c2 are even
             if (ctx_hi) {
                 uint32_t hh, ll;
                 pack_split(x, y, hh, ll);
@@ -304,8 +321,7 @@ __device__ __forceinline__ void store_dtile(const float (&acc)[D / 8][4], float*
             if (r >= T) continue;
             const float x = acc[nt][2 * hr], y = acc[nt][2 * hr + 1];
             const long off = (long)r * ld + nt * 8 + c2;
-            dst[off] = x;
-            dst[off + 1] = y;
+            *reinterpret_cast<float2*>(dst + off) = make_float2(x, y);   // ld and the column offsets are even
             if (dst_hi) {
                 uint32_t hh, ll;
                 pack_split(x, y, hh, ll);
@@ -361,7 +377,7 @@ __global__ void __launch_bounds__(THREADS, 1)
 attn_bwd_mma_kernel(const float* __restrict__ qkv, long ld, int q_off, int k_off, int v_off, const float* __restrict__ probs,
                     const float* __restrict__ dctx, long ld_ctx, float* __restrict__ dqkv, bf16* __restrict__ dqkv_hi,
                     bf16* __restrict__ dqkv_lo, int T, int H, float scale, float drop_p, unsigned long long seed, int vec,
-                    int vec_ctx) {
+                    int vec_ctx, uint32_t drop_thr) {
     using S = Smem<D>;
     constexpr int PITCH = S::PITCH, PP = S::PPITCH;
     extern __shared__ __align__(16) uint8_t smem_raw[];
@@ -410,32 +426,47 @@ attn_bwd_mma_kernel(const float* __restrict__ qkv, long ld, int q_off, int k_off
         const long prow0 = (((long)b * H + h) * T + r0) * T, prow1 = (((long)b * H + h) * T + r1) * T;
         float delta0 = 0.0f, delta1 = 0.0f;
         float pd[16][4];
-        // all probability loads first (64 per thread, independent), then the mask / delta arithmetic
+        // all probability loads first (independent; one 8-byte load per column pair when the rows are 8-byte aligned),
+        // then the mask / delta arithmetic
+        const bool pair_ok = (T & 1) == 0;
 #pragma unroll
         for (int nt = 0; nt < 16; ++nt) {
+            const int col = nt * 8 + c2;
+            float2 a0 = make_float2(0.0f, 0.0f), a1 = make_float2(0.0f, 0.0f);
+            if (col < T) {
+                if (pair_ok) {
+                    if (r0 < T) a0 = *reinterpret_cast<const float2*>(probs + prow0 + col);
+                    if (r1 < T) a1 = *reinterpret_cast<const float2*>(probs + prow1 + col);
+                } else {
+                    if (r0 < T) a0 = make_float2(probs[prow0 + col], col + 1 < T ? probs[prow0 + col + 1] : 0.0f);
+                    if (r1 < T) a1 = make_float2(probs[prow1 + col], col + 1 < T ? probs[prow1 + col + 1] : 0.0f);
+                }
+            }
+            pd[nt][0] = a0.x, pd[nt][1] = a0.y, pd[nt][2] = a1.x, pd[nt][3] = a1.y;
+        }
+        // keep / drop decision of every entry ONCE (bit nt * 4 + j of `keep`); it is used for dP and for the dropped P
+        unsigned long long keep = ~0ull;
+        if (drop_p > 0.0f) {
+            const uint32_t s_lo = (uint32_t)seed, s_hi = (uint32_t)(seed >> 32);
 #pragma unroll
-            for (int e = 0; e < 2; ++e) {
-                const int col = nt * 8 + c2 + e;
-                pd[nt][e] = (col < T && r0 < T) ? probs[prow0 + col] : 0.0f;
-                pd[nt][2 + e] = (col < T && r1 < T) ? probs[prow1 + col] : 0.0f;
+            for (int nt = 0; nt < 16; ++nt) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int col = nt * 8 + c2 + (j & 1);
+                    const bool in = col < T && ((j >> 1) ? r1 : r0) < T;
+                    const long off = ((j >> 1) ? prow1 : prow0) + col;
+                    if (in && hash_drop(hash_fold((unsigned long long)off), s_lo, s_hi, drop_thr)) keep &= ~(1ull << (nt * 4 + j));
+                }
             }
         }
 #pragma unroll
         for (int nt = 0; nt < 16; ++nt) {
 #pragma unroll
-            for (int e = 0; e < 2; ++e) {
-                const int col = nt * 8 + c2 + e;
-                const float p0 = pd[nt][e], p1 = pd[nt][2 + e];   // undropped P for now
-                float m0 = 1.0f, m1 = 1.0f;
-                if (drop_p > 0.0f && col < T) {
-                    if (r0 < T) m0 = hash_uniform(seed, (unsigned long long)(prow0 + col)) < drop_p ? 0.0f : drop_scale;
-                    if (r1 < T) m1 = hash_uniform(seed, (unsigned long long)(prow1 + col)) < drop_p ? 0.0f : drop_scale;
-                }
-                const float d0 = ds[nt][e] * m0, d1 = ds[nt][2 + e] * m1;
-                delta0 += d0 * p0;
-                delta1 += d1 * p1;
-                ds[nt][e] = d0;
-                ds[nt][2 + e] = d1;
+            for (int j = 0; j < 4; ++j) {
+                const float m = (keep >> (nt * 4 + j)) & 1ull ? drop_scale : 0.0f;
+                const float d = ds[nt][j] * (drop_p > 0.0f ? m : 1.0f);
+                if (j < 2) delta0 += d * pd[nt][j]; else delta1 += d * pd[nt][j];
+                ds[nt][j] = d;
             }
         }
         delta0 += __shfl_xor_sync(0xffffffffu, delta0, 1);
@@ -445,21 +476,19 @@ attn_bwd_mma_kernel(const float* __restrict__ qkv, long ld, int q_off, int k_off
 #pragma unroll
         for (int nt = 0; nt < 16; ++nt) {
 #pragma unroll
-            for (int e = 0; e < 2; ++e) {
-                const int col = nt * 8 + c2 + e;
-                const float p0 = pd[nt][e], p1 = pd[nt][2 + e];
-                ds[nt][e] = p0 * (ds[nt][e] - delta0) * scale;
-                ds[nt][2 + e] = p1 * (ds[nt][2 + e] - delta1) * scale;
-                if (drop_p > 0.0f) {
-                    // p == 0 outside the matrix, so the hash is only evaluated for real entries
-                    if (p0 != 0.0f)
-                        pd[nt][e] = hash_uniform(seed, (unsigned long long)(prow0 + col)) < drop_p ? 0.0f : p0 * drop_scale;
-                    if (p1 != 0.0f)
-                        pd[nt][2 + e] = hash_uniform(seed, (unsigned long long)(prow1 + col)) < drop_p ? 0.0f : p1 * drop_scale;
-                }
+            for (int j = 0; j < 4; ++j) {
+                const float pv = pd[nt][j];
+                ds[nt][j] = pv * (ds[nt][j] - (j < 2 ? delta0 : delta1)) * scale;
+                if (drop_p > 0.0f) pd[nt][j] = (keep >> (nt * 4 + j)) & 1ull ? pv * drop_scale : 0.0f;
             }
         }
         store_ptile(pd, Ph, Pl, PP, row0, lane);
+    }
+    // Q (needed for dK at the end) is read into registers now - the 64 registers of the probability tile are free -
+    // so that its memory round trip runs under the dQ MMAs instead of after them
+    TileRegs<D> rq;
+    load_tile_regs<D>(base + q_off, ld, T, vec != 0, rq);
+    if (active) {
         // ---- dQ = dS K ----
         float acc[D / 8][4];
 #pragma unroll
@@ -486,7 +515,7 @@ attn_bwd_mma_kernel(const float* __restrict__ qkv, long ld, int q_off, int k_off
                        dqkv_lo ? dqkv_lo + obase + q_off : nullptr, ld, row0, T, lane);
     }
     __syncthreads();   // dropped P complete; V and K tiles are dead
-    load_split_tile<D>(base + q_off, ld, T, 1.0f, Vh, Vl, vec);   // Q (unscaled) into the V region
+    store_split_regs<D>(rq, 1.0f, Vh, Vl);   // Q (unscaled) into the V region
     // ---- dV = Pdrop^T dO (this warp: keys row0 .. row0 + 15) ----
     if (active) {
         float acc[D / 8][4];
@@ -517,7 +546,7 @@ int launch_fwd(const float* qkv, long ld, int q_off, int k_off, int v_off, const
         attr = true;
     }
     kern<<<B * H, THREADS, Smem<D>::FWD_BYTES, stream>>>(qkv, ld, q_off, k_off, v_off, kv_lens, probs, ctx, ctx_hi, ctx_lo, ld_ctx,
-                                                         T, H, scale, drop_p, seed, vec);
+                                                         T, H, scale, drop_p, seed, vec, drop_threshold(drop_p));
     B2T_CHECK_LAUNCH("b2t_attention_fwd (mma)");
     return 0;
 }
@@ -533,7 +562,7 @@ int launch_bwd(const float* qkv, long ld, int q_off, int k_off, int v_off, const
         attr = true;
     }
     kern<<<B * H, THREADS, Smem<D>::BWD_BYTES, stream>>>(qkv, ld, q_off, k_off, v_off, probs, dctx, ld_ctx, dqkv, dqkv_hi, dqkv_lo,
-                                                         T, H, scale, drop_p, seed, vec, vec_ctx);
+                                                         T, H, scale, drop_p, seed, vec, vec_ctx, drop_threshold(drop_p));
     B2T_CHECK_LAUNCH("b2t_attention_bwd (mma)");
     return 0;
 }
