@@ -88,6 +88,11 @@ __device__ __forceinline__ void mma_bf16_16816(float* c, const uint32_t* a, uint
         : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
         : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
+__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                 : "r"(addr));
+}
 __device__ __forceinline__ uint32_t pack_bf16(bf16 lo_half, bf16 hi_half) {
     __nv_bfloat162 p = __halves2bfloat162(lo_half, hi_half);
     return *reinterpret_cast<uint32_t*>(&p);
@@ -124,13 +129,21 @@ struct GruFwdArgs {
     unsigned long long seed;
 };
 
+// Warp tiling of the step's matvec gh[16, 96] = h[16, H] . W_slice^T over the 12 warps.  With one warp per 8 gate
+// columns and all of K, every warp read the whole h (hi + lo, 32 KB at H = 512): 12 x 32 KB + 96 KB of W lo = 480 KB
+// per step against the 128 B/clk shared-memory port = 1.9 us of a 4.8 us step (ncu: the matvec sat on stall_mio).
+// KG = 4 splits K four ways instead: warp (gate, kg) owns the gate's 32 columns x a quarter of K, reads a quarter of h
+// (96 KB per step in total) and leaves a partial sum per K group that the gate phase adds up.
 template <int H>
 struct FwdSmem {
     static constexpr int KSTEPS = H / 16;
+    static constexpr int KG = KSTEPS % 4 == 0 ? 4 : 1;   // K groups
+    static constexpr int NT_W = KG;                        // 8-column tiles per warp (4 x 8 = the gate's 32 columns)
+    static constexpr int KS_W = KSTEPS / KG;               // k-steps per warp
     static constexpr int HP = H + 8;   // padded bf16 pitch: conflict-free A-fragment loads
     static constexpr size_t WLO = (size_t)12 * KSTEPS * 32 * 8;
     static constexpr size_t HBUF = (size_t)2 * 2 * RB * HP * 2;
-    static constexpr size_t GH = (size_t)RB * (NCOL + 1) * 4;
+    static constexpr size_t GH = (size_t)KG * RB * (NCOL + 1) * 4;
     static constexpr size_t HOWN = (size_t)RB * U * 4;
     static constexpr size_t STAGE = (size_t)2 * RB * U * 2;
     static constexpr size_t TOTAL = WLO + HBUF + GH + HOWN + STAGE;
@@ -156,22 +169,33 @@ __global__ void __launch_bounds__(384, 1) gru_fwd_kernel(const GruFwdArgs p) {
     const long M = (long)p.B * p.T;
     const int T = p.T;
 
-    // ---- resident weights: this warp's 8 gate columns, all K ---------------------------------
-    const int gate = warp >> 2, ntile = warp & 3;
-    uint32_t bhi[KSTEPS][2];
+    // ---- resident weights: this warp's gate columns x its K range --------------------------------
+    constexpr int KG = S::KG, NT_W = S::NT_W, KS_W = S::KS_W;
+    const int gate = warp >> 2, sub = warp & 3;
+    const int kg = KG == 4 ? sub : 0;            // K group
+    const int nt0 = KG == 4 ? 0 : sub;           // first 8-column tile of the gate's 32 columns
+    uint32_t bhi[KS_W][NT_W][2];
     {
-        const int col = gate * H + u0 + ntile * 8 + g;   // row of W_hh
-        const float* wr = p.w_hh + ((long)dir * 3 * H + col) * H;
 #pragma unroll
-        for (int ks = 0; ks < KSTEPS; ++ks) {
-            uint32_t l0, l1;
-            split_pair(wr[ks * 16 + 2 * tq], wr[ks * 16 + 2 * tq + 1], bhi[ks][0], l0);
-            split_pair(wr[ks * 16 + 2 * tq + 8], wr[ks * 16 + 2 * tq + 9], bhi[ks][1], l1);
-            wlo[(warp * KSTEPS + ks) * 32 + lane] = make_uint2(l0, l1);
+        for (int nt = 0; nt < NT_W; ++nt) {
+            const int col = gate * H + u0 + (nt0 + nt) * 8 + g;   // row of W_hh
+            const float* wr = p.w_hh + ((long)dir * 3 * H + col) * H + kg * KS_W * 16;
+#pragma unroll
+            for (int ks = 0; ks < KS_W; ++ks) {
+                uint32_t l0, l1;
+                split_pair(wr[ks * 16 + 2 * tq], wr[ks * 16 + 2 * tq + 1], bhi[ks][nt][0], l0);
+                split_pair(wr[ks * 16 + 2 * tq + 8], wr[ks * 16 + 2 * tq + 9], bhi[ks][nt][1], l1);
+                wlo[((warp * KS_W + ks) * NT_W + nt) * 32 + lane] = make_uint2(l0, l1);
+            }
         }
     }
-    const float bias_c0 = p.b_hh[(long)dir * 3 * H + gate * H + u0 + ntile * 8 + 2 * tq];
-    const float bias_c1 = p.b_hh[(long)dir * 3 * H + gate * H + u0 + ntile * 8 + 2 * tq + 1];
+    float bias_c[NT_W][2];
+#pragma unroll
+    for (int nt = 0; nt < NT_W; ++nt) {
+        const long bo = (long)dir * 3 * H + gate * H + u0 + (nt0 + nt) * 8 + 2 * tq;
+        bias_c[nt][0] = kg == 0 ? p.b_hh[bo] : 0.0f;       // the bias is added once, by K group 0
+        bias_c[nt][1] = kg == 0 ? p.b_hh[bo + 1] : 0.0f;
+    }
 
     // ---- initial state ----------------------------------------------------------------------
     for (int i = tid; i < RB * H; i += blockDim.x) {
@@ -218,6 +242,23 @@ __global__ void __launch_bounds__(384, 1) gru_fwd_kernel(const GruFwdArgs p) {
     };
     load_gi(0);
 
+    // push of the new h slice.  Gate warp w (w < 8) computes rows w and w + 8 of the slice, so it also sends them: its 16
+    // sixteen-byte pieces (hi / lo x 2 rows x 4) go to the CS CTAs of the cluster, lane -> piece lane & 15, destinations
+    // (lane >> 4), + 2, + 4, ...  Staging is warp-private (a __syncwarp instead of a CTA barrier on the critical path),
+    // and the cluster addresses are step-invariant (buffer 1 = buffer 0 + a constant): mapa runs once, here.
+    constexpr int PER = CS / 2 > 0 ? CS / 2 : 1;
+    const int pwhich = (lane & 15) >> 3, prow = warp + 8 * ((lane >> 2) & 1), pch = lane & 3;
+    uint32_t rdst[PER], rbar[PER];
+    if (warp < 8) {
+        const uint32_t dst0 = (uint32_t)__cvta_generic_to_shared(hbuf + pwhich * RB * HP + prow * HP + u0 + pch * 8);
+#pragma unroll
+        for (int i = 0; i < PER; ++i) {
+            const int dest = (lane >> 4) + 2 * i;
+            rdst[i] = map_to_cta(dst0, (uint32_t)(dest < CS ? dest : 0));
+            rbar[i] = map_to_cta(hbar0, (uint32_t)(dest < CS ? dest : 0));
+        }
+    }
+
     for (int s = 0; s < T; ++s) {
         const int t = dir == 0 ? s : T - 1 - s;
         const int cur = s & 1;
@@ -230,29 +271,35 @@ __global__ void __launch_bounds__(384, 1) gru_fwd_kernel(const GruFwdArgs p) {
         {
             const bf16* hh = hbuf + (cur * 2 + 0) * RB * HP;
             const bf16* hl = hbuf + (cur * 2 + 1) * RB * HP;
-            float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f}, acc2[4] = {0.f, 0.f, 0.f, 0.f};
+            // lanes 0-15: rows 0-15 at k0, lanes 16-31: the same rows at k0 + 8 -> registers a0..a3 of m16n8k16
+            const uint32_t hh_addr = (uint32_t)__cvta_generic_to_shared(hh + (lane & 15) * HP + (lane >> 4) * 8);
+            const uint32_t hl_addr = (uint32_t)__cvta_generic_to_shared(hl + (lane & 15) * HP + (lane >> 4) * 8);
+            float acc[NT_W][4];
 #pragma unroll
-            for (int ks = 0; ks < KSTEPS; ++ks) {
+            for (int nt = 0; nt < NT_W; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.0f;
+#pragma unroll
+            for (int ks = 0; ks < KS_W; ++ks) {
+                // one ldmatrix.x4 per operand half (registers a0..a3 of m16n8k16)
                 uint32_t ah[4], al[4];
-                const int k0 = ks * 16 + 2 * tq;
-                ah[0] = *reinterpret_cast<const uint32_t*>(hh + g * HP + k0);
-                ah[1] = *reinterpret_cast<const uint32_t*>(hh + (g + 8) * HP + k0);
-                ah[2] = *reinterpret_cast<const uint32_t*>(hh + g * HP + k0 + 8);
-                ah[3] = *reinterpret_cast<const uint32_t*>(hh + (g + 8) * HP + k0 + 8);
-                al[0] = *reinterpret_cast<const uint32_t*>(hl + g * HP + k0);
-                al[1] = *reinterpret_cast<const uint32_t*>(hl + (g + 8) * HP + k0);
-                al[2] = *reinterpret_cast<const uint32_t*>(hl + g * HP + k0 + 8);
-                al[3] = *reinterpret_cast<const uint32_t*>(hl + (g + 8) * HP + k0 + 8);
-                const uint2 bl = wlo[(warp * KSTEPS + ks) * 32 + lane];
-                mma_bf16_16816(acc0, ah, bhi[ks][0], bhi[ks][1]);
-                mma_bf16_16816(acc1, ah, bl.x, bl.y);
-                mma_bf16_16816(acc2, al, bhi[ks][0], bhi[ks][1]);
+                ldsm_x4(ah, hh_addr + (uint32_t)((kg * KS_W + ks) * 32));
+                ldsm_x4(al, hl_addr + (uint32_t)((kg * KS_W + ks) * 32));
+#pragma unroll
+                for (int nt = 0; nt < NT_W; ++nt) {
+                    const uint2 bl = wlo[((warp * KS_W + ks) * NT_W + nt) * 32 + lane];
+                    mma_bf16_16816(acc[nt], ah, bhi[ks][nt][0], bhi[ks][nt][1]);
+                    mma_bf16_16816(acc[nt], ah, bl.x, bl.y);
+                    mma_bf16_16816(acc[nt], al, bhi[ks][nt][0], bhi[ks][nt][1]);
+                }
             }
-            const int cidx = warp * 8 + 2 * tq;   // == gate*32 + ntile*8 + n
-            gh_s[g * (NCOL + 1) + cidx] = acc0[0] + acc1[0] + acc2[0] + bias_c0;
-            gh_s[g * (NCOL + 1) + cidx + 1] = acc0[1] + acc1[1] + acc2[1] + bias_c1;
-            gh_s[(g + 8) * (NCOL + 1) + cidx] = acc0[2] + acc1[2] + acc2[2] + bias_c0;
-            gh_s[(g + 8) * (NCOL + 1) + cidx + 1] = acc0[3] + acc1[3] + acc2[3] + bias_c1;
+            float* ghp = gh_s + kg * RB * (NCOL + 1);
+#pragma unroll
+            for (int nt = 0; nt < NT_W; ++nt) {
+                const int cidx = gate * U + (nt0 + nt) * 8 + 2 * tq;
+                ghp[g * (NCOL + 1) + cidx] = acc[nt][0] + bias_c[nt][0];
+                ghp[g * (NCOL + 1) + cidx + 1] = acc[nt][1] + bias_c[nt][1];
+                ghp[(g + 8) * (NCOL + 1) + cidx] = acc[nt][2] + bias_c[nt][0];
+                ghp[(g + 8) * (NCOL + 1) + cidx + 1] = acc[nt][3] + bias_c[nt][1];
+            }
         }
         __syncthreads();
         // ---- gates for the own 32 units (brain_feature_extractor.py nn.GRU equations, App. A.2) ----
@@ -261,9 +308,14 @@ __global__ void __launch_bounds__(384, 1) gru_fwd_kernel(const GruFwdArgs p) {
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
                 const int row = gr + 8 * j;
-                const float gh_r = gh_s[row * (NCOL + 1) + gu];
-                const float gh_z = gh_s[row * (NCOL + 1) + U + gu];
-                const float gh_n = gh_s[row * (NCOL + 1) + 2 * U + gu];
+                float gh_r = 0.0f, gh_z = 0.0f, gh_n = 0.0f;
+#pragma unroll
+                for (int q = 0; q < KG; ++q) {   // partial sums of the K groups
+                    const float* ghq = gh_s + (q * RB + row) * (NCOL + 1);
+                    gh_r += ghq[gu];
+                    gh_z += ghq[U + gu];
+                    gh_n += ghq[2 * U + gu];
+                }
                 const float r = sigmoid_acc(gi_v[j][0] + gh_r);
                 const float z = sigmoid_acc(gi_v[j][1] + gh_z);
                 const float n = tanhf(gi_v[j][2] + r * gh_n);
@@ -277,20 +329,20 @@ __global__ void __launch_bounds__(384, 1) gru_fwd_kernel(const GruFwdArgs p) {
                 rv[j] = r, zv[j] = z, nv[j] = n, ghnv[j] = gh_n, hpv[j] = hp, hnv[j] = hn;
             }
         }
-        load_gi(s + 1);
-        __syncthreads();
         // ---- push the new h slice (bf16 hi, lo) to every CTA of the cluster (not needed after the last step) ----
-        if (s + 1 < T) {
+        // No CTA barrier: gh_s is rewritten by the next step's matvec only after hbar[nxt] completed, which needs this
+        // CTA's own pushes, i.e. every gate warp is past its reads of gh_s.
+        if (warp < 8 && s + 1 < T) {
+            __syncwarp();
             const int nxt = cur ^ 1;
-            for (int idx = tid; idx < 128 * CS; idx += blockDim.x) {
-                const int dest = idx >> 7, c = idx & 127;
-                const int which = c >> 6, row = (c & 63) >> 2, ch = c & 3;
-                const uint4 v = *reinterpret_cast<const uint4*>(stage + which * RB * U + row * U + ch * 8);
-                bf16* dst = hbuf + (nxt * 2 + which) * RB * HP + row * HP + u0 + ch * 8;
-                st_async_v4(map_to_cta((uint32_t)__cvta_generic_to_shared(dst), (uint32_t)dest), v,
-                            map_to_cta(hbar0 + 8 * nxt, (uint32_t)dest));
+            const uint4 v = *reinterpret_cast<const uint4*>(stage + pwhich * RB * U + prow * U + pch * 8);
+#pragma unroll
+            for (int i = 0; i < PER; ++i) {
+                if ((lane >> 4) + 2 * i < CS)
+                    st_async_v4(rdst[i] + (uint32_t)(nxt * 2 * RB * HP * 2), v, rbar[i] + (uint32_t)(8 * nxt));
             }
         }
+        load_gi(s + 1);
         // ---- outputs and saved-for-backward values (off the recurrence's critical path) ----
         if (tid < 256) {
 #pragma unroll
@@ -495,8 +547,8 @@ __global__ void __launch_bounds__(BwdSmem<H>::THREADS, 1) gru_bwd_kernel(const G
         __syncthreads();
         // ---- partial dh[16, units of CTA `warp`] = dgh[16, 96 own columns] . W_slice, scattered to its owner ----
         if (warp < CS) {
-            const bf16* ah_ = aop;
-            const bf16* al_ = aop + RB * AP;
+            const uint32_t ah_addr = (uint32_t)__cvta_generic_to_shared(aop + (lane & 15) * AP + (lane >> 4) * 8);
+            const uint32_t al_addr = (uint32_t)__cvta_generic_to_shared(aop + RB * AP + (lane & 15) * AP + (lane >> 4) * 8);
             float acc[4][4];
 #pragma unroll
             for (int nt = 0; nt < 4; ++nt)
@@ -505,15 +557,8 @@ __global__ void __launch_bounds__(BwdSmem<H>::THREADS, 1) gru_bwd_kernel(const G
 #pragma unroll
             for (int ks = 0; ks < 6; ++ks) {
                 uint32_t ah[4], al[4];
-                const int k0 = ks * 16 + 2 * tq;
-                ah[0] = *reinterpret_cast<const uint32_t*>(ah_ + g * AP + k0);
-                ah[1] = *reinterpret_cast<const uint32_t*>(ah_ + (g + 8) * AP + k0);
-                ah[2] = *reinterpret_cast<const uint32_t*>(ah_ + g * AP + k0 + 8);
-                ah[3] = *reinterpret_cast<const uint32_t*>(ah_ + (g + 8) * AP + k0 + 8);
-                al[0] = *reinterpret_cast<const uint32_t*>(al_ + g * AP + k0);
-                al[1] = *reinterpret_cast<const uint32_t*>(al_ + (g + 8) * AP + k0);
-                al[2] = *reinterpret_cast<const uint32_t*>(al_ + g * AP + k0 + 8);
-                al[3] = *reinterpret_cast<const uint32_t*>(al_ + (g + 8) * AP + k0 + 8);
+                ldsm_x4(ah, ah_addr + (uint32_t)(ks * 32));
+                ldsm_x4(al, al_addr + (uint32_t)(ks * 32));
 #pragma unroll
                 for (int nt = 0; nt < 4; ++nt) {
                     const uint2 bl = wlo[((warp * 4 + nt) * 6 + ks) * 32 + lane];
