@@ -515,6 +515,10 @@ def gemm_roofline(model, opt, batch, step, peaks, workload_key="base"):
                      "B" + ("mn" if b.mn_major else "k"), "sk%d" % kw.get("split_k", 1), "bn%d" % kw.get("block_n", 0),
                      "+".join(x for x in ("out_f32", "out_pre", "out_hi", "bias", "residual", "aux", "colsum", "act") if kw.get(x) is not None))))
     ops.gemm = timed_gemm
+    # every launch is timed on the stream it runs on, one at a time: the weight-gradient side stream (which overlaps
+    # GEMMs of two streams in the product's step) is switched off for this measuring step
+    side_was = engine.Engine._side_enabled
+    engine.Engine._side_enabled = False
     try:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         step(batch)
@@ -525,6 +529,7 @@ def gemm_roofline(model, opt, batch, step, peaks, workload_key="base"):
         torch.cuda.synchronize()
     finally:
         ops.gemm = real
+        engine.Engine._side_enabled = side_was
     t_ms = sum(r[0].elapsed_time(r[1]) for r in rec)
     flops = sum(r[2] for r in rec)
     table = os.environ.get("B2T_GEMM_TABLE")

@@ -60,6 +60,11 @@ def _queue_backward_callback(fn) -> bool:
         return False
 
 
+def _side_streams():
+    from . import ops as _ops
+    return _ops.SIDE_STREAMS if torch.cuda.is_available() else ()
+
+
 class _BucketBase:
     def __init__(self, process_group, overlap: bool):
         self.group = process_group
@@ -80,11 +85,15 @@ class _BucketBase:
             return None
         if self.overlap:
             self.stream.wait_stream(torch.cuda.current_stream())
+            for st in _side_streams():      # weight gradients are produced on the engine's second stream
+                self.stream.wait_stream(st)
             with torch.cuda.stream(self.stream):
                 if self._avg:
                     return dist.all_reduce(flat, op=dist.ReduceOp.AVG, group=self.group, async_op=True)
                 flat.div_(self.world)
                 return dist.all_reduce(flat, group=self.group, async_op=True)
+        for st in _side_streams():
+            torch.cuda.current_stream().wait_stream(st)
         if self._avg:
             dist.all_reduce(flat, op=dist.ReduceOp.AVG, group=self.group)
         else:
@@ -242,6 +251,8 @@ class GradientBuckets(_BucketBase):
             return
         if self.overlap:
             self.stream.wait_stream(torch.cuda.current_stream())
+            for st in _side_streams():      # weight gradients are produced on the engine's second stream
+                self.stream.wait_stream(st)
             with torch.cuda.stream(self.stream):
                 flat = torch.cat([g.reshape(-1) for g in grads])
         else:

@@ -15,6 +15,8 @@ from __future__ import annotations
 import math
 from typing import Dict, List, Optional
 
+import os
+
 import torch
 
 from . import ops as _real_ops
@@ -195,6 +197,8 @@ class Engine:
     def finalize_grads(self, G: Dict[str, Tensor], only=None) -> None:
         """End of an autograd node: every gradient that was not produced in its arena slot is copied there, so that
         .grad tensors, all-reduce buckets and optimizer tables always see the slot."""
+        if only is None:
+            self.join_side()      # end of the node: autograd and the optimizer read the gradients on this stream
         if not self._arena_on:
             return
         for k in (list(G) if only is None else only):
@@ -204,6 +208,7 @@ class Engine:
             slot = self.grad_arena.view(k)
             if slot is None or self.grad_arena.owns(k, v):
                 continue
+            self.join_side()      # a gradient produced outside its slot may have come from the weight-gradient stream
             slot.copy_(v.view(slot.shape) if v.is_contiguous() else v.reshape(slot.shape))
             G[k] = slot
             self.arena_copies += 1
@@ -248,9 +253,54 @@ class Engine:
                 out = self._gout(name, (N, K), dy_hi.device, zero=sk > 1)
             else:
                 out = ops.zeros(N, K, device=dy_hi.device) if sk > 1 else torch.empty(N, K, dtype=torch.float32, device=dy_hi.device)
+        side = self._side()
+        if side is None:
+            ops.gemm(ops.mnmajor(dy_hi, dy_lo), ops.mnmajor(x_hi, x_lo), m_per_batch=N, n=K, k=M, out_f32=out,
+                     atomic=sk > 1, split_k=sk, alpha=alpha)
+            return out
+        # Weight gradients are off the backward pass's critical path (nothing reads them before the node ends): they go
+        # to a second stream, so that their CTAs fill the SMs the data-gradient chain leaves idle in the ramp-up and
+        # the last-tile tail of every persistent GEMM.  The side stream waits for everything queued so far (the
+        # producer of dY, the zeroing of the slot); operands are kept from reuse until the side stream has read them.
+        side.wait_stream(self._main_stream())
         ops.gemm(ops.mnmajor(dy_hi, dy_lo), ops.mnmajor(x_hi, x_lo), m_per_batch=N, n=K, k=M, out_f32=out,
-                 atomic=sk > 1, split_k=sk, alpha=alpha)
+                 atomic=sk > 1, split_k=sk, alpha=alpha, on_stream=side.cuda_stream)
+        for t in ((dy_hi, dy_lo, x_hi, x_lo) if self._arena_on else (dy_hi, dy_lo, x_hi, x_lo, out)):   # arena slots persist
+            if t is not None:
+                t.record_stream(side)
+        self._side_dirty = True
         return out
+
+    # ------------------------------------------------------------------------------------------
+    # weight-gradient stream (B2T_WGRAD_STREAM=0 switches it off)
+    # ------------------------------------------------------------------------------------------
+    side_stream = None
+    _side_dirty = False
+    _side_enabled = os.environ.get("B2T_WGRAD_STREAM", "1") == "1"
+
+    def _side(self):
+        if not self._side_enabled or ops is not _real_ops or not torch.cuda.is_available():
+            return None     # the CPU test-suite runs the schedule on an emulator of the C ABI: one stream
+        if self.side_stream is None:
+            self.side_stream = torch.cuda.Stream()
+            _real_ops.SIDE_STREAMS.append(self.side_stream)
+        return self.side_stream
+
+    _main = None
+
+    def _main_stream(self):
+        """torch.cuda.current_stream() costs ~18 us of Python per call; the stream object is cached per raw handle"""
+        raw = ops._lib.raw_stream()
+        m = self._main
+        if m is None or m[0] != raw:
+            m = self._main = (raw, torch.cuda.current_stream())
+        return m[1]
+
+    def join_side(self) -> None:
+        """the current stream waits for every weight gradient issued so far"""
+        if self._side_dirty:
+            self._main_stream().wait_stream(self.side_stream)
+            self._side_dirty = False
 
     def _dgrad(self, dy_hi, dy_lo, w_hl, M, N, K, **kw):
         """dX[M,K] = dY[M,N] . W[N,K]"""

@@ -164,18 +164,48 @@ def zeros(*shape, device) -> Tensor:
     return _ARENA.take(tuple(shape), device)
 
 
+SIDE_STREAMS = []        # streams other than the launching one that write gradients (engine weight-gradient stream): dist waits on them
 STREAM_K = False         # stream-K schedule switch: off by default (round-1 measurements: slower than whole-tile waves at K <= 4096)
 _SK_WS = {}
 
 
-def _sk_workspace(device) -> Tensor:
+def _sk_workspace(device, raw=None) -> Tensor:
     """Per (device, stream) stream-K scratch, zeroed once (b2t_gemm leaves its flags at zero)."""
-    key = (device.index, _lib.raw_stream())
+    key = (device.index, _lib.raw_stream() if raw is None else raw)
     ws = _SK_WS.get(key)
     if ws is None:
         ws = torch.zeros(int(lib().b2t_gemm_workspace_bytes()), dtype=torch.uint8, device=device)
         _SK_WS[key] = ws
     return ws
+
+
+# b2t_gemm_args is filled with ONE struct.pack_into call into a reused buffer: ~45 ctypes attribute assignments and a
+# dozen c_void_p objects per call were ~10 us of the ~20 us host cost of a GEMM launch, in a training step whose issue
+# time (1300 launches) had become what bounds it.  The format string is derived from the ctypes mirror, whose layout
+# tests/test_abi_cpu.py checks against the C compiler.
+import struct as _struct
+
+_GEMM_FIELDS = [f[0] for f in GemmArgs._fields_]
+_CT2FMT = {ctypes.c_void_p: "Q", ctypes.c_int64: "q", ctypes.c_int32: "i", ctypes.c_float: "f", ctypes.c_uint64: "Q"}
+_GEMM_FMT = "".join(_CT2FMT[f[1]] for f in GemmArgs._fields_)
+_GEMM_STRUCT = _struct.Struct("@" + _GEMM_FMT)
+# native alignment gives the packed values the offsets of the ctypes Structure (= the C compiler's)
+assert _GEMM_STRUCT.size <= ctypes.sizeof(GemmArgs)
+assert all(getattr(GemmArgs, name).offset == _struct.calcsize("@" + _GEMM_FMT[:i] + "0" + _GEMM_FMT[i])
+           for i, name in enumerate(_GEMM_FIELDS))
+assert _GEMM_FIELDS == [
+    "a_hi", "a_lo", "b_hi", "b_lo", "a_d0", "a_d1", "a_d2", "a_s1", "a_s2", "b_d0", "b_d1", "b_d2", "b_s1", "b_s2",
+    "a_mn_major", "b_mn_major", "k_spans_batches", "m_per_batch", "batches", "n", "k", "a_batched", "b_batched",
+    "b_batch_idx", "c_batch_idx", "out_f32", "out_pre", "out_hi", "out_lo", "ldc", "c_batch_stride", "bias", "residual",
+    "aux", "colsum", "act", "aux_mode", "atomic", "split_k", "alpha", "block_n", "drop_p", "drop_seed",
+    "bias_batch_stride", "out_scale", "sk_workspace", "sk_workspace_bytes", "stream_k", "cta_group"]   # order gemm() packs in
+_GEMM_BUF = ctypes.create_string_buffer(ctypes.sizeof(GemmArgs))
+_GEMM_BUF_PTR = ctypes.c_void_p(ctypes.addressof(_GEMM_BUF))
+_B2T_GEMM = None
+
+
+def _dp(t) -> int:
+    return 0 if t is None else t.data_ptr()
 
 
 def gemm(a: Operand, b: Operand, *, m_per_batch: int, n: int, k: int, batches: int = 1,
@@ -187,39 +217,33 @@ def gemm(a: Operand, b: Operand, *, m_per_batch: int, n: int, k: int, batches: i
          alpha: float = 1.0, k_spans_batches: bool = False, a_batched: bool = False, b_batched: bool = False,
          b_batch_idx: Optional[Tensor] = None, c_batch_idx: Optional[Tensor] = None, block_n: int = 0,
          drop_p: float = 0.0, drop_seed: int = 0, bias_batch_stride: int = 0, out_scale: float = 1.0,
-         stream_k: int = 0, cta_group: int = 0) -> None:
-    """D = epilogue(alpha * A . B^T) on the tcgen05 GEMM (see b2t_gemm in include/b2t_sm100.h)."""
+         stream_k: int = 0, cta_group: int = 0, on_stream: Optional[int] = None) -> None:
+    """D = epilogue(alpha * A . B^T) on the tcgen05 GEMM (see b2t_gemm in include/b2t_sm100.h).
+    on_stream: raw cudaStream_t to launch on instead of torch's current stream (the engine's weight-gradient stream)."""
+    global _B2T_GEMM
     _lib.ensure_device()
-    g = GemmArgs()
+    if _B2T_GEMM is None:
+        _B2T_GEMM = lib().b2t_gemm
+    sk_ws, sk_bytes, sk = 0, 0, -1
     if STREAM_K or stream_k > 0:
-        ws = _sk_workspace(a.hi.device)
-        g.sk_workspace, g.sk_workspace_bytes, g.stream_k = ptr(ws), ws.numel(), stream_k
-    else:
-        g.stream_k = -1
-    g.a_hi, g.a_lo, g.b_hi, g.b_lo = ptr(a.hi), ptr(a.lo), ptr(b.hi), ptr(b.lo)
-    g.a_d0, g.a_d1, g.a_d2, g.a_s1, g.a_s2 = a.d0, a.d1, a.d2, a.s1, a.s2
-    g.b_d0, g.b_d1, g.b_d2, g.b_s1, g.b_s2 = b.d0, b.d1, b.d2, b.s1, b.s2
-    g.a_mn_major, g.b_mn_major = int(a.mn_major), int(b.mn_major)
-    g.k_spans_batches = int(k_spans_batches)
-    g.m_per_batch, g.batches, g.n, g.k = m_per_batch, batches, n, k
-    g.a_batched, g.b_batched = int(a_batched), int(b_batched)
-    g.b_batch_idx, g.c_batch_idx = ptr(b_batch_idx), ptr(c_batch_idx)
-    g.out_f32, g.out_pre, g.out_hi, g.out_lo = ptr(out_f32), ptr(out_pre), ptr(out_hi), ptr(out_lo)
-    g.ldc = n if ldc is None else ldc
-    g.c_batch_stride = m_per_batch * g.ldc if c_batch_stride is None else c_batch_stride
-    g.bias, g.residual, g.aux, g.colsum = ptr(bias), ptr(residual), ptr(aux), ptr(colsum)
-    g.act = ACT[act]
-    g.aux_mode = ACT[aux_mode]
-    g.atomic = int(atomic)
-    g.split_k = split_k
-    g.alpha = alpha
-    g.block_n = block_n
-    g.drop_p = drop_p
-    g.drop_seed = drop_seed & 0xFFFFFFFFFFFFFFFF
-    g.bias_batch_stride = bias_batch_stride
-    g.out_scale = out_scale
-    g.cta_group = cta_group
-    check(lib().b2t_gemm(ctypes.byref(g), stream()), "b2t_gemm")
+        ws = _sk_workspace(a.hi.device, on_stream)
+        sk_ws, sk_bytes, sk = ws.data_ptr(), ws.numel(), stream_k
+    ldc_ = n if ldc is None else ldc
+    # positional, in the field order of b2t_gemm_args (_GEMM_FIELDS; asserted at import below the definition)
+    _GEMM_STRUCT.pack_into(
+        _GEMM_BUF, 0,
+        a.hi.data_ptr(), _dp(a.lo), b.hi.data_ptr(), _dp(b.lo),
+        a.d0, a.d1, a.d2, a.s1, a.s2, b.d0, b.d1, b.d2, b.s1, b.s2,
+        int(a.mn_major), int(b.mn_major), int(k_spans_batches), m_per_batch, batches, n, k,
+        int(a_batched), int(b_batched), _dp(b_batch_idx), _dp(c_batch_idx),
+        _dp(out_f32), _dp(out_pre), _dp(out_hi), _dp(out_lo),
+        ldc_, m_per_batch * ldc_ if c_batch_stride is None else c_batch_stride,
+        _dp(bias), _dp(residual), _dp(aux), _dp(colsum),
+        ACT[act], ACT[aux_mode], int(atomic), split_k, alpha, block_n, drop_p, drop_seed & 0xFFFFFFFFFFFFFFFF,
+        bias_batch_stride, out_scale, sk_ws, sk_bytes, sk, cta_group)
+    rc = _B2T_GEMM(_GEMM_BUF_PTR, ctypes.c_void_p(_lib.raw_stream() if on_stream is None else on_stream))
+    if rc != 0:
+        check(rc, "b2t_gemm")
     _count()
 
 

@@ -10,8 +10,9 @@ learning-rate groups — and for `torch.nn.utils.clip_grad_norm_` (src/train/tra
 torch does (unused / LayerDrop-skipped parameters must not be moved by weight decay).
 
 One launch updates every parameter of every group: a device table of (param, grad, exp_avg, exp_avg_sq) pointers plus
-a (tensor, chunk) list, one CTA per 64K elements.  Tables are cached per (pointer set, hyper-parameter class)
-signature, so with the flat gradient arena (stable gradient addresses) the host does no per-step table work.
+a (tensor, chunk) list, one CTA per 64K elements.  The chunk list is static over all parameters; the 48-byte-per-tensor
+table is refreshed every step through pinned staging and a non-blocking copy (class _Plan), with n = 0 for the
+parameters that have no gradient in that step.
 """
 from __future__ import annotations
 
@@ -68,6 +69,46 @@ class _TableCache:
         return t
 
 
+class _Plan:
+    """Static part of the one-launch update of a fixed parameter list: the (tensor, chunk) list over ALL parameters and
+    the device table; per step only the table (34 KB for the conformer's 716 tensors) is refreshed, through a ring of
+    pinned staging buffers and a non-blocking copy.  A parameter without gradient in this step (LayerDrop-skipped
+    layer, unused parameter) gets n = 0: its chunks find nothing to do, exactly torch's "skip parameters whose grad is
+    None".  (The first version rebuilt and synchronously uploaded a table whenever the set of parameters with a
+    gradient changed - with LayerDrop almost every step, 6 ms of host time in a step whose issue time is what bounds it.)"""
+    RING = 8
+
+    def __init__(self, params: List[torch.Tensor], device):
+        self.params = params
+        n = len(params)
+        self.numel = np.array([p.numel() for p in params], dtype=np.int64)
+        chunks = []
+        for i, ne in enumerate(self.numel):
+            nch = (int(ne) + MT_CHUNK - 1) // MT_CHUNK
+            chunks.append(np.stack([np.full(nch, i, dtype=np.int32), np.arange(nch, dtype=np.int32)], axis=1))
+        ch = np.concatenate(chunks, axis=0) if chunks else np.zeros((0, 2), dtype=np.int32)
+        self.n_chunks = int(ch.shape[0])
+        self.chunks = torch.from_numpy(np.ascontiguousarray(ch).reshape(-1)).to(device)
+        nbytes = max(n, 1) * _TENSOR_DT.itemsize
+        self.dev = torch.zeros(nbytes, dtype=torch.uint8, device=device)
+        self.host = [torch.zeros(nbytes, dtype=torch.uint8).pin_memory() for _ in range(self.RING)]
+        self.views = [h.numpy().view(_TENSOR_DT) for h in self.host]
+        self.events = [None] * self.RING
+        self.slot = 0
+
+    def upload(self, fill) -> None:
+        """fill(view) writes this step's table into a pinned staging buffer; it is then copied to the device table"""
+        i = self.slot
+        self.slot = (i + 1) % self.RING
+        if self.events[i] is not None:
+            self.events[i].synchronize()        # the copy that last used this staging buffer has completed
+        fill(self.views[i])
+        self.dev.copy_(self.host[i], non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        self.events[i] = ev
+
+
 class FusedAdam(torch.optim.Optimizer):
     """torch.optim.Adam semantics (amsgrad=False, maximize=False, L2 weight decay) in one kernel launch per step."""
 
@@ -75,7 +116,8 @@ class FusedAdam(torch.optim.Optimizer):
         if lr < 0 or eps < 0 or weight_decay < 0 or not (0 <= betas[0] < 1) or not (0 <= betas[1] < 1):
             raise ValueError("invalid Adam hyper-parameters")
         super().__init__(params, dict(lr=lr, betas=tuple(betas), eps=eps, weight_decay=weight_decay))
-        self._cache = _TableCache()
+        self._plan: Optional[_Plan] = None
+        self._plan_key = None
         self.grad_scale: Optional[torch.Tensor] = None     # optional device scalar multiplied into every gradient
         self.launches = 0
 
@@ -86,51 +128,81 @@ class FusedAdam(torch.optim.Optimizer):
             with torch.enable_grad():
                 loss = closure()
         _lib.ensure_device()
-        rows, sig = [], []
-        hyper: Dict[tuple, int] = {}
-        hlist: List[AdamGroup] = []
-        device = None
-        keep = []
+        # candidate parameters (fixed list -> static plan); the set that has a gradient varies per step
+        cand: List[torch.Tensor] = []
+        cand_group: List[int] = []
         for gi, group in enumerate(self.param_groups):
-            b1, b2 = group["betas"]
             for p in group["params"]:
-                g = p.grad
-                if g is None:
-                    continue
-                if g.is_sparse or p.dtype != torch.float32 or g.dtype != torch.float32 or not p.is_cuda:
+                if p.requires_grad:
+                    cand.append(p)
+                    cand_group.append(gi)
+        if not cand:
+            return loss
+        key = tuple(id(p) for p in cand)
+        if self._plan is None or self._plan_key != key or self._plan.dev.device != cand[0].device:
+            for p in cand:
+                if p.dtype != torch.float32 or not p.is_cuda:
                     raise RuntimeError("FusedAdam: dense fp32 CUDA parameters only")
                 if not p.is_contiguous():
                     raise RuntimeError("FusedAdam: parameters must be contiguous")
-                if not g.is_contiguous():
-                    g = p.grad = g.contiguous()
-                st = self.state[p]
-                if not st:
-                    st["step"] = 0
-                    st["exp_avg"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
-                    st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
-                st["step"] += 1
-                t = st["step"]
-                hk = (gi, t, float(group["lr"]))
-                hi = hyper.get(hk)
-                if hi is None:
-                    hi = hyper[hk] = len(hlist)
-                    # derived scalars in double (Python floats), rounded to fp32 once — torch's _single_tensor_adam
-                    hlist.append(AdamGroup(b2, group["eps"], group["weight_decay"], 1.0 - b1, 1.0 - b2,
-                                           group["lr"] / (1.0 - b1 ** t), math.sqrt(1.0 - b2 ** t), 0))
-                device = p.device
-                rows.append((p.data_ptr(), g.data_ptr(), st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr(), p.numel(), hi))
-                sig.append((rows[-1][0], rows[-1][1], hi))
-                keep.append(g)
-        if not rows:
+            self._plan, self._plan_key = _Plan(cand, cand[0].device), key
+        plan = self._plan
+        n = len(cand)
+        p_ptr = np.zeros(n, dtype=np.uint64)
+        g_ptr = np.zeros(n, dtype=np.uint64)
+        m_ptr = np.zeros(n, dtype=np.uint64)
+        v_ptr = np.zeros(n, dtype=np.uint64)
+        hyper_idx = np.zeros(n, dtype=np.int32)
+        active = np.zeros(n, dtype=bool)
+        hyper: Dict[tuple, int] = {}
+        hlist: List[AdamGroup] = []
+        keep = []
+        state = self.state
+        groups = self.param_groups
+        for i, p in enumerate(cand):
+            g = p.grad
+            if g is None:
+                continue
+            if g.is_sparse or g.dtype != torch.float32:
+                raise RuntimeError("FusedAdam: dense fp32 CUDA parameters only")
+            if not g.is_contiguous():
+                g = p.grad = g.contiguous()
+            st = state[p]
+            if not st:
+                st["step"] = 0
+                st["exp_avg"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
+                st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
+            t = st["step"] = st["step"] + 1
+            gi = cand_group[i]
+            group = groups[gi]
+            hk = (gi, t, float(group["lr"]))
+            hi = hyper.get(hk)
+            if hi is None:
+                hi = hyper[hk] = len(hlist)
+                b1, b2 = group["betas"]
+                # derived scalars in double (Python floats), rounded to fp32 once — torch's _single_tensor_adam
+                hlist.append(AdamGroup(b2, group["eps"], group["weight_decay"], 1.0 - b1, 1.0 - b2,
+                                       group["lr"] / (1.0 - b1 ** t), math.sqrt(1.0 - b2 ** t), 0))
+            p_ptr[i], g_ptr[i] = p.data_ptr(), g.data_ptr()
+            m_ptr[i], v_ptr[i] = st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr()
+            hyper_idx[i] = hi
+            active[i] = True
+            keep.append(g)
+        if not hlist:
             return loss
         # more hyper-parameter classes than one launch carries (LayerDrop lets the per-parameter step counts drift
-        # apart): one launch per slice of MAX_GROUPS classes
+        # apart): one launch per slice of MAX_GROUPS classes, tensors of the other slices masked out (n = 0)
         for lo in range(0, len(hlist), MAX_GROUPS):
-            sel = [(r, s) for r, s in zip(rows, sig) if lo <= r[5] < lo + MAX_GROUPS]
-            r2 = [r[:5] + (r[5] - lo,) for r, _ in sel]
-            table = self._cache.get(("adam", lo) + tuple(s for _, s in sel), r2, device)
+            sel = active & (hyper_idx >= lo) & (hyper_idx < lo + MAX_GROUPS)
+
+            def fill(view, sel=sel, lo=lo):
+                view["p"], view["g"], view["m"], view["v"] = p_ptr, g_ptr, m_ptr, v_ptr
+                view["n"] = np.where(sel, plan.numel, 0)
+                view["group"] = np.where(sel, hyper_idx - lo, 0)
+                view["pad"] = 0
+            plan.upload(fill)
             harr = (AdamGroup * len(hlist[lo:lo + MAX_GROUPS]))(*hlist[lo:lo + MAX_GROUPS])
-            check(lib().b2t_adam_multi(ptr(table.tensors), ptr(table.chunks), c_int(table.n_chunks), harr, c_int(len(harr)),
+            check(lib().b2t_adam_multi(ptr(plan.dev), ptr(plan.chunks), c_int(plan.n_chunks), harr, c_int(len(harr)),
                                        ptr(self.grad_scale), stream()), "b2t_adam_multi")
             self.launches += 1
         return loss
