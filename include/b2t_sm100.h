@@ -65,7 +65,7 @@ typedef struct {
     const float* aux;         /* same layout as out; value is multiplied by act'(aux) */
     float* colsum;            /* [n] += column sums of the final value (bias gradients) */
     int32_t act;              /* 0 none, 1 gelu(erf), 2 silu, 3 softsign */
-    int32_t aux_mode;         /* 0 none, 1 gelu', 2 silu', 3 softsign' */
+    int32_t aux_mode;         /* 0 none, 1 gelu', 2 silu', 3 softsign', 4 value *= aux (see pre_mode) */
     int32_t atomic;           /* out_f32 += value with red.add (split-K, overlapped folds) */
     int32_t split_k;          /* >=1; >1 requires atomic, act==0, no hi/lo/pre */
     float   alpha;
@@ -92,6 +92,13 @@ typedef struct {
     /* 0 = auto, 1 = single-CTA tiles (128 x block_n), 2 = CTA pair (tcgen05 cta_group::2, 256 x 256 tiles: each CTA
      * stages its own 128 rows of A and half of the B tile, UMMA M = 256) */
     int32_t  cta_group;
+    /* 0: out_pre receives the value before the activation (backward multiplies its gradient by act'(aux), aux_mode 1-3,
+     *    and regenerates the dropout mask from drop_seed).
+     * 1: out_pre receives the whole backward factor of the fused elementwise tail, d(value)/d(pre-activation) =
+     *    act'(x) * (dropped ? 0 : 1/(1-drop_p)) * out_scale, computed where act(x) and the keep/drop decision exist
+     *    anyway; the backward GEMM then passes it as aux with aux_mode 4 (plain multiply) and no drop_p. */
+    int32_t  pre_mode;
+    int32_t  reserved_;
 } b2t_gemm_args;
 
 int b2t_gemm(const b2t_gemm_args* args, b2t_stream stream);

@@ -52,6 +52,7 @@ def bench_epi(name, m, n, k, bn=128, b_mn=False, iters=20, cg=0, **flags):
     if flags.get("colsum"): kw["colsum"] = torch.zeros(n, device=dev)
     if flags.get("act"): kw["act"] = flags["act"]
     if flags.get("drop"): kw["drop_p"] = 0.1; kw["drop_seed"] = 7
+    if flags.get("prefac"): kw["pre_mode"] = 1
     def run(i):
         a, b = As[i % ncopy], Bs[i % ncopy]
         ops.gemm(ops.kmajor(*a), ops.mnmajor(*b) if b_mn else ops.kmajor(*b), m_per_batch=m, n=n, k=k, block_n=bn, cta_group=cg, **kw)
@@ -136,6 +137,9 @@ def shapes_fixed():
 EPI_CASES = [("f32", dict(f32=1)), ("hi/lo", dict(hi=1)), ("f32+hi/lo", dict(f32=1, hi=1)), ("hi/lo+aux(silu')", dict(hi=1, aux="silu")),
              ("hi/lo+colsum", dict(hi=1, colsum=1)), ("hi/lo+aux(silu')+colsum+drop", dict(hi=1, aux="silu", colsum=1, drop=1)),
              ("pre+hi/lo+bias+silu+drop", dict(pre=1, hi=1, bias=1, act="silu", drop=1)), ("pre+hi/lo+bias+gelu", dict(pre=1, hi=1, bias=1, act="gelu")),
+             ("prefac+hi/lo+bias+silu+drop", dict(pre=1, hi=1, bias=1, act="silu", drop=1, prefac=1)),
+             ("prefac+hi/lo+bias+gelu+drop", dict(pre=1, hi=1, bias=1, act="gelu", drop=1, prefac=1)),
+             ("hi/lo+aux(mul)+colsum", dict(hi=1, aux="mul", colsum=1)),
              ("f32+bias", dict(f32=1, bias=1)), ("f32+bias+res", dict(f32=1, bias=1, res=1)), ("f32+bias+drop+res", dict(f32=1, bias=1, res=1, drop=1))]
 
 

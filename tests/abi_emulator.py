@@ -118,7 +118,8 @@ def _dact(a, mode):
 def gemm(a, b, *, m_per_batch, n, k, batches=1, out_f32=None, out_pre=None, out_hi=None, out_lo=None, ldc=None,
          c_batch_stride=None, bias=None, residual=None, aux=None, colsum=None, act=None, aux_mode=None, atomic=False,
          split_k=1, alpha=1.0, k_spans_batches=False, a_batched=False, b_batched=False, b_batch_idx=None,
-         c_batch_idx=None, block_n=0, drop_p=0.0, drop_seed=0, bias_batch_stride=0, out_scale=1.0, stream_k=0, cta_group=0):
+         c_batch_idx=None, block_n=0, drop_p=0.0, drop_seed=0, bias_batch_stride=0, out_scale=1.0, stream_k=0, cta_group=0,
+         on_stream=None, pre_mode=0):
     global LAUNCHES
     LAUNCHES += 1
     ldc = n if ldc is None else ldc
@@ -156,14 +157,21 @@ def gemm(a, b, *, m_per_batch, n, k, batches=1, out_f32=None, out_pre=None, out_
                 bt_.index_add_(0, idx, val.flatten().to(t.dtype))
             else:
                 bt_[idx] = val.flatten().to(t.dtype)
-        if out_pre is not None:
+        if out_pre is not None and pre_mode == 0:
             wr(out_pre, x)
+        dfac = _dact(x, act) if (pre_mode == 1 and ACT[act]) else torch.ones_like(x)
         x = _act(x, act)
-        if ACT[aux_mode]:
+        if ACT[aux_mode] == 4:
+            x = x * rd(aux)
+        elif ACT[aux_mode]:
             x = x * _dact(rd(aux), aux_mode)
         if drop_p > 0:
-            x = x * _keep(drop_p, drop_seed, offs)
+            keep = _keep(drop_p, drop_seed, offs)
+            x = x * keep
+            dfac = dfac * keep
         x = x * out_scale
+        if out_pre is not None and pre_mode == 1:
+            wr(out_pre, dfac * out_scale)
         if residual is not None:
             x = x + rd(residual)
         if colsum is not None:

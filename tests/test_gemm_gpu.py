@@ -316,3 +316,46 @@ def test_pair_batched_operands():
              a_batched=True, b_batch_idx=day, act="softsign", cta_group=2)
     ref = torch.nn.functional.softsign(torch.einsum("btd,bdk->btk", y.double(), w.double()[day.long()]))
     assert rel(out, ref) < 2e-5
+
+
+@pytest.mark.parametrize("cg", [1, 2])
+@pytest.mark.parametrize("act", ["silu", "gelu", "softsign"])
+@pytest.mark.parametrize("n", [768, 330])      # 330: unaligned for bf16 rows of 8 -> fallback epilogue
+def test_pre_mode_stores_the_backward_factor(cg, act, n):
+    """pre_mode 1: out_pre = act'(z) * dropout factor * out_scale, from the same keep / drop decisions as the value;
+    aux_mode 'mul' multiplies by it in the backward GEMM."""
+    ops = _ops()
+    m, k = 520, 256
+    a, b, bias = rnd(m, k, seed=21, scale=0.3), rnd(n, k, seed=22, scale=0.3), rnd(n, seed=23)
+    ah, al = ops.split(a)
+    bh, bl = ops.split(b)
+    out = torch.empty(m, n, device="cuda")
+    pre = torch.empty(m, n, device="cuda")
+    p_drop, scale = 0.3, 0.5
+    ops.gemm(ops.kmajor(ah, al), ops.kmajor(bh, bl), m_per_batch=m, n=n, k=k, out_f32=out, out_pre=pre, bias=bias, act=act,
+             drop_p=p_drop, drop_seed=1234, out_scale=scale, pre_mode=1, cta_group=cg)
+    z = (a.double() @ b.double().t() + bias.double()).requires_grad_(True)
+    fz = {"silu": torch.nn.functional.silu, "gelu": torch.nn.functional.gelu, "softsign": torch.nn.functional.softsign}[act](z)
+    dz, = torch.autograd.grad(fz.sum(), z)
+    # the mask of the value: the same seed / offsets without pre_mode
+    ref_out = torch.empty(m, n, device="cuda")
+    ops.gemm(ops.kmajor(ah, al), ops.kmajor(bh, bl), m_per_batch=m, n=n, k=k, out_f32=ref_out, bias=bias, act=act,
+             drop_p=p_drop, drop_seed=1234, out_scale=scale, cta_group=1)
+    assert torch.equal(out == 0, ref_out == 0) and rel(out, ref_out) < 1e-6
+    keep = (ref_out != 0).double()
+    assert 0.25 < 1.0 - keep.mean().item() < 0.35
+    assert rel(out, fz.detach() * keep / (1 - p_drop) * scale) < 2e-5
+    assert rel(pre, dz * keep / (1 - p_drop) * scale) < 2e-5
+    if n % 8:
+        return      # (an MN-major operand needs 16-byte aligned rows)
+    # backward: dX = (dY . W) * factor, bias gradient = its column sums
+    dy, w = rnd(m, 192, seed=24, scale=0.3), rnd(192, n, seed=25, scale=0.3)     # dY [m, 192], W [192, n]
+    dyh, dyl = ops.split(dy)
+    wh, wl = ops.split(w)
+    dx = torch.empty(m, n, device="cuda")
+    cs = torch.zeros(n, device="cuda")
+    ops.gemm(ops.kmajor(dyh, dyl), ops.mnmajor(wh, wl), m_per_batch=m, n=n, k=192, out_f32=dx, aux=pre, aux_mode="mul", colsum=cs,
+             cta_group=cg)
+    ref_dx = (dy.double() @ w.double()) * pre.double()
+    assert rel(dx, ref_dx) < 2e-5
+    assert rel(cs, ref_dx.sum(0)) < 1e-4

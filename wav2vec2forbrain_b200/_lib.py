@@ -42,7 +42,7 @@ class GemmArgs(ctypes.Structure):
         ("drop_p", c_float), ("drop_seed", ctypes.c_uint64), ("bias_batch_stride", c_int64),
         ("out_scale", c_float),
         ("sk_workspace", c_void_p), ("sk_workspace_bytes", c_int64), ("stream_k", c_int32),
-        ("cta_group", c_int32),
+        ("cta_group", c_int32), ("pre_mode", c_int32), ("reserved_", c_int32),
     ]
 
 

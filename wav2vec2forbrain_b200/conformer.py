@@ -51,7 +51,9 @@ def _ffn_forward(eng, P, pfx: str, ln: str, h: Tensor, M: int, training: bool, s
     _, pre, f_hi, f_lo = eng._linear_fwd(u_hi, u_lo, eng._w(P, pfx + "intermediate_dense.weight"),
                                          P[pfx + "intermediate_dense.bias"], M, F, D, want_f32=False, want_split=True,
                                          want_pre=training, act=cfg.hidden_act, drop_p=p_act,
-                                         drop_seed=_seed(seed, layer, site))
+                                         drop_seed=_seed(seed, layer, site), pre_mode=1 if training else 0)
+    # pre_mode 1: `pre` holds SiLU'(x) * dropout factor (the whole backward factor of this elementwise tail), so the
+    # backward GEMM's epilogue is one multiply instead of a sigmoid and a mask hash per element
     out, _, _, _ = eng._linear_fwd(f_hi, f_lo, eng._w(P, pfx + "output_dense.weight"), P[pfx + "output_dense.bias"], M, D, F,
                                    residual=h, drop_p=p_h, drop_seed=_seed(seed, layer, site + 1), out_scale=0.5)
     st[tag] = dict(x=h, ln=(m, r), u_hi=u_hi, u_lo=u_lo, pre=pre, f_hi=f_hi, f_lo=f_lo)
@@ -163,8 +165,7 @@ def _ffn_backward(eng, P, G, pfx: str, ln: str, st: dict, g_hi, g_lo, db_out: Te
                                                 name=pfx + "output_dense.weight")
     db1 = _gz(eng, pfx + "intermediate_dense.bias", F, g_hi.device)
     _, dp_hi, dp_lo = eng._dgrad(g_hi, g_lo, eng._w(P, pfx + "output_dense.weight"), M, D, F, want_f32=False, want_split=True,
-                                 aux=st["pre"], aux_mode=cfg.hidden_act, drop_p=p_act, drop_seed=_seed(seed, layer, site),
-                                 colsum=db1, alpha=0.5)
+                                 aux=st["pre"], aux_mode="mul", colsum=db1, alpha=0.5)
     G[pfx + "intermediate_dense.bias"] = db1
     G[pfx + "intermediate_dense.weight"] = eng._wgrad(dp_hi, dp_lo, st["u_hi"], st["u_lo"], F, D, M,
                                                       name=pfx + "intermediate_dense.weight")

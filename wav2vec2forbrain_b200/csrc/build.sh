@@ -17,6 +17,13 @@ for f in *.cu; do
     pids="$pids $!"
   fi
 done
-for p in $pids; do wait $p; done
+# second pass over gemm_tc.cu: the 1-term instantiations (see B2T_GEMM_PART in the file)
+o=build/gemm_tc_part1.o
+OBJS="$OBJS $o"
+if [ ! -f "$o" ] || [ gemm_tc.cu -nt "$o" ] || [ common.cuh -nt "$o" ] || [ ../../include/b2t_sm100.h -nt "$o" ]; then
+  ( $NVCC $FLAGS -DB2T_GEMM_PART=1 ${PTXAS_V:+-Xptxas -v} -c gemm_tc.cu -o "$o" 2> build/gemm_tc_part1.log || { cat build/gemm_tc_part1.log; exit 1; } ) &
+  pids="$pids $!"
+fi
+for p in $pids; do wait $p || exit 1; done
 $NVCC -shared -o libb2t_sm100.so $OBJS -cudart static
 echo "built $(pwd)/libb2t_sm100.so"

@@ -52,6 +52,7 @@ struct KParams {
     const float* aux;
     float* colsum;
     int act, aux_mode, atomic, split_k;
+    int pre_mode;   // 1: out_pre = act'(x) * dropout factor * out_scale (the backward factor) instead of x
     float alpha;
     float drop_p, drop_scale, out_scale;
     uint32_t drop_thr;   // drop_threshold(drop_p): keep / drop as an integer compare (computed on the host, it needs fp64)
@@ -390,6 +391,7 @@ enum : uint32_t {
     F_ALPHA = 1u << 0, F_BIAS = 1u << 1, F_PRE = 1u << 2, F_ACT = 1u << 3, F_AUX = 1u << 4, F_DROP = 1u << 5,
     F_SCALE = 1u << 6, F_RES = 1u << 7, F_F32 = 1u << 8, F_ATOMIC = 1u << 9, F_HI = 1u << 10, F_LO = 1u << 11,
     F_COLSUM = 1u << 12, F_VEC = 1u << 13,
+    F_PREFAC = 1u << 15,   // out_pre holds the backward factor (pre_mode 1)
     F_TMA = 1u << 14,   // aligned AND rows / batches of the output do not overlap in memory: TMA-store epilogue
 };
 
@@ -589,9 +591,10 @@ __device__ __forceinline__ void st4(float* a, const float (&t)[4], int nv) {
 
 // st: this warp's 4 KB staging buffer.  v: the lane's row (TMEM lane) x 32 columns.  row0: output row of
 // lane 0 inside the batch; base_off: element offset of the batch slot; col_base: first column of the chunk.
-template <bool VEC>
-__device__ __forceinline__ void epi_chunk32(const KParams& p, const uint32_t F, float* st, const float (&v)[32], int lane,
+template <bool VEC, bool PREFAC_OK>
+__device__ __forceinline__ void epi_chunk32(const KParams& p, const uint32_t F_, float* st, const float (&v)[32], int lane,
                                             int row0, long long base_off, int col_base, const float* bias_ptr) {
+    const uint32_t F = PREFAC_OK ? F_ : (F_ & ~F_PREFAC);
 #pragma unroll
     for (int j = 0; j < 8; ++j)
         *reinterpret_cast<float4*>(st + lane * 32 + ((j ^ (lane & 7)) << 2)) =
@@ -638,10 +641,16 @@ __device__ __forceinline__ void epi_chunk32(const KParams& p, const uint32_t F, 
         }
         if (F & F_ALPHA) { EPI_ALL(x[i][e] *= p.alpha) }
         EPI_ALL(x[i][e] += b4[e])
-        if (F & F_PRE) {
+        if ((F & F_PRE) && !(F & F_PREFAC)) {
 #pragma unroll
             for (int i = 0; i < 4; ++i)
                 if (ok[i]) st4<VEC>(p.out_pre + off[i], x[i], nv);
+        }
+        float dd[4][4];   // pre_mode 1: d(value)/d(pre-activation), stored in place of the pre-activation
+        if (F & F_PREFAC) {
+            if (p.act == 1) { EPI_ALL(dd[i][e] = gelu_erf_grad(x[i][e])) }
+            else if (p.act == 2) { EPI_ALL(dd[i][e] = silu_grad(x[i][e])) }
+            else { EPI_ALL(const float d = 1.0f + fabsf(x[i][e]); dd[i][e] = rcp_approx(d * d)) }
         }
         if (F & F_ACT) {
             if (p.act == 1) { EPI_ALL(x[i][e] = gelu_erf(x[i][e])) }
@@ -651,12 +660,19 @@ __device__ __forceinline__ void epi_chunk32(const KParams& p, const uint32_t F, 
         if (F & F_AUX) {
             if (p.aux_mode == 1) { EPI_ALL(x[i][e] *= gelu_erf_grad(ax[i][e])) }
             else if (p.aux_mode == 2) { EPI_ALL(x[i][e] *= silu_grad(ax[i][e])) }
+            else if (p.aux_mode == 4) { EPI_ALL(x[i][e] *= ax[i][e]) }
             else { EPI_ALL(const float d = 1.0f + fabsf(ax[i][e]); x[i][e] *= rcp_approx(d * d)) }
         }
         if (F & F_DROP) {
-            EPI_ALL(x[i][e] = hash_uniform(p.drop_seed, (unsigned long long)(off[i] + e)) < p.drop_p ? 0.0f : x[i][e] * p.drop_scale)
+            EPI_ALL(const float kf = hash_uniform(p.drop_seed, (unsigned long long)(off[i] + e)) < p.drop_p ? 0.0f : p.drop_scale;
+                    x[i][e] *= kf; if (F & F_PREFAC) dd[i][e] *= kf)
         }
-        if (F & F_SCALE) { EPI_ALL(x[i][e] *= p.out_scale) }
+        if (F & F_SCALE) { EPI_ALL(x[i][e] *= p.out_scale; if (F & F_PREFAC) dd[i][e] *= p.out_scale) }
+        if (F & F_PREFAC) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                if (ok[i]) st4<VEC>(p.out_pre + off[i], dd[i], nv);
+        }
         if (F & F_RES) { EPI_ALL(x[i][e] += rs[i][e]) }
         EPI_ALL(x[i][e] = (ok[i] && e < nv) ? x[i][e] : 0.0f)
         if (F & F_F32) {
@@ -789,9 +805,13 @@ __device__ __forceinline__ uint32_t pack_bf16x2(bf16 a, bf16 b) {
 // v: the lane's accumulator row (row0 + lane inside the batch), 32 columns from col_base.  st / st_addr: this warp's
 // 4 KB staging buffer (generic pointer / shared address, 1024-byte aligned).  `pending`: a bulk store of this warp may
 // still be reading the buffer (lane 0 is the only lane that commits and waits).
-__device__ __forceinline__ void epi_row32(const KParams& p, const uint32_t F, float* st, uint32_t st_addr, float (&v)[32],
+template <int EMODE>
+__device__ __forceinline__ void epi_row32(const KParams& p, const uint32_t F_, float* st, uint32_t st_addr, float (&v)[32],
                                           int lane, int row0, int cbatch, long long base_off, int col_base,
                                           const float* bias_ptr, const EpiMaps& maps, float4 (&t)[8]) {
+    // compile-time dead stages: no input stages without EPI_IN; the backward-factor output (pre_mode 1, forward GEMMs
+    // only) exists in the input-free instantiation - the two sets of temporaries never share a register budget
+    const uint32_t F = EMODE == 1 ? (F_ & ~F_PREFAC) : (EMODE == 2 ? (F_ & ~(F_AUX | F_RES)) : F_);
 #define EPI32(stmt) _Pragma("unroll") for (int e = 0; e < 32; ++e) { stmt; }
     auto buffer_free = [&]() {   // every earlier bulk store of this warp has read the buffer, every lane is past its own reads
         if (lane == 0 && !(p.debug & 64)) bulk_wait_read0();
@@ -810,19 +830,67 @@ __device__ __forceinline__ void epi_row32(const KParams& p, const uint32_t F, fl
             }
         }
     }
-    if (F & F_PRE) {
+    auto store_pre = [&](const float (&w)[32]) {
         buffer_free();
 #pragma unroll
         for (int j = 0; j < 8; ++j)
-            *reinterpret_cast<float4*>(st + lane * 32 + ((j ^ (lane & 7)) << 2)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            *reinterpret_cast<float4*>(st + lane * 32 + ((j ^ (lane & 7)) << 2)) = make_float4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) {
             tma_store_3d(maps.pre, st_addr, col_base, row0, cbatch);
             bulk_commit();
         }
-    }
-    if (F & F_ACT) {
+    };
+    if ((F & F_PRE) && !(F & F_PREFAC)) store_pre(v);
+    if (F & F_PREFAC) {
+        // activation and its derivative from one sigmoid / erf; the keep / drop decision scales both; the factor goes out
+        // in place of the pre-activation, so that the backward GEMM's epilogue is one multiply per element.  Two halves
+        // of 16 columns: only 16 factor registers are live next to the 32 accumulators and the prefetched input chunk.
+        const uint32_t thr = p.drop_thr, s_lo = (uint32_t)p.drop_seed, s_hi = (uint32_t)(p.drop_seed >> 32);
+        const unsigned long long o0 = (unsigned long long)off_row;
+        const bool no_carry = (uint32_t)o0 <= 0xFFFFFFFFu - 32u;
+        const uint32_t f0 = hash_fold(o0);
+        const float oscale = (F & F_SCALE) ? p.out_scale : 1.0f;
+        buffer_free();
+#pragma unroll
+        for (int hf = 0; hf < 2; ++hf) {
+            float d[16];
+            // one mode branch around 16 independent chains
+#define PREFAC16(stmt) _Pragma("unroll") for (int i = 0; i < 16; ++i) { const int e = hf * 16 + i; const float x = v[e]; float a, g; stmt; v[e] = a; d[i] = g; }
+            if (p.act == 1) {
+                PREFAC16(const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
+                         g = cdf + x * 0.39894228040143267794f * __expf(-0.5f * x * x); a = x * cdf)
+            } else if (p.act == 2) {
+                PREFAC16(const float sg = sigmoidf_(x); g = sg * (1.0f + x * (1.0f - sg)); a = x * sg)
+            } else {
+                PREFAC16(const float r = rcp_approx(1.0f + fabsf(x)); g = r * r; a = x * r)
+            }
+#undef PREFAC16
+            if (F & F_DROP) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const int e = hf * 16 + i;
+                    const float k = hash_drop(no_carry ? f0 + (uint32_t)e : hash_fold(o0 + e), s_lo, s_hi, thr) ? 0.0f : p.drop_scale * oscale;
+                    v[e] *= k;
+                    d[i] *= k;
+                }
+            } else if (F & F_SCALE) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) v[hf * 16 + i] *= oscale, d[i] *= oscale;
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                *reinterpret_cast<float4*>(st + lane * 32 + (((hf * 4 + j) ^ (lane & 7)) << 2)) =
+                    make_float4(d[4 * j], d[4 * j + 1], d[4 * j + 2], d[4 * j + 3]);
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+            tma_store_3d(maps.pre, st_addr, col_base, row0, cbatch);
+            bulk_commit();
+        }
+    } else if (F & F_ACT) {
         if (p.act == 1) { EPI32(v[e] = gelu_erf(v[e])) }
         else if (p.act == 2) { EPI32(v[e] = silu_f(v[e])) }
         else { EPI32(v[e] = v[e] * rcp_approx(1.0f + fabsf(v[e]))) }
@@ -843,10 +911,11 @@ __device__ __forceinline__ void epi_row32(const KParams& p, const uint32_t F, fl
         // times: 4 chains per segment and an instruction stream scattered over 1600 slots - stall_no_inst in ncu)
         if (p.aux_mode == 1) { EPI32(v[e] *= gelu_erf_grad(a[e])) }
         else if (p.aux_mode == 2) { EPI32(v[e] *= silu_grad(a[e])) }
+        else if (p.aux_mode == 4) { EPI32(v[e] *= a[e]) }
         else { EPI32(const float d = 1.0f + fabsf(a[e]); v[e] *= rcp_approx(d * d)) }
         if (F & F_RES) chunk_ldg(p, p.residual, base_off, row0, col_base, lane, t);   // both inputs: the second read is exposed
     }
-    if (F & F_DROP) {
+    if ((F & F_DROP) && !(F & F_PREFAC)) {
         // same keep / drop decision as hash_uniform(seed, offset) < p, with the 64-bit index folded once per row segment
         const uint32_t thr = p.drop_thr, s_lo = (uint32_t)p.drop_seed, s_hi = (uint32_t)(p.drop_seed >> 32);
         const unsigned long long o0 = (unsigned long long)off_row;
@@ -857,7 +926,7 @@ __device__ __forceinline__ void epi_row32(const KParams& p, const uint32_t F, fl
             EPI32(v[e] = hash_drop(hash_fold(o0 + e), s_lo, s_hi, thr) ? 0.0f : v[e] * p.drop_scale)
         }
     }
-    if (F & F_SCALE) { EPI32(v[e] *= p.out_scale) }
+    if ((F & F_SCALE) && !(F & F_PREFAC)) { EPI32(v[e] *= p.out_scale) }
     if (F & F_RES) {
         buffer_free();
         chunk_to_rows_store(st, lane, t);
@@ -927,7 +996,11 @@ __device__ __forceinline__ void epi_row32(const KParams& p, const uint32_t F, fl
 #undef EPI32
 }
 
-template <int NTERMS, bool A_MN, bool B_MN, int BN, int CG>
+// EMODE: which epilogue stages are compiled in.  0 = all (single-CTA tiles); the pair kernel, where the register budget
+// of the row-per-thread epilogue decides whether its 32 independent chains per stage fit without spilling, has two:
+// 1 = with a second input (aux / residual: the prefetched input chunk, 64 registers) but without the backward-factor
+// output, 2 = without inputs (forward GEMMs; pre_mode 1 lives here).
+template <int NTERMS, bool A_MN, bool B_MN, int BN, int CG, int EMODE>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__ CUtensorMap tmAl,
                const __grid_constant__ CUtensorMap tmBh, const __grid_constant__ CUtensorMap tmBl,
@@ -1142,6 +1215,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
         const int half = (warp - EPI_WARP0) >> 2;
         int local_iter = 0;
         uint32_t F = p.flags;
+        constexpr bool EPI_IN = EMODE != 2;
+        if (!EPI_IN) F &= ~(F_AUX | F_RES);   // (the host never selects this instantiation with either input set)
         asm volatile("" : "+r"(F));   // pin the stage bits in a register (else ptxas re-reads the constant bank per test)
         Sched sch(p, CG, rank);
         Item it;
@@ -1172,7 +1247,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
             }
             // TMA-store epilogue: the aux (else residual) chunk is read one chunk ahead of its use - the first one
             // here, under the tile's MMAs - so that no chunk waits for a memory round trip
-            const bool tin_on = (F & F_TMA) && (F & (F_AUX | F_RES)) && it.mode != 1 && !(p.debug & 1);
+            const bool tin_on = EMODE != 2 && (F & F_TMA) && (F & (F_AUX | F_RES)) && it.mode != 1 && !(p.debug & 1);
             const float* const tin_src = (F & F_AUX) ? p.aux : p.residual;
             float4 tin[8], tnext[8];
             if (tin_on && n_blk * BN + half * 32 < p.n)
@@ -1243,11 +1318,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
                     }
                 }
                 if (F & F_TMA)
-                    epi_row32(p, F, epi_buf, epi_buf_addr, v, lane, m_blk * BM + q * 32, cbatch, base_off, col_base, bias_ptr, emaps, tin);
+                    epi_row32<EMODE>(p, F, epi_buf, epi_buf_addr, v, lane, m_blk * BM + q * 32, cbatch, base_off, col_base, bias_ptr, emaps, tin);
                 else if (F & F_VEC)
-                    epi_chunk32<true>(p, F, epi_buf, v, lane, m_blk * BM + q * 32, base_off, col_base, bias_ptr);
+                    epi_chunk32<true, EMODE != 1>(p, F, epi_buf, v, lane, m_blk * BM + q * 32, base_off, col_base, bias_ptr);
                 else
-                    epi_chunk32<false>(p, F, epi_buf, v, lane, m_blk * BM + q * 32, base_off, col_base, bias_ptr);
+                    epi_chunk32<false, EMODE != 1>(p, F, epi_buf, v, lane, m_blk * BM + q * 32, base_off, col_base, bias_ptr);
             }
             if (p.debug & 8) {
             } else if (it.mode == 1) {
@@ -1382,7 +1457,21 @@ int encode_map(CUtensorMap* map, const void* ptr, int64_t d0, int64_t d1, int64_
 // collective: a persistent grid of one CTA per SM whose tiles are statically strided runs a second wave for
 // the CTAs that could not get an SM while NCCL kernels hold some (measured at 2 GPUs: the step grows by about
 // the all-reduce time).
-int g_sm_limit = 0;
+}  // namespace
+// gemm_tc.cu is compiled twice (build.sh): B2T_GEMM_PART 0 = the API + the bf16x3 (3-term) instantiations, 1 = the plain
+// bf16 (1-term) instantiations behind b2t_gemm_part1 - 40 kernel instantiations in one translation unit took 5 minutes.
+#ifndef B2T_GEMM_PART
+#define B2T_GEMM_PART 0
+#endif
+#if B2T_GEMM_PART == 0
+__attribute__((visibility("hidden"))) int b2t_g_sm_limit = 0;
+#else
+extern __attribute__((visibility("hidden"))) int b2t_g_sm_limit;
+#endif
+#define g_sm_limit b2t_g_sm_limit
+// internal to the library (hidden: not part of the C ABI of include/b2t_sm100.h)
+extern "C" __attribute__((visibility("hidden"))) int b2t_gemm_part1(const b2t_gemm_args* a, const void* kparams, int bn, int cg, void* stream);
+namespace {
 int num_sms() {
     static int n = 0;
     if (!n) {
@@ -1395,7 +1484,7 @@ int num_sms() {
     return (g_sm_limit > 0 && g_sm_limit < n) ? g_sm_limit : n;
 }
 
-template <int NTERMS, bool A_MN, bool B_MN, int BN, int CG>
+template <int NTERMS, bool A_MN, bool B_MN, int BN, int CG, int EMODE>
 int launch(const b2t_gemm_args* a, const KParams& kp, cudaStream_t stream) {
     using C = Cfg<NTERMS, BN, CG>;
     CUtensorMap mAh, mAl, mBh, mBl;
@@ -1422,7 +1511,7 @@ int launch(const b2t_gemm_args* a, const KParams& kp, cudaStream_t stream) {
         if (a->out_hi && (rc = make_map(&mHi, a->out_hi, a->n, a->m_per_batch, slots, a->ldc, s2, MAP_OUT_BF16, "out_hi"))) return rc;
         if (a->out_lo && (rc = make_map(&mLo, a->out_lo, a->n, a->m_per_batch, slots, a->ldc, s2, MAP_OUT_BF16, "out_lo"))) return rc;
     }
-    auto kern = gemm_tc_kernel<NTERMS, A_MN, B_MN, BN, CG>;
+    auto kern = gemm_tc_kernel<NTERMS, A_MN, B_MN, BN, CG, EMODE>;
     {
         // per device: the attribute belongs to the function in ONE device's context
         static bool attr_set[64] = {};
@@ -1468,18 +1557,28 @@ int launch(const b2t_gemm_args* a, const KParams& kp, cudaStream_t stream) {
     return 0;
 }
 
+template <int NTERMS, int BN, int CG, int EMODE>
+int dispatch_major2(const b2t_gemm_args* a, const KParams& kp, cudaStream_t s) {
+    if (a->a_mn_major) {
+        if (a->b_mn_major) return launch<NTERMS, true, true, BN, CG, EMODE>(a, kp, s);
+        return launch<NTERMS, true, false, BN, CG, EMODE>(a, kp, s);
+    }
+    if (a->b_mn_major) return launch<NTERMS, false, true, BN, CG, EMODE>(a, kp, s);
+    return launch<NTERMS, false, false, BN, CG, EMODE>(a, kp, s);
+}
 template <int NTERMS, int BN, int CG>
 int dispatch_major(const b2t_gemm_args* a, const KParams& kp, cudaStream_t s) {
-    if (a->a_mn_major) {
-        if (a->b_mn_major) return launch<NTERMS, true, true, BN, CG>(a, kp, s);
-        return launch<NTERMS, true, false, BN, CG>(a, kp, s);
+    if constexpr (CG == 2) {   // the specialised epilogues exist for the pair kernel only (40 instantiations in all)
+        if (a->aux_mode || a->residual) return dispatch_major2<NTERMS, BN, CG, 1>(a, kp, s);
+        return dispatch_major2<NTERMS, BN, CG, 2>(a, kp, s);
+    } else {
+        return dispatch_major2<NTERMS, BN, CG, 0>(a, kp, s);
     }
-    if (a->b_mn_major) return launch<NTERMS, false, true, BN, CG>(a, kp, s);
-    return launch<NTERMS, false, false, BN, CG>(a, kp, s);
 }
 
 }  // namespace
 
+#if B2T_GEMM_PART == 0
 extern "C" int b2t_gemm_set_sm_limit(int sms) {
     g_sm_limit = sms > 0 ? sms : 0;
     return 0;
@@ -1537,6 +1636,10 @@ extern "C" int b2t_gemm(const b2t_gemm_args* a, b2t_stream stream_) {
     kp.colsum = a->colsum;
     kp.act = a->act;
     kp.aux_mode = a->aux_mode;
+    kp.pre_mode = a->pre_mode;
+    B2T_CHECK_ARG(a->pre_mode == 0 || (a->pre_mode == 1 && a->out_pre && a->act >= 1 && a->act <= 3 && !a->aux_mode && !a->residual),
+                  "b2t_gemm: pre_mode 1 needs out_pre and an activation, and excludes aux / residual");
+    B2T_CHECK_ARG(a->aux_mode >= 0 && a->aux_mode <= 4 && a->act >= 0 && a->act <= 3, "b2t_gemm: bad act / aux_mode");
     kp.atomic = a->atomic;
     kp.split_k = a->split_k;
     kp.alpha = a->alpha;
@@ -1557,7 +1660,7 @@ extern "C" int b2t_gemm(const b2t_gemm_args* a, b2t_stream stream_) {
     kp.flags = (kp.alpha != 1.0f ? F_ALPHA : 0u) | (kp.bias ? F_BIAS : 0u) | (kp.out_pre ? F_PRE : 0u) | (kp.act ? F_ACT : 0u) |
                (kp.aux_mode ? F_AUX : 0u) | (kp.drop_p > 0.0f ? F_DROP : 0u) | (kp.out_scale != 1.0f ? F_SCALE : 0u) |
                (kp.residual ? F_RES : 0u) | (kp.out_f32 ? F_F32 : 0u) | (kp.atomic ? F_ATOMIC : 0u) | (kp.out_hi ? F_HI : 0u) |
-               (kp.out_lo ? F_LO : 0u) | (kp.colsum ? F_COLSUM : 0u) | (kp.vec4 ? F_VEC : 0u);
+               (kp.out_lo ? F_LO : 0u) | (kp.colsum ? F_COLSUM : 0u) | (kp.vec4 ? F_VEC : 0u) | (kp.pre_mode == 1 ? F_PREFAC : 0u);
     {
         // overlapping-stride outputs (the folded unfold gradient: ldc < n) keep the per-element red.add path
         static int no_tma = -1;
@@ -1646,13 +1749,19 @@ extern "C" int b2t_gemm(const b2t_gemm_args* a, b2t_stream stream_) {
     }
 
     const bool three = a->a_lo != nullptr;
-    if (cg == 2) return three ? dispatch_major<3, 256, 2>(a, kp, stream) : dispatch_major<1, 256, 2>(a, kp, stream);
-    if (three) {
-        if (bn == 64) return dispatch_major<3, 64, 1>(a, kp, stream);
-        if (bn == 128) return dispatch_major<3, 128, 1>(a, kp, stream);
-        return dispatch_major<3, 256, 1>(a, kp, stream);
-    }
+    if (!three) return b2t_gemm_part1(a, &kp, bn, cg, (void*)stream);
+    if (cg == 2) return dispatch_major<3, 256, 2>(a, kp, stream);
+    if (bn == 64) return dispatch_major<3, 64, 1>(a, kp, stream);
+    if (bn == 128) return dispatch_major<3, 128, 1>(a, kp, stream);
+    return dispatch_major<3, 256, 1>(a, kp, stream);
+}
+#else   // B2T_GEMM_PART == 1
+extern "C" __attribute__((visibility("hidden"))) int b2t_gemm_part1(const b2t_gemm_args* a, const void* kparams, int bn, int cg, void* stream_) {
+    const KParams& kp = *reinterpret_cast<const KParams*>(kparams);
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (cg == 2) return dispatch_major<1, 256, 2>(a, kp, stream);
     if (bn == 64) return dispatch_major<1, 64, 1>(a, kp, stream);
     if (bn == 128) return dispatch_major<1, 128, 1>(a, kp, stream);
     return dispatch_major<1, 256, 1>(a, kp, stream);
 }
+#endif

@@ -659,6 +659,8 @@ class Engine:
                                                    P[Lq + "feed_forward.intermediate_dense.bias"], M, F, D, want_f32=False,
                                                    want_split=True, want_pre=training, act=cfg.hidden_act, drop_p=p_act,
                                                    drop_seed=_mix(seed, 1000 + 10 * i + 3))
+            # (the conformer's SiLU feed-forward stores the backward factor instead, b2t_gemm pre_mode 1; for GELU the
+            # extra erf-derivative in the forward epilogue measured +29 us against -26 us in backward: not taken)
             st.update(pre1=pre1, f_hi=f_hi, f_lo=f_lo)
             u2, _, _, _ = self._linear_fwd(f_hi, f_lo, self._w(P, Lq + "feed_forward.output_dense.weight"),
                                            P[Lq + "feed_forward.output_dense.bias"], M, D, F, residual=res2, drop_p=p_h,

@@ -15,7 +15,7 @@ from . import _lib
 from ._lib import GemmArgs, c_int, c_int64, c_float, check, lib, ptr, stream
 
 Tensor = torch.Tensor
-ACT = {None: 0, "none": 0, "gelu": 1, "silu": 2, "swish": 2, "softsign": 3}
+ACT = {None: 0, "none": 0, "gelu": 1, "silu": 2, "swish": 2, "softsign": 3, "mul": 4}
 
 # number of kernels of this library launched so far (bench.py reports it as gpu_launches)
 LAUNCHES = 0
@@ -198,7 +198,8 @@ assert _GEMM_FIELDS == [
     "a_mn_major", "b_mn_major", "k_spans_batches", "m_per_batch", "batches", "n", "k", "a_batched", "b_batched",
     "b_batch_idx", "c_batch_idx", "out_f32", "out_pre", "out_hi", "out_lo", "ldc", "c_batch_stride", "bias", "residual",
     "aux", "colsum", "act", "aux_mode", "atomic", "split_k", "alpha", "block_n", "drop_p", "drop_seed",
-    "bias_batch_stride", "out_scale", "sk_workspace", "sk_workspace_bytes", "stream_k", "cta_group"]   # order gemm() packs in
+    "bias_batch_stride", "out_scale", "sk_workspace", "sk_workspace_bytes", "stream_k", "cta_group", "pre_mode",
+    "reserved_"]   # order gemm() packs in
 _GEMM_BUF = ctypes.create_string_buffer(ctypes.sizeof(GemmArgs))
 _GEMM_BUF_PTR = ctypes.c_void_p(ctypes.addressof(_GEMM_BUF))
 _B2T_GEMM = None
@@ -217,7 +218,7 @@ def gemm(a: Operand, b: Operand, *, m_per_batch: int, n: int, k: int, batches: i
          alpha: float = 1.0, k_spans_batches: bool = False, a_batched: bool = False, b_batched: bool = False,
          b_batch_idx: Optional[Tensor] = None, c_batch_idx: Optional[Tensor] = None, block_n: int = 0,
          drop_p: float = 0.0, drop_seed: int = 0, bias_batch_stride: int = 0, out_scale: float = 1.0,
-         stream_k: int = 0, cta_group: int = 0, on_stream: Optional[int] = None) -> None:
+         stream_k: int = 0, cta_group: int = 0, on_stream: Optional[int] = None, pre_mode: int = 0) -> None:
     """D = epilogue(alpha * A . B^T) on the tcgen05 GEMM (see b2t_gemm in include/b2t_sm100.h).
     on_stream: raw cudaStream_t to launch on instead of torch's current stream (the engine's weight-gradient stream)."""
     global _B2T_GEMM
@@ -240,7 +241,7 @@ def gemm(a: Operand, b: Operand, *, m_per_batch: int, n: int, k: int, batches: i
         ldc_, m_per_batch * ldc_ if c_batch_stride is None else c_batch_stride,
         _dp(bias), _dp(residual), _dp(aux), _dp(colsum),
         ACT[act], ACT[aux_mode], int(atomic), split_k, alpha, block_n, drop_p, drop_seed & 0xFFFFFFFFFFFFFFFF,
-        bias_batch_stride, out_scale, sk_ws, sk_bytes, sk, cta_group)
+        bias_batch_stride, out_scale, sk_ws, sk_bytes, sk, cta_group, pre_mode, 0)
     rc = _B2T_GEMM(_GEMM_BUF_PTR, ctypes.c_void_p(_lib.raw_stream() if on_stream is None else on_stream))
     if rc != 0:
         check(rc, "b2t_gemm")
