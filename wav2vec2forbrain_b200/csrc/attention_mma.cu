@@ -151,6 +151,7 @@ __global__ void __launch_bounds__(THREADS, 2)
 attn_fwd_mma_kernel(const float* __restrict__ qkv, long ld, int q_off, int k_off, int v_off, const int* __restrict__ kv_lens,
                     float* __restrict__ probs, float* __restrict__ ctx, bf16* __restrict__ ctx_hi, bf16* __restrict__ ctx_lo,
                     long ld_ctx, int T, int H, float scale, float drop_p, unsigned long long seed, int vec, uint32_t drop_thr) {
+    B2T_PDL_TRIGGER();
     using S = Smem<D>;
     constexpr int PITCH = S::PITCH;
     extern __shared__ __align__(16) uint8_t smem_raw[];
@@ -378,6 +379,7 @@ attn_bwd_mma_kernel(const float* __restrict__ qkv, long ld, int q_off, int k_off
                     const float* __restrict__ dctx, long ld_ctx, float* __restrict__ dqkv, bf16* __restrict__ dqkv_hi,
                     bf16* __restrict__ dqkv_lo, int T, int H, float scale, float drop_p, unsigned long long seed, int vec,
                     int vec_ctx, uint32_t drop_thr) {
+    B2T_PDL_TRIGGER();
     using S = Smem<D>;
     constexpr int PITCH = S::PITCH, PP = S::PPITCH;
     extern __shared__ __align__(16) uint8_t smem_raw[];

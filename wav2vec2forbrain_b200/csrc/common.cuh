@@ -136,4 +136,8 @@ __device__ __forceinline__ bool hash_drop(uint32_t folded, uint32_t seed_lo, uin
     h ^= h >> 16;
     return (h >> 8) < thr;
 }
+// Programmatic dependent launch: lets a following kernel that was launched with the programmatic-stream-serialization
+// attribute (the tcgen05 GEMM) run its prologue while this grid's last CTAs finish.  Harmless otherwise: a dependent
+// still executes griddepcontrol.wait before it touches memory, a normally launched successor ignores the trigger.
+#define B2T_PDL_TRIGGER() asm volatile("griddepcontrol.launch_dependents;" ::: "memory")
 #endif

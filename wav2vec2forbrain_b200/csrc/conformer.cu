@@ -43,6 +43,7 @@ __global__ void __launch_bounds__(256) ln_rope_fwd_kernel(const float* __restric
                                                           float* __restrict__ mean_out, float* __restrict__ rstd_out,
                                                           const float* __restrict__ cos_t, const float* __restrict__ sin_t,
                                                           int rows, int n, int T, int hd) {
+    B2T_PDL_TRIGGER();
     extern __shared__ float srow[];   // [warps][n]
     const int lane = threadIdx.x & 31;
     const int wib = threadIdx.x >> 5;
@@ -110,6 +111,7 @@ __global__ void __launch_bounds__(256) ln_rope_fwd_kernel(const float* __restric
 __global__ void rope_bwd_add_kernel(const float* __restrict__ d_rot, long ld_rot, const float* __restrict__ d_plain,
                                     long ld_plain, float* __restrict__ out, const float* __restrict__ cos_t,
                                     const float* __restrict__ sin_t, long rows, int n, int T, int hd) {
+    B2T_PDL_TRIGGER();
     const int half = hd >> 1;
     const long total = rows * n;
     for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -147,6 +149,7 @@ __device__ __forceinline__ float silu_acc_grad(float x) {
 __global__ void __launch_bounds__(256) glu_dwconv_fwd_kernel(const float* __restrict__ g, const float* __restrict__ w,
                                                              float* __restrict__ out, double* __restrict__ ssum,
                                                              double* __restrict__ ssq, int T, int D, int K) {
+    B2T_PDL_TRIGGER();
     __shared__ float s[DW_ROWS][DW_CH];
     __shared__ float sw[DW_MAX_K][DW_CH];
     __shared__ float red[2][8][DW_CH];
@@ -329,6 +332,7 @@ __global__ void __launch_bounds__(128) bn_silu_fwd_vec_kernel(const float* __res
                                                               long long* __restrict__ nbt, float* __restrict__ mean_out,
                                                               float* __restrict__ rstd_out, bf16* __restrict__ y_hi,
                                                               bf16* __restrict__ y_lo, long M, int D, int training) {
+    B2T_PDL_TRIGGER();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int c = blockIdx.x * 128 + lane * 4;
     if (c >= D) return;
@@ -379,6 +383,7 @@ __global__ void __launch_bounds__(128) bn_silu_bwd_stats_vec_kernel(const float*
                                                                     const float* __restrict__ gamma, const float* __restrict__ beta,
                                                                     float* __restrict__ dgamma, float* __restrict__ dbeta, long M,
                                                                     int D) {
+    B2T_PDL_TRIGGER();
     __shared__ float red[2][4][128];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int c = blockIdx.x * 128 + lane * 4;
@@ -433,6 +438,7 @@ __global__ void __launch_bounds__(256) glu_dwconv_bwd_kernel(const float* __rest
                                                              bf16* __restrict__ dg_hi, bf16* __restrict__ dg_lo,
                                                              float* __restrict__ dw, int T, int D, int K, long M,
                                                              int training) {
+    B2T_PDL_TRIGGER();
     extern __shared__ float dyn[];
     float (*dd)[DW_CH] = reinterpret_cast<float (*)[DW_CH]>(dyn);                       // d(dwconv out), with halo
     float (*s)[DW_CH] = reinterpret_cast<float (*)[DW_CH]>(dyn + DW_ROWS * DW_CH);      // glu, with halo

@@ -1064,6 +1064,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
         __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr_gen;
+    // Programmatic dependent launch: everything above (barrier init, TMEM allocation, tensor-map prefetch) touches no
+    // memory a predecessor writes, so under the programmatic-stream-serialization launch attribute it runs while the
+    // previous kernel of the stream drains; from here on the predecessor is complete and its writes are visible.  The
+    // trigger lets the NEXT kernel start its own prologue as soon as SMs free up behind this grid's last tiles.
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
     if (warp < EPI_WARP0) {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(REGS_CTRL));
@@ -1535,22 +1541,34 @@ int launch(const b2t_gemm_args* a, const KParams& kp, cudaStream_t stream) {
             units = kp.total_items < units_max ? kp.total_items : units_max;
         }
     }
-    if (CG == 1) {
-        kern<<<units, NUM_THREADS, C::SMEM_BYTES, stream>>>(mAh, mAl, mBh, mBl, mC, mPre, mHi, mLo, kq);
-    } else {
+    {
+        static int pdl = -1;
+        if (pdl < 0) {
+            const char* e = getenv("B2T_GEMM_PDL");
+            pdl = e ? atoi(e) : 1;
+        }
         cudaLaunchConfig_t cfg;
         memset(&cfg, 0, sizeof(cfg));
         cfg.gridDim = dim3((unsigned)(units * CG), 1, 1);
         cfg.blockDim = dim3(NUM_THREADS, 1, 1);
         cfg.dynamicSmemBytes = C::SMEM_BYTES;
         cfg.stream = stream;
-        cudaLaunchAttribute at[1];
-        at[0].id = cudaLaunchAttributeClusterDimension;
-        at[0].val.clusterDim.x = CG;
-        at[0].val.clusterDim.y = 1;
-        at[0].val.clusterDim.z = 1;
+        cudaLaunchAttribute at[2];
+        int na = 0;
+        if (CG > 1) {
+            at[na].id = cudaLaunchAttributeClusterDimension;
+            at[na].val.clusterDim.x = CG;
+            at[na].val.clusterDim.y = 1;
+            at[na].val.clusterDim.z = 1;
+            ++na;
+        }
+        if (pdl) {   // the kernel's prologue may overlap the previous kernel's tail (griddepcontrol.wait in the kernel)
+            at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            at[na].val.programmaticStreamSerializationAllowed = 1;
+            ++na;
+        }
         cfg.attrs = at;
-        cfg.numAttrs = 1;
+        cfg.numAttrs = na;
         B2T_CUDA(cudaLaunchKernelEx(&cfg, kern, mAh, mAl, mBh, mBl, mC, mPre, mHi, mLo, kq));
     }
     B2T_CHECK_LAUNCH("b2t_gemm");

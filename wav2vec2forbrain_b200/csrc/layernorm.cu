@@ -159,6 +159,7 @@ __global__ void __launch_bounds__(256) ln_fwd_vec_kernel(const float* __restrict
                                                          bf16* __restrict__ y_hi, bf16* __restrict__ y_lo,
                                                          float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows,
                                                          int n, float drop_p, unsigned long long seed) {
+    B2T_PDL_TRIGGER();
     const int lane = threadIdx.x & 31;
     const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int nwarps = (gridDim.x * blockDim.x) >> 5;
@@ -215,6 +216,7 @@ __global__ void __launch_bounds__(256, 2) ln_bwd_vec_kernel(const float* __restr
                                                          bf16* __restrict__ dx_hi, bf16* __restrict__ dx_lo, int rows, int n,
                                                          float out_drop_p, unsigned long long out_seed, float br_drop_p,
                                                          unsigned long long br_seed, const float* __restrict__ dres) {
+    B2T_PDL_TRIGGER();
     const int lane = threadIdx.x & 31;
     const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int nwarps = (gridDim.x * blockDim.x) >> 5;
@@ -284,6 +286,7 @@ __global__ void __launch_bounds__(256) ln_fwd_vec2_kernel(const float* __restric
                                                           bf16* __restrict__ y_hi, bf16* __restrict__ y_lo,
                                                           float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows,
                                                           int n, float drop_p, unsigned long long seed) {
+    B2T_PDL_TRIGGER();
     __shared__ float red[2][4][2];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int rl = warp >> 1, half = warp & 1;
@@ -348,6 +351,7 @@ __global__ void __launch_bounds__(256) ln_bwd_vec2_kernel(const float* __restric
                                                           bf16* __restrict__ dx_hi, bf16* __restrict__ dx_lo, int rows, int n,
                                                           float out_drop_p, unsigned long long out_seed, float br_drop_p,
                                                           unsigned long long br_seed, const float* __restrict__ dres) {
+    B2T_PDL_TRIGGER();
     __shared__ float red[4][2][2];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int rl = warp >> 1, half = warp & 1;
@@ -468,6 +472,7 @@ __global__ void __launch_bounds__(256) ln_bwd_cols_vec_kernel(const float* __res
                                                               float* __restrict__ dbeta, float* __restrict__ dcol, int rows, int n,
                                                               float out_drop_p, unsigned long long out_seed, float br_drop_p,
                                                               unsigned long long br_seed) {
+    B2T_PDL_TRIGGER();
     __shared__ float4 part[3][8][33];
     const int c = (blockIdx.x * 32 + threadIdx.x) * 4;
     const int r0 = blockIdx.y * LNCV_ROWS;
@@ -540,6 +545,7 @@ __global__ void __launch_bounds__(256) ln_bwd_cols_vec_kernel(const float* __res
 // p == 0 degenerates to a plain split.  Also the backward (apply to the incoming gradient).
 __global__ void dropout_kernel(const float* __restrict__ x, float* __restrict__ y, bf16* __restrict__ hi,
                                bf16* __restrict__ lo, long n, float p, unsigned long long seed) {
+    B2T_PDL_TRIGGER();
     const float scale = 1.0f / (1.0f - p);
     for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
         float v = x[i];
@@ -557,6 +563,7 @@ __global__ void dropout_kernel(const float* __restrict__ x, float* __restrict__ 
 // out[c] += sum_r x[r, c]; x row stride ld.  grid (col tiles of 32, row slabs); 32x8 threads
 __global__ void colsum_kernel(const float* __restrict__ x, float* __restrict__ out, long rows, int n, long ld,
                               long rows_per_block) {
+    B2T_PDL_TRIGGER();
     __shared__ float part[8][33];
     const int c = blockIdx.x * 32 + threadIdx.x;
     const long r0 = (long)blockIdx.y * rows_per_block;
@@ -576,6 +583,7 @@ __global__ void colsum_kernel(const float* __restrict__ x, float* __restrict__ o
 
 __global__ void axpby_kernel(const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ out, long n,
                              float alpha, float beta_) {
+    B2T_PDL_TRIGGER();
     for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
         out[i] = alpha * a[i] + (b ? beta_ * b[i] : 0.0f);
 }
