@@ -196,6 +196,17 @@ int64_t b2t_ctc_workspace_floats(int B, int T, int s_max);
 int b2t_ctc_fwd_bwd(const float* logits, int64_t ld_t, int64_t ld_b, const int64_t* targets, int s_max,
                     const int32_t* input_lens, const int64_t* target_lens, float* alpha_ws, float* nll, float* loss,
                     float* grad, int B, int T, int V, int zero_infinity, b2t_stream stream);
+/* Allocation-free variant of b2t_ctc_fwd_bwd.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same arguments minus alpha_ws: the lattice scratch is a static device array of b2t_ctc_static_max_floats()
+ * floats (2 Mi floats = 8 MiB, held by every GPU that loads the library until exit); a problem whose
+ * b2t_ctc_workspace_floats(B,T,s_max) exceeds it is rejected with an argument error.  Allocates nothing (no cudaMalloc /
+ * cudaFree / library allocation).  All calls share the array: calls that overlap on the GPU race - issue them on one
+ * stream.  The scratch needs no clearing between calls. */
+int64_t b2t_ctc_static_max_floats(void);
+int b2t_ctc_fwd_bwd_static(const float* logits, int64_t ld_t, int64_t ld_b, const int64_t* targets, int s_max,
+                           const int32_t* input_lens, const int64_t* target_lens, float* nll, float* loss, float* grad,
+                           int B, int T, int V, int zero_infinity, b2t_stream stream);
 /* argmax [B,T]; ids [B,T] = collapsed repeats without blanks (0-padded); lens [B] */
 int b2t_greedy_decode(const float* logits, int64_t ld_t, int64_t ld_b, int32_t* argmax, int32_t* ids,
                       int32_t* lens, int B, int T, int V, b2t_stream stream);

@@ -258,6 +258,43 @@ extern "C" int b2t_ctc_fwd_bwd(const float* logits, int64_t ld_t, int64_t ld_b, 
     return 0;
 }
 
+// ------------------------------------------------------------------------------------------
+// Allocation-free variant of b2t_ctc_fwd_bwd (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops, harnesses that forbid it).
+// The alpha lattice lives in a file-scope device array instead of a caller-provided buffer.  Every GPU that loads the
+// library holds these 8 MiB until exit.  All calls share the array: calls that overlap on the GPU (two streams, two
+// host threads) race.  Nothing in it has to start at zero - the kernel writes alpha[t] of a trial before the beta pass
+// reads it - so stale contents of the previous call are harmless.
+// ------------------------------------------------------------------------------------------
+#define B2T_CTC_STATIC_MAX_FLOATS (2 * 1024 * 1024)   /* = b2t_ctc_static_max_floats(); e.g. B=128, T=118, S<=63 */
+static __device__ __align__(256) float g_ctc_static_ws[B2T_CTC_STATIC_MAX_FLOATS];
+
+extern "C" int64_t b2t_ctc_static_max_floats(void) { return (int64_t)B2T_CTC_STATIC_MAX_FLOATS; }
+
+extern "C" int b2t_ctc_fwd_bwd_static(const float* logits, int64_t ld_t, int64_t ld_b, const int64_t* targets, int s_max,
+                                      const int32_t* input_lens, const int64_t* target_lens, float* nll, float* loss,
+                                      float* grad, int B, int T, int V, int zero_infinity, b2t_stream stream_) {
+    B2T_CHECK_ARG(B > 0 && T > 0 && s_max >= 0, "b2t_ctc_fwd_bwd_static: bad sizes B=%d T=%d S=%d", B, T, s_max);
+    const int64_t need = b2t_ctc_workspace_floats(B, T, s_max);
+    B2T_CHECK_ARG(need <= (int64_t)B2T_CTC_STATIC_MAX_FLOATS,
+                  "b2t_ctc_fwd_bwd_static: B=%d T=%d S=%d needs %lld workspace floats, the static scratch holds %d "
+                  "(use b2t_ctc_fwd_bwd with a caller-owned workspace)", B, T, s_max, (long long)need, B2T_CTC_STATIC_MAX_FLOATS);
+    // The array's name is a host-side stand-in in host code, not a device address: resolve it once per device, with
+    // that device current.
+    static float* ws_of_device[64] = {};
+    int dev = -1;
+    B2T_CUDA(cudaGetDevice(&dev));
+    B2T_CHECK_ARG(dev >= 0 && dev < 64, "b2t_ctc_fwd_bwd_static: device index %d out of range", dev);
+    float* ws = ws_of_device[dev];
+    if (!ws) {
+        B2T_CUDA(cudaGetSymbolAddress((void**)&ws, g_ctc_static_ws));
+        B2T_CHECK_ARG(ws != nullptr, "b2t_ctc_fwd_bwd_static: cudaGetSymbolAddress returned NULL");
+        ws_of_device[dev] = ws;
+    }
+    return b2t_ctc_fwd_bwd(logits, ld_t, ld_b, targets, s_max, input_lens, target_lens, ws, nll, loss, grad, B, T, V,
+                           zero_infinity, stream_);
+}
+
 extern "C" int b2t_greedy_decode(const float* logits, int64_t ld_t, int64_t ld_b, int32_t* argmax, int32_t* ids,
                                  int32_t* lens, int B, int T, int V, b2t_stream stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
