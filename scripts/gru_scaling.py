@@ -1,4 +1,5 @@
-import sys; sys.path.insert(0,'/root/repo'); sys.path.insert(0,'/root/repo/scripts')
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__)))); sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 import torch
 from wav2vec2forbrain_b200 import ops, _lib
 _lib.ensure_device()

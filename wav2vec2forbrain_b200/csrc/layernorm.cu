@@ -421,6 +421,130 @@ __global__ void __launch_bounds__(256) ln_bwd_vec2_kernel(const float* __restric
     }
 }
 
+// One-pass LayerNorm backward for wide rows: ln_bwd_vec2_kernel's row math in a loop over row groups (grid = 2 CTAs per
+// SM), with the column sums (dgamma, dbeta, dcol) accumulated in registers - a thread's columns are the same in every
+// iteration - and folded through 12 KB of shared memory into one vector red.add per 4 columns and CTA at the end.
+// The separate column kernel re-read dy, x and dx (12 of the 32 bytes per element of the two-kernel version).
+template <int VPL>
+__global__ void __launch_bounds__(256, 2) ln_bwd_fused_kernel(const float* __restrict__ dy, const float* __restrict__ x,
+                                                             const float* __restrict__ gamma, const float* __restrict__ mean_in,
+                                                             const float* __restrict__ rstd_in, float* __restrict__ dx,
+                                                             bf16* __restrict__ dx_hi, bf16* __restrict__ dx_lo,
+                                                             float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                             float* __restrict__ dcol, int rows, int n, float out_drop_p,
+                                                             unsigned long long out_seed, float br_drop_p,
+                                                             unsigned long long br_seed, const float* __restrict__ dres) {
+    B2T_PDL_TRIGGER();
+    __shared__ float red[2][4][2][2];
+    __shared__ float csum[3][1024];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int rl = warp >> 1, half = warp & 1;
+    const float inv_n = 1.0f / (float)n;
+    const float out_scale = 1.0f / (1.0f - out_drop_p), br_scale = 1.0f / (1.0f - br_drop_p);
+    for (int i = threadIdx.x; i < 3 * 1024; i += 256) (&csum[0][0])[i] = 0.0f;
+    float ag[VPL][4], ab[VPL][4], ac[VPL][4];
+    float4 ga[VPL];
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+        const int c = ((half * VPL + i) * 32 + lane) * 4;
+        ga[i] = c < n ? *reinterpret_cast<const float4*>(gamma + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) ag[i][e] = ab[i][e] = ac[i][e] = 0.0f;
+    }
+    const int groups = (rows + 3) / 4;
+    int par = 0;
+    for (int grp = blockIdx.x; grp < groups; grp += gridDim.x, par ^= 1) {
+        const int row = grp * 4 + rl;
+        const bool row_ok = row < rows;
+        const float mean = row_ok ? mean_in[row] : 0.0f, rstd = row_ok ? rstd_in[row] : 0.0f;
+        float xh[VPL][4], g[VPL][4];
+        float4 d4[VPL], x4[VPL];
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {   // all loads of the row first
+            const int c = ((half * VPL + i) * 32 + lane) * 4;
+            const long off = (long)row * n + c;
+            const bool ok = row_ok && c < n;
+            d4[i] = ok ? *reinterpret_cast<const float4*>(dy + off) : make_float4(0.f, 0.f, 0.f, 0.f);
+            x4[i] = ok ? *reinterpret_cast<const float4*>(x + off) : make_float4(0.f, 0.f, 0.f, 0.f);
+            if (ok && dres && (lane & 7) == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(dres + off));
+        }
+        float s1 = 0.0f, s2 = 0.0f;
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            const int c = ((half * VPL + i) * 32 + lane) * 4;
+            const long off = (long)row * n + c;
+            const bool ok = row_ok && c < n;
+            float d[4] = {d4[i].x, d4[i].y, d4[i].z, d4[i].w};
+            const float xv[4] = {x4[i].x, x4[i].y, x4[i].z, x4[i].w};
+            const float gv[4] = {ga[i].x, ga[i].y, ga[i].z, ga[i].w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                if (out_drop_p > 0.0f && ok)
+                    d[e] = hash_uniform(out_seed, (unsigned long long)(off + e)) < out_drop_p ? 0.0f : d[e] * out_scale;
+                xh[i][e] = ok ? (xv[e] - mean) * rstd : 0.0f;
+                g[i][e] = d[e] * gv[e];
+                s1 += g[i][e];
+                s2 += g[i][e] * xh[i][e];
+                ag[i][e] += d[e] * xh[i][e];
+                ab[i][e] += d[e];
+            }
+        }
+        s1 = warp_sum(s1);
+        s2 = warp_sum(s2);
+        if (lane == 0) {
+            red[par][rl][half][0] = s1;
+            red[par][rl][half][1] = s2;
+        }
+        __syncthreads();
+        s1 = (red[par][rl][0][0] + red[par][rl][1][0]) * inv_n;
+        s2 = (red[par][rl][0][1] + red[par][rl][1][1]) * inv_n;
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            const int c = ((half * VPL + i) * 32 + lane) * 4;
+            if (row_ok && c < n) {
+                const long off = (long)row * n + c;
+                float o[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) o[e] = rstd * (g[i][e] - s1 - xh[i][e] * s2);
+                if (dres) {
+                    const float4 r4 = *reinterpret_cast<const float4*>(dres + off);
+                    o[0] += r4.x, o[1] += r4.y, o[2] += r4.z, o[3] += r4.w;
+                }
+                if (dx) *reinterpret_cast<float4*>(dx + off) = make_float4(o[0], o[1], o[2], o[3]);
+                if (br_drop_p > 0.0f && (dx_hi || dcol)) {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                        o[e] = hash_uniform(br_seed, (unsigned long long)(off + e)) < br_drop_p ? 0.0f : o[e] * br_scale;
+                }
+                if (dx_hi) store_split4(o, dx_hi, dx_lo, off);
+#pragma unroll
+                for (int e = 0; e < 4; ++e) ac[i][e] += o[e];
+            }
+        }
+    }
+    __syncthreads();   // csum was zeroed by the first loop of the kernel before anyone adds to it
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+        const int c = ((half * VPL + i) * 32 + lane) * 4;
+        if (c < n) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                atomicAdd(&csum[0][c + e], ag[i][e]);
+                atomicAdd(&csum[1][c + e], ab[i][e]);
+                atomicAdd(&csum[2][c + e], ac[i][e]);
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 3 * (n >> 2); i += 256) {
+        const int which = i / (n >> 2), c = (i - which * (n >> 2)) * 4;
+        float* dst = which == 0 ? dgamma : (which == 1 ? dbeta : dcol);
+        if (!dst) continue;
+        const float4 v = *reinterpret_cast<const float4*>(&csum[which][c]);
+        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + c), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+    }
+}
+
 // column sums of the LayerNorm backward: dgamma += sum_r dy.xhat, dbeta += sum_r dy, dcol += sum_r mask.dx
 // grid (ceil(n / 32), row slabs), block (32, 8): a warp reads 128 contiguous bytes of a row.
 constexpr int LNC_ROWS = 128;
@@ -653,6 +777,28 @@ extern "C" int b2t_layernorm_bwd(const float* dy, const float* x, const float* g
 #define VCALL(V)                                                                                                          \
     ln_bwd_vec_kernel<V><<<vgrid, 256, 0, stream>>>(dy, x, gamma, mean, rstd, dx, (bf16*)dx_hi, (bf16*)dx_lo, rows, n, out_drop_p, \
                                                     (unsigned long long)out_seed, br_drop_p, (unsigned long long)br_seed, dres)
+        const bool cols16 = (((uintptr_t)dgamma | (uintptr_t)dbeta | (uintptr_t)dcol) & 15) == 0;
+        static int fused_on = -1;
+        if (fused_on < 0) {
+            const char* e = getenv("B2T_LN_BWD_FUSED");
+            fused_on = e ? atoi(e) : 1;
+        }
+        if (n >= 512 && (dgamma || dbeta || dcol) && cols16 && fused_on) {
+            // one pass: row gradients and column sums together
+            const int v2 = (n / 4 + 63) / 64, groups = (rows + 3) / 4;
+            int sms = 148, dev = 0;
+            cudaGetDevice(&dev);
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+            const int gf = groups < 2 * sms ? groups : 2 * sms;
+#define FCALL(V)                                                                                                          \
+    ln_bwd_fused_kernel<V><<<gf, 256, 0, stream>>>(dy, x, gamma, mean, rstd, dx, (bf16*)dx_hi, (bf16*)dx_lo, dgamma, dbeta, dcol, \
+                                                   rows, n, out_drop_p, (unsigned long long)out_seed, br_drop_p,                 \
+                                                   (unsigned long long)br_seed, dres)
+            if (v2 <= 2) { FCALL(2); } else if (v2 <= 3) { FCALL(3); } else { FCALL(4); }
+#undef FCALL
+            B2T_CHECK_LAUNCH("b2t_layernorm_bwd (fused)");
+            return 0;
+        }
         if (n >= 512) {
             const int v2 = (n / 4 + 63) / 64, g2 = (rows + 3) / 4;
 #define V2CALL(V)                                                                                                         \
