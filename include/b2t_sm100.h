@@ -104,6 +104,11 @@ typedef struct {
 int b2t_gemm(const b2t_gemm_args* args, b2t_stream stream);
 /* cap the persistent grid at `sms` CTAs (0 = all SMs): leaves SMs to a concurrent collective (also env B2T_GEMM_SMS) */
 int b2t_gemm_set_sm_limit(int sms);
+/* 1: work items are handed out by the hardware's cluster launch control (one cluster launched per item; resident
+ * clusters cancel and take over the items of clusters that are not resident yet) instead of a fixed persistent grid with
+ * strided item lists - for GEMMs that share the device with long-running collective kernels.  0 (default): fixed grid.
+ * Also env B2T_GEMM_CLC. */
+int b2t_gemm_set_dynamic_schedule(int on);
 /* bytes of b2t_gemm_args.sk_workspace that cover every tile shape on the current device */
 int64_t b2t_gemm_workspace_bytes(void);
 

@@ -359,3 +359,42 @@ def test_pre_mode_stores_the_backward_factor(cg, act, n):
     ref_dx = (dy.double() @ w.double()) * pre.double()
     assert rel(dx, ref_dx) < 2e-5
     assert rel(cs, ref_dx.sum(0)) < 1e-4
+
+
+def test_dynamic_schedule_cluster_launch_control():
+    """opt-in dynamic schedule (one cluster per work item, cluster launch control): same results as the fixed grid, on
+    multi-wave pair tiles with every epilogue stage, single-CTA tiles, split-K, and a grid smaller than the device"""
+    ops = _ops()
+    from wav2vec2forbrain_b200 import _lib
+    lib = _lib.lib()
+    cases = [(3776, 4096, 256, 2, 1), (3776, 1024, 1024, 2, 1), (2048, 512, 3776, 2, 4), (1000, 328, 520, 1, 1), (260, 256, 64, 2, 1)]
+    try:
+        for m, n, k, cg, sk in cases:
+            a, b = rnd(m, k, seed=31, scale=0.3), rnd(n, k, seed=32, scale=0.3)
+            bias, res = rnd(n, seed=33), rnd(m, n, seed=34)
+            ah, al = ops.split(a)
+            bh, bl = ops.split(b)
+            outs = []
+            for dyn in (0, 1):
+                lib.b2t_gemm_set_dynamic_schedule(dyn)
+                if sk > 1:
+                    out = torch.ones(m, n, device="cuda")
+                    ops.gemm(ops.kmajor(ah, al), ops.kmajor(bh, bl), m_per_batch=m, n=n, k=k, out_f32=out, atomic=True, split_k=sk,
+                             cta_group=cg)
+                    outs.append((out,))
+                else:
+                    out = torch.full((m, n), float("nan"), device="cuda")
+                    hi = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
+                    cs = torch.zeros(n, device="cuda")
+                    ops.gemm(ops.kmajor(ah, al), ops.kmajor(bh, bl), m_per_batch=m, n=n, k=k, out_f32=out, out_hi=hi, bias=bias,
+                             residual=res, colsum=cs, act="gelu", drop_p=0.1, drop_seed=5, cta_group=cg)
+                    outs.append((out, hi.float(), cs))
+                torch.cuda.synchronize()
+            for x0, x1 in zip(*outs):
+                assert torch.isfinite(x1).all()
+                assert rel(x1, x0) < 1e-5
+            ref = a.double() @ b.double().t()
+            if sk > 1:
+                assert rel(outs[1][0], ref + 1.0) < 2e-5
+    finally:
+        lib.b2t_gemm_set_dynamic_schedule(0)

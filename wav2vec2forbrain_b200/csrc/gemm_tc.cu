@@ -62,6 +62,7 @@ struct KParams {
     unsigned long long drop_seed;
     int m_tiles, n_tiles, total_items;
     // stream-K: the tiles' k-blocks form one line of `sk_units` units cut into gridDim.x equal ranges
+    int dynamic;       // work items are handed out by cluster launch control (one cluster launched per item, see Sched)
     int stream_k;
     int sk_tile0;      // tiles [0, sk_tile0) run as whole tiles, tiles [sk_tile0, tiles) form the stream-K line
     long long sk_units;
@@ -81,13 +82,59 @@ struct Item {
 // `idx` / `G`: this CTA's position among, and the number of, scheduling units of the grid - CTAs for cta_group::1,
 // CTA pairs for cta_group::2 (both CTAs of a pair walk the same item list; the pair's tile is 2 x BM rows, the
 // CTA of cluster rank r owns row block m_blk = 2 * (pair row block) + r, kept in it.m_blk).
+//
+// Dynamic schedule (p.dynamic; opt-in, b2t_gemm_set_dynamic_schedule / B2T_GEMM_CLC=1): the grid has ONE cluster per work item and the hardware's cluster launch
+// control hands the items out.  A resident cluster processes its own item, and while it does, asks to CANCEL the launch
+// of a not-yet-launched cluster (clusterlaunchcontrol.try_cancel): if that succeeds it owns that cluster's item next,
+// if it fails nothing is left and the cluster finishes.  Clusters that cannot become resident - SMs held by an NCCL
+// kernel, by the GEMM of the other stream, by the previous kernel's tail under programmatic dependent launch - simply
+// have their items taken by the resident ones; with a fixed persistent grid and statically strided item lists those CTAs
+// started late and then ran their WHOLE list (up to twice the kernel's time, measured as exposed all-reduce time).
+// Responses arrive through a ring of two 16-byte slots per CTA (multicast to both CTAs of a pair): a query is issued as
+// soon as every consumer role of the cluster (TMA producers, MMA issuer, epilogue warps) has read the slot's previous
+// response, i.e. a cluster is committed to at most two items beyond the one its epilogue works on.
+constexpr int CLC_OFF = 256;        // byte offset of {clc_full[2], clc_empty[2], pad, resp[2]} inside the barrier block
+constexpr int CLC_RESP_OFF = 320;
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity);
+__device__ __forceinline__ void mbar_arrive(uint32_t bar);
+__device__ __forceinline__ void mbar_arrive_cluster_release(uint32_t cluster_bar);
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank);
+// (valid, first CTA id of the cancelled cluster) of a response slot
+__device__ __forceinline__ bool clc_read(uint32_t resp_addr, int& ctaid_x) {
+    uint32_t x = 0, y, z, valid;
+    asm volatile(
+        "{\n\t.reg .pred p1;\n\t.reg .b128 r;\n\t"
+        "ld.shared.b128 r, [%4];\n\t"
+        "clusterlaunchcontrol.query_cancel.is_canceled.pred.b128 p1, r;\n\t"
+        "selp.u32 %3, 1, 0, p1;\n\t"
+        "@p1 clusterlaunchcontrol.query_cancel.get_first_ctaid.v4.b32.b128 {%0, %1, %2, _}, r;\n\t}"
+        : "+r"(x), "=r"(y), "=r"(z), "=r"(valid)
+        : "r"(resp_addr)
+        : "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the slot is rewritten by the async proxy
+    ctaid_x = (int)x;
+    return valid != 0;
+}
+__device__ __forceinline__ void clc_issue(uint32_t resp_addr, uint32_t bar) {
+    asm volatile(
+        "clusterlaunchcontrol.try_cancel.async.shared::cta.mbarrier::complete_tx::bytes.multicast::cluster::all.b128 [%0], [%1];"
+        ::"r"(resp_addr), "r"(bar)
+        : "memory");
+}
+
 struct Sched {
     const KParams& p;
     const int idx, G, cg, rank;
     int item;
     long long u, u_end;
-    __device__ __forceinline__ Sched(const KParams& p_, int cg_, int rank_)
-        : p(p_), idx((int)blockIdx.x / cg_), G((int)gridDim.x / cg_), cg(cg_), rank(rank_), item((int)blockIdx.x / cg_), u(0), u_end(0) {
+    // dynamic schedule: this consumer's position in the response ring
+    uint32_t clc_base, clc_empty_leader, use;
+    bool first, warp_consumer;
+    // bar_base: shared address of the CTA's barrier block; warp_consumer: next() is executed by all 32 lanes of a warp
+    __device__ __forceinline__ Sched(const KParams& p_, int cg_, int rank_, uint32_t bar_base, bool warp_consumer_)
+        : p(p_), idx((int)blockIdx.x / cg_), G((int)gridDim.x / cg_), cg(cg_), rank(rank_), item((int)blockIdx.x / cg_), u(0), u_end(0),
+          clc_base(bar_base + CLC_OFF), use(0), first(true), warp_consumer(warp_consumer_) {
+        clc_empty_leader = cg_ == 2 ? mapa_u32(bar_base + CLC_OFF + 16, 0) : bar_base + CLC_OFF + 16;
         if (p.stream_k && idx < p.sk_G) {
             u = (long long)idx * p.sk_units / p.sk_G;
             u_end = (long long)(idx + 1) * p.sk_units / p.sk_G;
@@ -100,6 +147,26 @@ struct Sched {
         it.batch = t / p.m_tiles;
     }
     __device__ __forceinline__ bool next(Item& it) {
+        if (p.dynamic) {
+            if (first) {
+                first = false;
+            } else {
+                const uint32_t slot = use & 1u;
+                mbar_wait(clc_base + 8u * slot, (use >> 1) & 1u);
+                int ctaid;
+                const bool valid = clc_read(clc_base + (CLC_RESP_OFF - CLC_OFF) + 16u * slot, ctaid);
+                if (warp_consumer) __syncwarp();
+                if (!warp_consumer || (threadIdx.x & 31) == 0) {   // this role has read the slot
+                    if (cg == 2)
+                        mbar_arrive_cluster_release(clc_empty_leader + 8u * slot);
+                    else
+                        mbar_arrive(clc_empty_leader + 8u * slot);
+                }
+                ++use;
+                if (!valid) return false;
+                item = ctaid / cg;
+            }
+        }
         if (!p.stream_k) {
             if (item >= p.total_items) return false;
             const int per_split = p.n_tiles * p.m_tiles * p.batches;
@@ -108,7 +175,7 @@ struct Sched {
             it.kb0 = (int)(((long long)it.split * p.num_k_blocks) / p.split_k);
             it.kb1 = (int)(((long long)(it.split + 1) * p.num_k_blocks) / p.split_k);
             it.mode = 0, it.n_contrib = 0, it.owner = 0;
-            item += G;
+            if (!p.dynamic) item += G;
             return true;
         }
         // Hybrid schedule: the last (tiles mod G) tiles would be a mostly empty wave, so THEIR k-blocks are cut into G
@@ -202,6 +269,9 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar) {
     // relaxed: the TMEM reads this arrive publishes are ordered by tcgen05.wait::ld + tcgen05.fence::before_thread_sync; a
     // release at cluster scope would first drain the warp's outstanding global stores (MEMBAR, seen as stall_membar in ncu)
     asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster_release(uint32_t cluster_bar) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
 }
 // the load lands in THIS CTA's shared memory, its bytes are counted on the pair leader's barrier
 __device__ __forceinline__ void tma_load_3d_pair(uint32_t dst, const CUtensorMap* map, uint32_t cluster_bar, int c0, int c1,
@@ -1041,6 +1111,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
         for (int s = 0; s < 2; ++s) {
             mbar_init(tfull_bar(s), 1);
             mbar_init(tempty_bar(s), CG * NUM_EPI_WARPS);
+            // cluster-launch-control ring (Sched): full = 16 response bytes; empty (used in the leader) = every consumer role
+            // of the cluster: its 2 + NUM_EPI_WARPS, plus the peer's 1 + NUM_EPI_WARPS
+            mbar_init(bar_base + CLC_OFF + 8u * s, 1);
+            mbar_init(bar_base + CLC_OFF + 16u + 8u * s, CG == 2 ? 2 * NUM_EPI_WARPS + 3 : NUM_EPI_WARPS + 2);
+        }
+        if (p.dynamic) {
+            mbar_expect_tx(bar_base + CLC_OFF, 16);
+            mbar_expect_tx(bar_base + CLC_OFF + 8u, 16);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -1078,7 +1156,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            Sched sch(p, CG, rank);
+            Sched sch(p, CG, rank, bar_base, false);
             Item it;
             auto tma_load = [&](uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2) {
                 if (CG == 2)
@@ -1171,7 +1249,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
         int stage = 0;
         uint32_t phase = 0;
         int local_iter = 0;
-        Sched sch(p, CG, rank);
+        Sched sch(p, CG, rank, bar_base, true);
         Item it;
         for (; sch.next(it); ++local_iter) {
             const int kb0 = it.kb0, kb1 = it.kb1;
@@ -1210,6 +1288,29 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
                 }
             }
         }
+    } else if (warp == 2) {
+        // ================================ scheduler (dynamic schedule only) ================================
+        // One thread per CTA follows the response ring: it re-arms each slot's barrier after a response has landed and
+        // stops at the first failed cancellation; the pair leader's thread also issues the queries (multicast to both
+        // CTAs), each as soon as the slot's previous response has been read by every consumer role of the cluster.
+        if (p.dynamic && lane == 0) {
+            const uint32_t clc_full0 = bar_base + CLC_OFF, clc_empty0 = bar_base + CLC_OFF + 16u;
+            const uint32_t resp0 = bar_base + CLC_RESP_OFF;
+            if (rank == 0) clc_issue(resp0, clc_full0);
+            for (uint32_t use = 0;;) {
+                const uint32_t slot = use & 1u;
+                mbar_wait(clc_full0 + 8u * slot, (use >> 1) & 1u);
+                int ctaid;
+                const bool valid = clc_read(resp0 + 16u * slot, ctaid);
+                mbar_expect_tx(clc_full0 + 8u * slot, 16);   // arm the slot's next use (issued only after its empty barrier)
+                ++use;
+                if (!valid) break;
+                if (rank == 0) {
+                    if (use >= 2) mbar_wait(clc_empty0 + 8u * (use & 1u), ((use - 2) >> 1) & 1u);
+                    clc_issue(resp0 + 16u * (use & 1u), clc_full0 + 8u * (use & 1u));
+                }
+            }
+        }
     }
     } else {
         asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(REGS_EPI));
@@ -1224,7 +1325,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmAh, const __grid_constant__
         constexpr bool EPI_IN = EMODE != 2;
         if (!EPI_IN) F &= ~(F_AUX | F_RES);   // (the host never selects this instantiation with either input set)
         asm volatile("" : "+r"(F));   // pin the stage bits in a register (else ptxas re-reads the constant bank per test)
-        Sched sch(p, CG, rank);
+        Sched sch(p, CG, rank, bar_base, true);
         Item it;
         const uint32_t tempty_remote0 = CG == 2 ? mapa_u32(tempty_bar(0), 0) : 0u;   // the leader's tmem_empty barriers
         float* const epi_buf =
@@ -1474,6 +1575,11 @@ __attribute__((visibility("hidden"))) int b2t_g_sm_limit = 0;
 #else
 extern __attribute__((visibility("hidden"))) int b2t_g_sm_limit;
 #endif
+#if B2T_GEMM_PART == 0
+__attribute__((visibility("hidden"))) int b2t_g_dynamic = -1;
+#else
+extern __attribute__((visibility("hidden"))) int b2t_g_dynamic;
+#endif
 #define g_sm_limit b2t_g_sm_limit
 // internal to the library (hidden: not part of the C ABI of include/b2t_sm100.h)
 extern "C" __attribute__((visibility("hidden"))) int b2t_gemm_part1(const b2t_gemm_args* a, const void* kparams, int bn, int cg, void* stream);
@@ -1531,6 +1637,20 @@ int launch(const b2t_gemm_args* a, const KParams& kp, cudaStream_t stream) {
     const int units_max = num_sms() / CG;   // CTAs (CG == 1) or CTA pairs (CG == 2) of the persistent grid
     int units = kp.total_items < units_max ? kp.total_items : units_max;
     KParams kq = kp;
+    {
+        // Off by default: measured on the step it costs more than it gains where it could be measured (round 2, one box:
+        // isolated 240-tile GEMMs +3 us of 72, conformer step 52.7 -> 54.1 ms at 1 GPU, 54.7 -> 56.8 ms at 2 GPUs with the
+        // exposed all-reduce unchanged at 2.2-2.4 ms).  Its case is an 8-GPU box where NCCL kernels hold SMs for long.
+        int& clc = b2t_g_dynamic;
+        if (clc < 0) {
+            const char* e = getenv("B2T_GEMM_CLC");
+            clc = e ? atoi(e) : 0;
+        }
+        // dynamic schedule: one cluster per work item, handed out by cluster launch control (see Sched); the stream-K
+        // ranges and an explicit SM limit keep the fixed persistent grid
+        kq.dynamic = clc && !kq.stream_k && !(g_sm_limit > 0) && !kq.debug;
+        if (kq.dynamic) units = kp.total_items;
+    }
     if (kq.stream_k) {
         // the stream-K line is cut into one range per unit of the FULL grid (the host computed sk_tile0 for it); every
         // CTA is resident (grid <= #SMs, 1 CTA/SM), which the owners' waits rely on
@@ -1599,6 +1719,11 @@ int dispatch_major(const b2t_gemm_args* a, const KParams& kp, cudaStream_t s) {
 #if B2T_GEMM_PART == 0
 extern "C" int b2t_gemm_set_sm_limit(int sms) {
     g_sm_limit = sms > 0 ? sms : 0;
+    return 0;
+}
+
+extern "C" int b2t_gemm_set_dynamic_schedule(int on) {
+    b2t_g_dynamic = on ? 1 : 0;
     return 0;
 }
 
