@@ -52,6 +52,15 @@ def conv(B, T=118, D=1024, K=31):
     timeit("bn_silu_bwd_stats", lambda: ops.bn_silu_bwd_stats(ds, dwo, mean, rstd, ga, be), bytes_=M * D * 8)
     timeit("glu_dwconv_bwd", lambda: ops.glu_dwconv_bwd(ds, dwo, g, w, mean, rstd, ga, be, dgam, dbet, B, T, True), bytes_=M * D * 24)
 
+def rope(B, T=118, D=1024, hd=64):
+    M = B * T
+    x = rnd(M, D); g = rnd(D); b = rnd(D); inv = torch.exp(-torch.arange(0, hd, 2, device="cuda").float() / hd * 9.21)
+    cos, sin = ops.rope_table(inv, T, hd)
+    drot = rnd(M, D); dplain = rnd(M, D)
+    timeit(f"ln_rope_fwd [{M},{D}] plain+rotated hi/lo", lambda: ops.layernorm_rope_fwd(x, g, b, 1e-5, cos, sin, T, hd), bytes_=M * D * 12)
+    timeit(f"rope_bwd_add [{M},{D}]", lambda: ops.rope_bwd_add(drot, dplain, cos, sin, T, hd), bytes_=M * D * 12)
+
+
 def pre(B, T=500, C=256):
     x = rnd(B, T, C); taps = torch.softmax(rnd(20), 0).repeat(C, 1).contiguous()
     timeit(f"smooth_fwd B={B} (hi/lo out)", lambda: ops.smooth_fwd(x, taps, 9), bytes_=B * T * C * 8)
@@ -62,6 +71,8 @@ if __name__ == "__main__":
         pre(64); pre(32); sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "ln":
         ln(3776, 1024); sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "rope":
+        rope(32); sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "conv":
         conv(32); sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "gru":
@@ -72,3 +83,5 @@ if __name__ == "__main__":
     attn(64, 12); attn(32, 16)
     ln(7552, 768); ln(3776, 1024)
     conv(32)
+    rope(32)
+    pre(64)

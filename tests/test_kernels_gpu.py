@@ -130,7 +130,8 @@ def test_attention_dropout_and_key_mask(T, d):
     assert rel(dh.double() + dl.double(), x.grad) < 3e-5
 
 
-@pytest.mark.parametrize("B,T,H,ndir,h0", [(3, 17, 32, 2, False), (5, 30, 64, 1, True), (20, 118, 512, 2, False)])
+@pytest.mark.parametrize("B,T,H,ndir,h0", [(3, 17, 32, 2, False), (5, 30, 64, 1, True), (20, 118, 512, 2, False),
+                                            (64, 40, 512, 2, True), (100, 25, 512, 2, False), (128, 20, 512, 1, False)])
 def test_gru_recurrence_fwd_bwd(B, T, H, ndir, h0):
     ops = _ops()
     M = B * T
