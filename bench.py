@@ -562,8 +562,10 @@ def gemm_roofline(model, opt, batch, step, peaks, workload_key="base"):
     step_ms = e0.elapsed_time(e1)
     achieved = flops / (t_ms * 1e-3) / 1e12
     peak = peaks["bf16_tflops_sustained"]
-    traffic = None   # DRAM bytes per GEMM launch from the committed ncu capture (profiles/gemm_traffic_r01.json)
-    tpath = os.path.join(REPO, "profiles", "gemm_traffic_r01.json")
+    traffic = None   # DRAM bytes per GEMM launch from the committed ncu capture (scripts/gpu_traffic.sh -> scripts/traffic_json.py)
+    tpath = os.path.join(REPO, "profiles", "gemm_traffic_r02.json")
+    if not os.path.exists(tpath):
+        tpath = os.path.join(REPO, "profiles", "gemm_traffic_r01.json")
     if os.path.exists(tpath):
         with open(tpath) as fh:
             tj = json.load(fh).get(workload_key)
