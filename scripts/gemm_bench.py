@@ -152,6 +152,11 @@ if __name__ == "__main__":
         for nm, fl in EPI_CASES:
             bench_epi("outproj (N=1024,K=1024) " + nm, M, 1024, 1024, bn=0, cg=2, **fl)
         sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "epi3":   # short run for ncu: single-wave GEMM with / without the residual input
+        ops.STREAM_K = False
+        bench_epi("outproj f32+bias", M, 1024, 1024, bn=0, iters=2, f32=1, bias=1)
+        bench_epi("outproj f32+bias+res", M, 1024, 1024, bn=0, iters=2, f32=1, bias=1, res=1)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "prof2":   # short run for ncu --set full: the pair kernel, epilogue-bound and MMA-bound
         ops.STREAM_K = False
         bench("ffn1 K=64 (epilogue-bound)", M, 4096, 64, True, cg=2, stream_k=-1, out="split", iters=1)
