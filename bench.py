@@ -345,7 +345,8 @@ def run_ours(args):
     dp = None
     if multi:
         dp = bdist.DataParallel(model)
-        dp.attach_optimizer(opt)
+        # no gradient clipping in this loop (the reference's default): the optimizer may wait per parameter group
+        dp.attach_optimizer(opt, lazy=os.environ.get("B2T_DP_LAZY", "1") == "1")
     hb = make_host_batch(B, seed=1234 + rank, pin=True)
     batch = to_device_batch(models, hb, dev)
     torch.cuda.synchronize()

@@ -43,6 +43,19 @@ def init_process_group(backend: Optional[str] = None) -> None:
         torch.cuda.set_device(local_rank)
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     os.environ.setdefault("MASTER_PORT", "29500")
+    if backend == "nccl" and os.environ.get("B2T_NCCL_HIPRI", "1") == "1":
+        # NCCL's kernels on a high-priority stream: the compute stream runs persistent one-CTA-per-SM GEMMs back to back
+        # (programmatic dependent launch, a second stream for weight gradients), so at normal priority a collective's CTAs
+        # can wait a long time for SMs - measured at 2 GPUs as an intermittent 17-65 ms of exposed all-reduce per step
+        # where 1.5-2.5 ms is the norm.  At high priority they are placed first whenever a GEMM's CTAs retire.
+        try:
+            opts = dist.ProcessGroupNCCL.Options()
+            opts.is_high_priority_stream = True
+            dist.init_process_group(backend=backend, rank=rank, world_size=world, pg_options=opts)
+            return
+        except Exception:        # an older / different torch: plain initialisation
+            if dist.is_initialized():
+                return
     dist.init_process_group(backend=backend, rank=rank, world_size=world)
 
 
@@ -70,7 +83,7 @@ class _BucketBase:
         self.group = process_group
         self.world = dist.get_world_size(process_group)
         self.overlap = overlap and torch.cuda.is_available()
-        self.stream = torch.cuda.Stream() if self.overlap else None
+        self.stream = torch.cuda.Stream(priority=-1) if self.overlap else None
         self._avg = dist.get_backend(process_group) == "nccl"      # gloo has no ReduceOp.AVG
         self.enabled = True          # bench.py switches the collective off to measure the exposed communication
         self.bytes_per_step = 0
@@ -176,20 +189,41 @@ class ArenaBuckets(_BucketBase):
     def _launch(self, bi: int) -> None:
         self._launched[bi] = True
         work = self._all_reduce(self.buckets[bi])
-        self._work.append(work)
+        self._work.append((bi, work))
 
     # ---- end of backward ------------------------------------------------------------------------------------
-    def finish(self) -> None:
+    lazy = False      # DataParallel.attach_optimizer(..., lazy=True): see wait_prefix
+
+    def finish(self, force: bool = False) -> None:
+        """Everything that has not left yet is launched; the compute stream then waits for all of it - unless `lazy`, where
+        the waiting is left to wait_prefix() calls of the optimizer (and to the finish(force=True) after its step)."""
+        if not self._active:
+            return
+        self.node_end("")
+        if self.lazy and not force:
+            return
+        if self.overlap:
+            for _, w in self._work:
+                if w is not None:
+                    w.wait()          # the current (compute) stream waits for that collective
+        self._reset()
+
+    def wait_prefix(self, prefix: str) -> None:
+        """The compute stream waits for the buckets of one autograd node only ("brain_encoder." / "w2v_encoder."): the
+        optimizer updates the encoder's parameters while the last buckets - the brain encoder's, whose backward runs
+        last - are still being reduced."""
         if not self._active:
             return
         self.node_end("")
         if self.overlap:
-            with torch.cuda.stream(self.stream):
-                for w in self._work:
+            rest = []
+            for bi, w in self._work:
+                if self.bucket_tag[bi] == prefix:
                     if w is not None:
                         w.wait()
-            torch.cuda.current_stream().wait_stream(self.stream)
-        self._reset()
+                else:
+                    rest.append((bi, w))
+            self._work = rest
 
 
 class GradientBuckets(_BucketBase):
@@ -309,6 +343,14 @@ class DataParallel:
             rt.rank = dist.get_rank(process_group)   # per-rank dropout masks; LayerDrop generator stays shared
             # the engine caches bf16 operand copies per parameter version: whatever ran before the broadcast is stale
             rt.engine.weights._cache.clear()
+        if torch.cuda.is_available() and dist.get_world_size(process_group) > 1 and os.environ.get("B2T_GEMM_CLC") is None:
+            # GEMMs that share the device with NCCL kernels take their work items dynamically (cluster launch control):
+            # with the fixed persistent grid, CTAs that find their SM held by a collective start late and then run their
+            # whole strided list.  Measured at 2 GPUs (conformer-large, round 2): fixed grid 52.5 ms per step on a good
+            # run but 94-107 ms (37-56 ms of exposed all-reduce) on others of the same box; dynamic + high-priority NCCL
+            # 53.3-53.4 ms with 0.7-1.1 ms exposed, every time.  (Single-GPU training keeps the fixed grid: 2.6 % faster.)
+            from . import _lib
+            _lib.lib().b2t_gemm_set_dynamic_schedule(1)
         if early_reduce is None:
             early_reduce = os.environ.get("B2T_DP_EARLY", "1") == "1"
         arena = rt.grad_arena() if (rt is not None and hasattr(rt, "grad_arena")) else None
@@ -319,13 +361,40 @@ class DataParallel:
         else:
             self.buckets = GradientBuckets(list(model.parameters()), bucket_bytes, process_group, overlap)
 
-    def attach_optimizer(self, optimizer: torch.optim.Optimizer) -> None:
+    def attach_optimizer(self, optimizer: torch.optim.Optimizer, lazy: bool = False) -> None:
         """Belt and braces: finish() is idempotent, and backward passes driven outside autograd's engine (where the
-        end-of-backward callback cannot be queued) are still reduced before the step."""
-        optimizer.register_step_pre_hook(lambda opt, args, kwargs: self.finish())
+        end-of-backward callback cannot be queued) are still reduced before the step.
+
+        lazy=True (only with this package's FusedAdam and the arena buckets, and only when NOTHING reads gradients between
+        backward() and step() - no clip_grad_norm_): the end of backward no longer makes the compute stream wait for
+        every bucket; the optimizer updates one parameter group per launch and waits, per group, for that group's
+        buckets only.  The brain encoder's gradients are produced last, so their all-reduce then runs under the update
+        of the (much larger) wav2vec2 encoder instead of in front of the optimizer."""
+        lazy = lazy and isinstance(self.buckets, ArenaBuckets) and hasattr(optimizer, "group_wait")
+        if not lazy:
+            optimizer.register_step_pre_hook(lambda opt, args, kwargs: self.finish())
+            return
+        name_of = {id(p): n for n, p in self.model.named_parameters()}
+        prefixes = []
+        for g in optimizer.param_groups:
+            tags = {self.buckets._tag(name_of.get(id(p), "")) for p in g["params"] if p.requires_grad}
+            prefixes.append(tags.pop() if len(tags) == 1 else None)
+        if any(t is None or t == "" for t in prefixes):
+            optimizer.register_step_pre_hook(lambda opt, args, kwargs: self.finish())
+            return
+        self.buckets.lazy = True
+        # groups whose gradients are complete first go first: the arena is filled from its end, the brain encoder last
+        order = sorted(range(len(prefixes)), key=lambda gi: 0 if prefixes[gi] == "w2v_encoder." else 1)
+        optimizer.group_order = order
+        optimizer.group_wait = lambda gi: self.buckets.wait_prefix(prefixes[gi])
+        optimizer.register_step_post_hook(lambda opt, args, kwargs: self.buckets.finish(force=True))
 
     def finish(self) -> None:
-        self.buckets.finish()
+        """explicit synchronisation point (e.g. before reading gradients in lazy mode): waits for every bucket"""
+        if isinstance(self.buckets, ArenaBuckets):
+            self.buckets.finish(force=True)
+        else:
+            self.buckets.finish()
 
     def __call__(self, *a, **kw):
         return self.model(*a, **kw)

@@ -120,6 +120,10 @@ class FusedAdam(torch.optim.Optimizer):
         self._plan_key = None
         self.grad_scale: Optional[torch.Tensor] = None     # optional device scalar multiplied into every gradient
         self.launches = 0
+        # data parallel (dist.DataParallel.attach_optimizer(lazy=True)): one launch per parameter group, in `group_order`,
+        # each after group_wait(group index) has made the stream wait for that group's gradient buckets
+        self.group_wait = None
+        self.group_order = None
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -190,21 +194,33 @@ class FusedAdam(torch.optim.Optimizer):
             keep.append(g)
         if not hlist:
             return loss
-        # more hyper-parameter classes than one launch carries (LayerDrop lets the per-parameter step counts drift
-        # apart): one launch per slice of MAX_GROUPS classes, tensors of the other slices masked out (n = 0)
-        for lo in range(0, len(hlist), MAX_GROUPS):
-            sel = active & (hyper_idx >= lo) & (hyper_idx < lo + MAX_GROUPS)
+        cg_arr = np.asarray(cand_group, dtype=np.int32)
 
-            def fill(view, sel=sel, lo=lo):
-                view["p"], view["g"], view["m"], view["v"] = p_ptr, g_ptr, m_ptr, v_ptr
-                view["n"] = np.where(sel, plan.numel, 0)
-                view["group"] = np.where(sel, hyper_idx - lo, 0)
-                view["pad"] = 0
-            plan.upload(fill)
-            harr = (AdamGroup * len(hlist[lo:lo + MAX_GROUPS]))(*hlist[lo:lo + MAX_GROUPS])
-            check(lib().b2t_adam_multi(ptr(plan.dev), ptr(plan.chunks), c_int(plan.n_chunks), harr, c_int(len(harr)),
-                                       ptr(self.grad_scale), stream()), "b2t_adam_multi")
-            self.launches += 1
+        def launch(mask) -> None:
+            # more hyper-parameter classes than one launch carries (LayerDrop lets the per-parameter step counts drift
+            # apart): one launch per slice of MAX_GROUPS classes, tensors of the other slices masked out (n = 0)
+            for lo in range(0, len(hlist), MAX_GROUPS):
+                sel = mask & (hyper_idx >= lo) & (hyper_idx < lo + MAX_GROUPS)
+                if not sel.any():
+                    continue
+
+                def fill(view, sel=sel, lo=lo):
+                    view["p"], view["g"], view["m"], view["v"] = p_ptr, g_ptr, m_ptr, v_ptr
+                    view["n"] = np.where(sel, plan.numel, 0)
+                    view["group"] = np.where(sel, hyper_idx - lo, 0)
+                    view["pad"] = 0
+                plan.upload(fill)
+                harr = (AdamGroup * len(hlist[lo:lo + MAX_GROUPS]))(*hlist[lo:lo + MAX_GROUPS])
+                check(lib().b2t_adam_multi(ptr(plan.dev), ptr(plan.chunks), c_int(plan.n_chunks), harr, c_int(len(harr)),
+                                           ptr(self.grad_scale), stream()), "b2t_adam_multi")
+                self.launches += 1
+
+        if self.group_wait is None:
+            launch(active)
+        else:
+            for gi in (self.group_order or range(len(self.param_groups))):
+                self.group_wait(gi)          # the stream waits for this group's gradient buckets only
+                launch(active & (cg_arr == gi))
         return loss
 
 
