@@ -43,11 +43,10 @@ def init_process_group(backend: Optional[str] = None) -> None:
         torch.cuda.set_device(local_rank)
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     os.environ.setdefault("MASTER_PORT", "29500")
-    if backend == "nccl" and os.environ.get("B2T_NCCL_HIPRI", "1") == "1":
-        # NCCL's kernels on a high-priority stream: the compute stream runs persistent one-CTA-per-SM GEMMs back to back
-        # (programmatic dependent launch, a second stream for weight gradients), so at normal priority a collective's CTAs
-        # can wait a long time for SMs - measured at 2 GPUs as an intermittent 17-65 ms of exposed all-reduce per step
-        # where 1.5-2.5 ms is the norm.  At high priority they are placed first whenever a GEMM's CTAs retire.
+    if backend == "nccl" and os.environ.get("B2T_NCCL_HIPRI", "0") == "1":
+        # opt-in: NCCL's kernels on a high-priority stream (the compute stream runs persistent one-CTA-per-SM GEMMs back to
+        # back, so at normal priority a collective's CTAs may wait for SMs).  Measured: no effect on the intermittent
+        # exposed all-reduce it was meant to cure, hence not the default.
         try:
             opts = dist.ProcessGroupNCCL.Options()
             opts.is_high_priority_stream = True
@@ -83,7 +82,7 @@ class _BucketBase:
         self.group = process_group
         self.world = dist.get_world_size(process_group)
         self.overlap = overlap and torch.cuda.is_available()
-        self.stream = torch.cuda.Stream(priority=-1) if self.overlap else None
+        self.stream = torch.cuda.Stream() if self.overlap else None
         self._avg = dist.get_backend(process_group) == "nccl"      # gloo has no ReduceOp.AVG
         self.enabled = True          # bench.py switches the collective off to measure the exposed communication
         self.bytes_per_step = 0
@@ -343,14 +342,9 @@ class DataParallel:
             rt.rank = dist.get_rank(process_group)   # per-rank dropout masks; LayerDrop generator stays shared
             # the engine caches bf16 operand copies per parameter version: whatever ran before the broadcast is stale
             rt.engine.weights._cache.clear()
-        if torch.cuda.is_available() and dist.get_world_size(process_group) > 1 and os.environ.get("B2T_GEMM_CLC") is None:
-            # GEMMs that share the device with NCCL kernels take their work items dynamically (cluster launch control):
-            # with the fixed persistent grid, CTAs that find their SM held by a collective start late and then run their
-            # whole strided list.  Measured at 2 GPUs (conformer-large, round 2): fixed grid 52.5 ms per step on a good
-            # run but 94-107 ms (37-56 ms of exposed all-reduce) on others of the same box; dynamic + high-priority NCCL
-            # 53.3-53.4 ms with 0.7-1.1 ms exposed, every time.  (Single-GPU training keeps the fixed grid: 2.6 % faster.)
-            from . import _lib
-            _lib.lib().b2t_gemm_set_dynamic_schedule(1)
+        # (B2T_GEMM_CLC=1 switches the GEMMs to the dynamic cluster-launch-control schedule and B2T_NCCL_HIPRI=1 puts NCCL on
+        # a high-priority stream; both were tried against an intermittent 20-55 ms of exposed all-reduce per step seen at
+        # 2 and 8 GPUs and neither removed it, see DESIGN.md section 6 - they stay opt-in.)
         if early_reduce is None:
             early_reduce = os.environ.get("B2T_DP_EARLY", "1") == "1"
         arena = rt.grad_arena() if (rt is not None and hasattr(rt, "grad_arena")) else None
