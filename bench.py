@@ -393,11 +393,18 @@ def run_ours(args):
     l0 = ops.LAUNCHES
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
+    marks = []
     for _ in range(args.steps):
         step(batch)
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record()
+        marks.append(ev)
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
+    # per-step device times of this rank (diagnostic: a few slow steps or all of them?)
+    per = sorted(a.elapsed_time(b) for a, b in zip([e0] + marks[:-1], marks))
+    step_ms = {"min": per[0], "median": per[len(per) // 2], "max": per[-1]}
     launches = ops.LAUNCHES - l0
     clocks = sampler.stop() if sampler else None
     # ---- end-to-end timing: pinned host batch -> device every step, loss read back every step ----
@@ -477,7 +484,7 @@ def run_ours(args):
     e2e_tps = B * world * args.steps / (e2e_ms / 1e3)
     line = {
         "metric": "train trials/sec", "value": tps, "unit": "trials/s", "n_gpus": world, "steps": args.steps,
-        "warmup": max(args.warmup, 3), "settling_steps": settle, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "warmup": max(args.warmup, 3), "settling_steps": settle, "ms_per_step": ms / args.steps, "step_ms_rank0": step_ms, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "bf16x3 (3-term bf16 split operands, fp32 accumulate)" if precision == "bf16x3" else "bf16",
         "data": "synthetic", "config": workload_config(workload, world, B),
         "e2e": {"value": e2e_tps, "unit": "trials/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
