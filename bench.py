@@ -363,6 +363,7 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    bdist.tune_gc()      # (also what a training script would call once after building model and optimizer)
     sampler = make_sampler(local_rank) if rank == 0 else None
     if sampler:
         sampler.wait_ready()

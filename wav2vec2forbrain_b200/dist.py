@@ -58,6 +58,20 @@ def init_process_group(backend: Optional[str] = None) -> None:
     dist.init_process_group(backend=backend, rank=rank, world_size=world)
 
 
+def tune_gc() -> None:
+    """Host-side hygiene for a loop that issues ~1300 kernel launches per step from Python: everything alive now (model,
+    optimizer state, cached plans) is moved out of the garbage collector's reach and full collections are made rare.  A
+    generation-2 collection in ONE rank stalls that rank's launch stream for 100s of milliseconds, and every other rank
+    waits for it inside the next collective (round 2: 2-GPU runs whose median step was 55 ms contained single steps of
+    410 ms; B2T_GC_TUNE=0 switches this off)."""
+    if os.environ.get("B2T_GC_TUNE", "1") != "1":
+        return
+    import gc
+    gc.collect()
+    gc.freeze()
+    gc.set_threshold(200000, 100, 1000)
+
+
 def shard_indices(n: int, rank: int, world: int) -> List[int]:
     """rank r takes indices r::world of the (identically shuffled) epoch order (SURVEY.md §8e)."""
     return list(range(rank, n, world))
