@@ -225,6 +225,7 @@ def _wrap_create_model(cls, fused: bool) -> None:
         if world > 1:
             bdist.init_process_group()
             model._dp = bdist.DataParallel(model.cuda())
+            bdist.tune_gc()      # a full garbage collection in one rank stalls every rank at the next collective
         return model
     cls._create_model = _create_model
 
