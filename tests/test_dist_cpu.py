@@ -42,7 +42,9 @@ def _worker(rank, world, port, outdir):
             p.add_(rank)                   # ranks start different; DataParallel must broadcast rank 0's weights
     dp = bdist.DataParallel(m, bucket_bytes=64, overlap=False)
     opt = torch.optim.SGD(m.parameters(), lr=0.1)
-    dp.attach_optimizer(opt)
+    dp.attach_optimizer(opt, lazy=True)    # lazy needs FusedAdam + the arena buckets: anything else keeps the full wait
+    assert not getattr(dp.buckets, "lazy", False)
+    bdist.tune_gc()
     g = torch.Generator().manual_seed(100)
     data = torch.randn(2, 8, 6, generator=g)
     res = []
