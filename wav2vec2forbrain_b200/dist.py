@@ -178,6 +178,8 @@ class ArenaBuckets(_BucketBase):
     def sink(self, named) -> None:
         """named: [(parameter name, finished gradient = its arena slot)].  A bucket whose every gradient has arrived
         starts its all-reduce right away, behind everything issued so far on the compute stream."""
+        if self._ended:               # lazy mode, and no optimizer step since the last backward pass: finish that one now
+            self.finish(force=True)
         self._mark_active()
         for name, _ in named:
             bi = self.bucket_of.get(name)
@@ -206,6 +208,7 @@ class ArenaBuckets(_BucketBase):
 
     # ---- end of backward ------------------------------------------------------------------------------------
     lazy = False      # DataParallel.attach_optimizer(..., lazy=True): see wait_prefix
+    _ended = False
 
     def finish(self, force: bool = False) -> None:
         """Everything that has not left yet is launched; the compute stream then waits for all of it - unless `lazy`, where
@@ -214,7 +217,9 @@ class ArenaBuckets(_BucketBase):
             return
         self.node_end("")
         if self.lazy and not force:
+            self._ended = True        # a backward pass that starts before the optimizer ran must wait and reset first (sink)
             return
+        self._ended = False
         if self.overlap:
             for _, w in self._work:
                 if w is not None:
