@@ -581,6 +581,7 @@ def gemm_roofline(model, opt, batch, step, peaks, workload_key="base"):
         if tj:
             traffic = tj["dram_bytes_per_launch"]
     return {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05/TMA, all launches of one step)", "achieved": achieved,
+            "achieved_mma_tflops": achieved * (3.0 if getattr(getattr(getattr(model, "runtime", None), "engine", None), "three", True) else 1.0),
             "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
             "peak_source": peaks["source"] + " (sustained cuBLAS bf16)", "launches": len(rec), "gemm_ms_per_step": t_ms,
             "gemm_share_of_step": t_ms / step_ms,
