@@ -93,8 +93,8 @@ def test_bucketed_allreduce_matches_global_batch_gradient(tmp_path):
         assert torch.allclose(outs[0][2][k], p.detach(), atol=1e-6) and torch.allclose(outs[1][2][k], p.detach(), atol=1e-6)
 
 
-def _worker_model(rank, world, port, outdir):
-    """The product model classes on the ABI emulator (CPU), flat gradient arena + in-place bucket all-reduce over gloo."""
+def _product_model(rank, world, port):
+    """The product model classes on the ABI emulator (CPU), weights offset per rank (DataParallel must broadcast rank 0's)."""
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
     import sys
     sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -120,15 +120,19 @@ def _worker_model(rank, world, port, outdir):
     with torch.no_grad():
         for p in m.parameters():
             p.add_(0.01 * rank)                      # DataParallel must broadcast rank 0's weights
+    B = batch["input"].shape[0]
+    sel = [rank % B]                                 # every rank gets a shard of the same size (B = 3 in the golden)
+    mb = models.B2tSampleBatch(batch["input"][sel], batch["target"][sel])
+    mb.day_idxs, mb.input_lens, mb.target_lens = batch["day_idxs"][sel], batch["input_lens"][sel], batch["target_lens"][sel]
+    return m, mb, bdist
+
+
+def _worker_model(rank, world, port, outdir):
+    """flat gradient arena + in-place bucket all-reduce over gloo"""
+    m, mb, bdist = _product_model(rank, world, port)
     dp = bdist.DataParallel(m, bucket_bytes=4096, overlap=False)
     assert isinstance(dp.buckets, bdist.ArenaBuckets) and len(dp.buckets.buckets) > 4
     m.train()
-    B = batch["input"].shape[0]
-    sel = [b for b in range(B) if b % world == rank] if B >= world else [0]
-    # every rank gets a shard of the same size (B = 3 in the golden: trials 0 / 1)
-    sel = [rank % B]
-    mb = models.B2tSampleBatch(batch["input"][sel], batch["target"][sel])
-    mb.day_idxs, mb.input_lens, mb.target_lens = batch["day_idxs"][sel], batch["input_lens"][sel], batch["target_lens"][sel]
     res = []
     for step in range(3):
         m.zero_grad(set_to_none=True)
@@ -176,3 +180,75 @@ def test_product_model_arena_buckets_average_in_place(tmp_path):
         total = torch.sqrt(sum((v.double() ** 2).sum() for v in r0.values())).item()
         assert abs(n0 - total) < 1e-5 * total and abs(n1 - total) < 1e-5 * total   # clip saw the averaged gradients
     assert saw_skip, "layerdrop=0.5 over 3 steps should have skipped a layer at least once (seeded)"
+
+
+class _GroupedSGD(torch.optim.Optimizer):
+    """Stand-in for FusedAdam's data-parallel protocol (optim.py `group_wait` / `group_order`, CUDA only): one update per
+    parameter group, in group_order, each after group_wait(group index)."""
+
+    def __init__(self, groups):
+        super().__init__(groups, dict(lr=0.1))
+        self.group_wait = None
+        self.group_order = None
+        self.waited = []
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        for gi in (self.group_order or range(len(self.param_groups))):
+            self.group_wait(gi)
+            self.waited.append(gi)
+            for p in self.param_groups[gi]["params"]:
+                if p.grad is not None:
+                    p.add_(p.grad, alpha=-self.param_groups[gi]["lr"])
+
+
+def _worker_lazy(rank, world, port, outdir):
+    """lazy waits (bench.py's default under data parallel): the end of backward() leaves the buckets in flight, the optimizer
+    waits per parameter group (wav2vec2 encoder first), its post-hook closes the step; a backward pass that starts without an
+    optimizer step in between closes the previous reduction itself"""
+    m, mb, bdist = _product_model(rank, world, port)
+    dp = bdist.DataParallel(m, bucket_bytes=4096, overlap=False)
+    opt = _GroupedSGD([{"params": list(m.brain_encoder.parameters()), "lr": 0.05},          # the reference's two groups
+                       {"params": list(m.w2v_encoder.parameters()), "lr": 0.01}])           # (b2t_gru_w2v_experiment.py:111-128)
+    dp.attach_optimizer(opt, lazy=True)
+    bk = dp.buckets
+    assert bk.lazy and opt.group_order == [1, 0]
+    m.train()
+    res = []
+    for step in range(3):
+        m.zero_grad(set_to_none=True)
+        m.forward(mb).loss.backward()
+        assert bk._ended and bk._active and all(bk._launched[bi] for bi in range(len(bk.buckets)) if bk._seen[bi])
+        if step == 1:
+            # no optimizer step: the next backward pass has to finish this one first (sink), and must not see
+            # "arrived twice"
+            m.zero_grad(set_to_none=True)
+            m.forward(mb).loss.backward()
+            assert bk._ended and bk._active
+        grads = {k: p.grad.clone() for k, p in m.named_parameters() if p.grad is not None}
+        opt.step()
+        assert not bk._ended and not bk._active and bk._work == []
+        res.append(grads)
+    assert opt.waited == [1, 0] * 3
+    torch.save((rank, res, {k: v.detach().clone() for k, v in m.named_parameters()}), os.path.join(outdir, f"z{rank}.pt"))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_lazy_group_waits_keep_ranks_identical(tmp_path):
+    world, port = 2, _free_port()
+    ctx = mp.get_context("spawn")
+    procs = [ctx.Process(target=_worker_lazy, args=(r, world, port, str(tmp_path))) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=600)
+        assert p.exitcode == 0
+    outs = [torch.load(os.path.join(str(tmp_path), f"z{r}.pt"), weights_only=False) for r in range(world)]
+    for step in range(3):
+        g0, g1 = outs[0][1][step], outs[1][1][step]
+        assert set(g0) == set(g1)
+        for k in g0:
+            assert torch.equal(g0[k], g1[k]), (step, k)             # both ranks hold the averaged gradient
+    for k, v in outs[0][2].items():
+        assert torch.equal(v, outs[1][2][k]), k                     # and the same weights after three steps
