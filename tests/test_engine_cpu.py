@@ -118,3 +118,49 @@ def test_flat_gradient_arena_through_the_model_classes(engine_mod, monkeypatch, 
     for k, p in m.named_parameters():
         if p.grad is not None:
             assert torch.allclose(p.grad, 2 * before[k], rtol=1e-6, atol=1e-12), k
+
+
+@pytest.mark.parametrize("name", ["tiny_base", "tiny_conformer"])
+def test_training_step_leaves_no_reference_cycles(engine_mod, monkeypatch, name):
+    """dist.tune_gc() makes garbage collections rare on purpose, so a step must not create cyclic garbage: a cycle that
+    holds activations would keep device memory alive until the next collection and grow the allocator pool mid-run."""
+    import gc
+    from wav2vec2forbrain_b200 import models
+    from wav2vec2forbrain_b200.config import W2VConfig
+    monkeypatch.setattr(models, "_EMULATED", True)
+    rec, _, _, sd, batch = load_case(name)
+    be, w = rec["be"], rec["w2v"]
+    ck = "golden/cycles_" + name
+    models.register_architecture(ck, lambda **kw: W2VConfig(**dict(dict(
+        kind=w["kind"], hidden=w["hidden"], layers=w["layers"], heads=w["heads"], ffn=w["ffn"], vocab=w["vocab"],
+        pos_conv_k=w["pos_conv_k"], pos_conv_groups=w["pos_conv_groups"], dw_kernel=w["dw_kernel"],
+        hidden_act="gelu" if w["kind"] == "base" else "swish", layerdrop=0.3), **kw)), be["out_size"])
+    args = models.BrainEncoderArgs(encoder_gru_hidden_size=be["gru_hidden"], encoder_num_gru_layers=be["gru_layers"],
+                                   encoder_fc_hidden_sizes=tuple(be["fc_hidden"]), gaussian_smooth_width=be["smooth_sigma"])
+    brain = models.B2P2TModel(args, models.B2TBrainFeatureExtractor(args, ck, 256 * 32), wav2vec_checkpoint=ck)
+    m = models.W2VBrainEncoderModel(args, brain, ck, None, True) if w["kind"] == "base" else \
+        models.W2VConformerBrainEncoderModel(brain, ck)
+    m.train()
+    mb = models.B2tSampleBatch(batch["input"], batch["target"])
+    mb.day_idxs, mb.input_lens, mb.target_lens = batch["day_idxs"], batch["input_lens"], batch["target_lens"]
+    opt = torch.optim.SGD([p for p in m.parameters() if p.requires_grad], lr=1e-4)
+
+    def step():
+        opt.zero_grad(set_to_none=True)
+        out = m.forward(mb)
+        out.loss.backward()
+        _ = out.metrics["ctc_loss"]          # the lazy metrics dict is read as the Trainer reads it
+        opt.step()
+    for _ in range(2):
+        step()
+    gc.collect()
+    was_enabled = gc.isenabled()
+    gc.disable()
+    try:
+        for _ in range(3):
+            step()
+        found = gc.collect()
+    finally:
+        if was_enabled:
+            gc.enable()
+    assert found == 0, f"{found} unreachable objects after 3 training steps"
